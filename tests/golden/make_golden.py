@@ -1,0 +1,448 @@
+"""Generate golden input/output vectors by running the UNMODIFIED reference (torchmetrics 1.4.0dev).
+
+Run in the build container only (the GPU box has no /root/reference):
+
+    python tests/golden/make_golden.py
+
+It imports the reference from /root/reference/src with the 4-symbol `lightning_utilities` stand-in in
+tests/golden/_refshim, runs the hot-path functions on seeded inputs on CPU and writes
+tests/golden/*.npz. Each file holds a list of cases; every case stores its inputs, its parameters
+(JSON) and the reference's outputs, so tests never need the reference at run time.
+"""
+import json
+import os
+import sys
+import warnings
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SRC = os.environ.get("TM_REFERENCE_SRC", "/root/reference/src")
+sys.path.insert(0, REF_SRC)
+sys.path.insert(0, os.path.join(HERE, "_refshim"))
+
+import torch  # noqa: E402
+import torchmetrics  # noqa: E402
+import torchmetrics.functional.classification as F  # noqa: E402
+import importlib  # noqa: E402
+
+# the package re-exports functions under the same names as its sub-modules, so fetch the modules explicitly
+Fcm = importlib.import_module("torchmetrics.functional.classification.confusion_matrix")
+Fprc = importlib.import_module("torchmetrics.functional.classification.precision_recall_curve")
+Fss = importlib.import_module("torchmetrics.functional.classification.stat_scores")
+
+assert torchmetrics.__version__.startswith("1.4.0"), torchmetrics.__version__
+warnings.filterwarnings("ignore")
+
+
+class Book:
+    def __init__(self, name):
+        self.name = name
+        self.flat = {}
+        self.metas = []
+
+    def add(self, meta, **arrays):
+        i = len(self.metas)
+        self.metas.append(meta)
+        for k, v in arrays.items():
+            if isinstance(v, torch.Tensor):
+                v = v.detach().cpu().numpy()
+            self.flat[f"c{i}__{k}"] = np.asarray(v)
+
+    def save(self):
+        self.flat["__meta__"] = np.array(json.dumps(self.metas))
+        path = os.path.join(HERE, f"{self.name}.npz")
+        np.savez_compressed(path, **self.flat)
+        print(f"{path}: {len(self.metas)} cases, {os.path.getsize(path) / 1024:.0f} KiB")
+
+
+def rng(seed):
+    g = torch.Generator()
+    g.manual_seed(seed)
+    return g
+
+
+# ------------------------------------------------------------------ config 1: README example
+def make_readme():
+    b = Book("readme_accuracy")
+    torch.manual_seed(0)
+    micro = torchmetrics.Accuracy(task="multiclass", num_classes=5)
+    macro = torchmetrics.classification.MulticlassAccuracy(num_classes=5)
+    P, T, per_batch_micro, per_batch_macro = [], [], [], []
+    for _ in range(10):
+        preds = torch.randn(10, 5).softmax(dim=-1)
+        target = torch.randint(5, (10,))
+        per_batch_micro.append(micro(preds, target).item())
+        per_batch_macro.append(macro(preds, target).item())
+        P.append(preds)
+        T.append(target)
+    b.add({"num_classes": 5}, preds=torch.stack(P), target=torch.stack(T),
+          per_batch_micro=np.array(per_batch_micro, np.float32), per_batch_macro=np.array(per_batch_macro, np.float32),
+          final_micro=micro.compute(), final_macro=macro.compute())
+    b.save()
+
+
+# ------------------------------------------------------------------ confusion matrices
+def make_confmat():
+    b = Book("confusion_matrix")
+    seed = 100
+    for C, N in [(5, 257), (17, 4099), (128, 20000), (1000, 30011)]:
+        for ignore_index in [None, -1, 0]:
+            for dt in [torch.int64, torch.int32, torch.uint8]:
+                if dt == torch.uint8 and C > 255:
+                    continue
+                seed += 1
+                g = rng(seed)
+                preds = torch.randint(0, C, (N,), generator=g).to(dt)
+                target = torch.randint(0, C, (N,), generator=g)
+                if ignore_index is not None:
+                    m = torch.rand(N, generator=g) < 0.1
+                    target = torch.where(m, torch.tensor(ignore_index), target)
+                if dt == torch.uint8 and ignore_index == -1:
+                    continue
+                target = target.to(dt)
+                p2, t2 = Fcm._multiclass_confusion_matrix_format(preds, target, ignore_index)
+                upd = Fcm._multiclass_confusion_matrix_update(p2, t2, C)
+                pub = F.multiclass_confusion_matrix(preds, target, C, ignore_index=ignore_index, validate_args=False)
+                assert torch.equal(upd, pub)
+                b.add({"kind": "multiclass_labels", "num_classes": C, "ignore_index": ignore_index},
+                      preds=preds, target=target, confmat=upd)
+    # float preds (N, C) and (N, C, X) -> argmax
+    for C, shape in [(5, (64, 5)), (7, (33, 7, 3)), (100, (1000, 100))]:
+        seed += 1
+        g = rng(seed)
+        preds = torch.randn(*shape, generator=g)
+        tshape = (shape[0],) + tuple(shape[2:])
+        target = torch.randint(0, C, tshape, generator=g)
+        for ignore_index in [None, 1]:
+            cm = F.multiclass_confusion_matrix(preds, target, C, ignore_index=ignore_index, validate_args=False)
+            norm = F.multiclass_confusion_matrix(preds, target, C, ignore_index=ignore_index, normalize="true",
+                                                 validate_args=False)
+            b.add({"kind": "multiclass_scores", "num_classes": C, "ignore_index": ignore_index},
+                  preds=preds, target=target, confmat=cm, confmat_norm_true=norm)
+    # binary
+    for kind in ["labels", "probs", "logits"]:
+        for shape in [(301,), (40, 7)]:
+            for ignore_index in [None, -1]:
+                seed += 1
+                g = rng(seed)
+                if kind == "labels":
+                    preds = torch.randint(0, 2, shape, generator=g)
+                elif kind == "probs":
+                    preds = torch.rand(*shape, generator=g)
+                else:
+                    preds = torch.randn(*shape, generator=g) * 3
+                target = torch.randint(0, 2, shape, generator=g)
+                if ignore_index is not None:
+                    target = torch.where(torch.rand(*shape, generator=g) < 0.15, torch.tensor(ignore_index), target)
+                cm = F.binary_confusion_matrix(preds, target, threshold=0.4, ignore_index=ignore_index,
+                                               validate_args=False)
+                b.add({"kind": "binary_" + kind, "threshold": 0.4, "ignore_index": ignore_index},
+                      preds=preds, target=target, confmat=cm)
+    # multilabel
+    for kind in ["labels", "probs", "logits"]:
+        for shape in [(203, 6), (50, 4, 5)]:
+            for ignore_index in [None, -1]:
+                seed += 1
+                g = rng(seed)
+                L = shape[1]
+                if kind == "labels":
+                    preds = torch.randint(0, 2, shape, generator=g)
+                elif kind == "probs":
+                    preds = torch.rand(*shape, generator=g)
+                else:
+                    preds = torch.randn(*shape, generator=g) * 3
+                target = torch.randint(0, 2, shape, generator=g)
+                if ignore_index is not None:
+                    target = torch.where(torch.rand(*shape, generator=g) < 0.15, torch.tensor(ignore_index), target)
+                cm = F.multilabel_confusion_matrix(preds, target, L, threshold=0.5, ignore_index=ignore_index,
+                                                   validate_args=False)
+                b.add({"kind": "multilabel_" + kind, "num_labels": L, "threshold": 0.5, "ignore_index": ignore_index},
+                      preds=preds, target=target, confmat=cm)
+    b.save()
+
+
+# ------------------------------------------------------------------ stat scores + derived metrics
+def make_stat_scores():
+    b = Book("stat_scores")
+    seed = 500
+    # binary
+    for kind in ["labels", "probs", "logits"]:
+        for shape in [(311,), (30, 5, 2)]:
+            for ignore_index in [None, -1, 0]:
+                for mda in ["global", "samplewise"]:
+                    if mda == "samplewise" and len(shape) == 1:
+                        continue
+                    seed += 1
+                    g = rng(seed)
+                    preds = {"labels": lambda: torch.randint(0, 2, shape, generator=g),
+                             "probs": lambda: torch.rand(*shape, generator=g),
+                             "logits": lambda: torch.randn(*shape, generator=g) * 2}[kind]()
+                    target = torch.randint(0, 2, shape, generator=g)
+                    if ignore_index is not None:
+                        target = torch.where(torch.rand(*shape, generator=g) < 0.2, torch.tensor(ignore_index), target)
+                    kw = dict(threshold=0.5, multidim_average=mda, ignore_index=ignore_index, validate_args=False)
+                    ss = F.binary_stat_scores(preds, target, **kw)
+                    out = {"stat_scores": ss}
+                    for name in ["accuracy", "precision", "recall", "f1_score", "specificity"]:
+                        out[name] = getattr(F, "binary_" + name)(preds, target, **kw)
+                    out["fbeta2"] = F.binary_fbeta_score(preds, target, beta=2.0, **kw)
+                    b.add({"kind": "binary_" + kind, "threshold": 0.5, "ignore_index": ignore_index,
+                           "multidim_average": mda}, preds=preds, target=target, **out)
+    # multilabel
+    for kind in ["labels", "probs", "logits"]:
+        for shape in [(257, 6), (40, 4, 3), (64, 100)]:
+            for ignore_index in [None, -1]:
+                for mda in ["global", "samplewise"]:
+                    if mda == "samplewise" and len(shape) == 2:
+                        continue
+                    seed += 1
+                    g = rng(seed)
+                    L = shape[1]
+                    preds = {"labels": lambda: torch.randint(0, 2, shape, generator=g),
+                             "probs": lambda: torch.rand(*shape, generator=g),
+                             "logits": lambda: torch.randn(*shape, generator=g) * 2}[kind]()
+                    target = torch.randint(0, 2, shape, generator=g)
+                    if ignore_index is not None:
+                        target = torch.where(torch.rand(*shape, generator=g) < 0.2, torch.tensor(ignore_index), target)
+                    out = {}
+                    for avg in ["micro", "macro", "weighted", "none"]:
+                        kw = dict(num_labels=L, threshold=0.5, average=avg, multidim_average=mda,
+                                  ignore_index=ignore_index, validate_args=False)
+                        out["stat_scores_" + avg] = F.multilabel_stat_scores(preds, target, **kw)
+                        for name in ["accuracy", "precision", "recall", "f1_score"]:
+                            out[f"{name}_{avg}"] = getattr(F, "multilabel_" + name)(preds, target, **kw)
+                    b.add({"kind": "multilabel_" + kind, "num_labels": L, "threshold": 0.5,
+                           "ignore_index": ignore_index, "multidim_average": mda}, preds=preds, target=target, **out)
+    # multiclass
+    for kind in ["labels", "scores"]:
+        for C, shape in [(5, (203,)), (5, (31, 4)), (11, (500,))]:
+            for ignore_index in [None, -1, 1]:
+                for mda in ["global", "samplewise"]:
+                    if mda == "samplewise" and len(shape) == 1:
+                        continue
+                    for top_k in [1, 2]:
+                        if top_k != 1 and kind == "labels":
+                            continue
+                        seed += 1
+                        g = rng(seed)
+                        if kind == "labels":
+                            preds = torch.randint(0, C, shape, generator=g)
+                        else:
+                            preds = torch.randn(shape[0], C, *shape[1:], generator=g)
+                        target = torch.randint(0, C, shape, generator=g)
+                        if ignore_index is not None:
+                            target = torch.where(torch.rand(*shape, generator=g) < 0.2, torch.tensor(ignore_index),
+                                                 target)
+                        out = {}
+                        for avg in ["micro", "macro", "weighted", "none"]:
+                            kw = dict(num_classes=C, average=avg, top_k=top_k, multidim_average=mda,
+                                      ignore_index=ignore_index, validate_args=False)
+                            out["stat_scores_" + avg] = F.multiclass_stat_scores(preds, target, **kw)
+                            for name in ["accuracy", "precision", "recall", "f1_score"]:
+                                out[f"{name}_{avg}"] = getattr(F, "multiclass_" + name)(preds, target, **kw)
+                        b.add({"kind": "multiclass_" + kind, "num_classes": C, "top_k": top_k,
+                               "ignore_index": ignore_index, "multidim_average": mda},
+                              preds=preds, target=target, **out)
+    b.save()
+
+
+# ------------------------------------------------------------------ binned curves
+def make_binned():
+    b = Book("binned_curve")
+    seed = 900
+    thr200 = torch.linspace(0, 1, 200)
+    # binary: small (vectorised variant) and > 50 000 (loop variant, the one config 3 exercises)
+    cases = [
+        ("probs", 1000, 200, None), ("probs", 60_001, 200, None), ("probs", 60_001, 5, None),
+        ("logits", 3000, 200, None), ("logits", 52_000, 50, -1), ("probs", 4000, "list_unsorted", -1),
+        ("special", 0, 200, None), ("grid", 20_000, 200, None), ("probs", 2500, "tensor17", None),
+    ]
+    for kind, N, thr, ignore_index in cases:
+        seed += 1
+        g = rng(seed)
+        if kind == "probs":
+            preds = torch.rand(N, generator=g)
+        elif kind == "logits":
+            preds = torch.randn(N, generator=g) * 3
+        elif kind == "grid":
+            # every score is exactly one of the reference's own fp32 thresholds (or one ulp either side)
+            idx = torch.randint(0, 200, (N,), generator=g)
+            preds = thr200[idx].clone()
+            bump = torch.randint(0, 3, (N,), generator=g)
+            preds = torch.where(bump == 1, torch.nextafter(preds, torch.tensor(2.0)), preds)
+            preds = torch.where(bump == 2, torch.nextafter(preds, torch.tensor(-1.0)), preds).clamp(0, 1)
+        else:
+            preds = torch.tensor([0.0, -0.0, 1.0, 0.5, 0.25, 0.75, 1e-45, 1 - 2**-24, 2**-24, 0.5000001, 0.4999999,
+                                  float(thr200[57]), float(thr200[101]), float(thr200[199]), float(thr200[1])],
+                                 dtype=torch.float32)
+            N = preds.numel()
+        target = (torch.rand(N, generator=g) < 0.3 + 0.4 * preds.clamp(0, 1)).long()
+        if ignore_index is not None:
+            target = torch.where(torch.rand(N, generator=g) < 0.1, torch.tensor(ignore_index), target)
+        if thr == "list_unsorted":
+            thr_arg = [0.7, 0.1, 0.5, 0.30000001192092896, 0.9, 0.0, 1.0, 0.5]
+        elif thr == "tensor17":
+            thr_arg = torch.sort(torch.rand(17, generator=g)).values
+        else:
+            thr_arg = thr
+        p2, t2, thr_t = Fprc._binary_precision_recall_curve_format(preds, target, thr_arg, ignore_index)
+        state = Fprc._binary_precision_recall_curve_update(p2, t2, thr_t)
+        if 0 < p2.numel() <= 50_000:
+            loop = Fprc._binary_precision_recall_curve_update_loop(p2, t2, thr_t)
+            assert torch.equal(loop, state)
+        kw = dict(thresholds=thr_arg, ignore_index=ignore_index, validate_args=False)
+        prec, rec, _ = F.binary_precision_recall_curve(preds, target, **kw)
+        fpr, tpr, _ = F.binary_roc(preds, target, **kw)
+        b.add({"kind": "binary_" + kind, "ignore_index": ignore_index,
+               "thresholds_arg": thr if isinstance(thr, (int, str)) else None},
+              preds=preds, target=target, thresholds=thr_t, confmat=state,
+              **({"formatted_preds": p2} if kind == "logits" else {}),
+              auroc=F.binary_auroc(preds, target, **kw), ap=F.binary_average_precision(preds, target, **kw),
+              auroc_maxfpr=F.binary_auroc(preds, target, max_fpr=0.3, **kw),
+              precision=prec, recall=rec, fpr=fpr, tpr=tpr)
+    # multiclass: vectorised (N*C*C <= 1e6) and loop
+    for kind, N, C, T, ignore_index in [("probs", 500, 5, 50, None), ("logits", 700, 7, 20, -1),
+                                        ("probs", 28_000, 6, 30, None), ("logits", 1200, 40, 10, 3)]:
+        seed += 1
+        g = rng(seed)
+        preds = torch.randn(N, C, generator=g)
+        if kind == "probs":
+            preds = preds.softmax(1)
+        target = torch.randint(0, C, (N,), generator=g)
+        if ignore_index is not None:
+            target = torch.where(torch.rand(N, generator=g) < 0.1, torch.tensor(ignore_index), target)
+        out = {}
+        for avg in [None, "micro"]:
+            p2, t2, thr_t = Fprc._multiclass_precision_recall_curve_format(preds, target, C, T, ignore_index, avg)
+            out["confmat_" + str(avg)] = Fprc._multiclass_precision_recall_curve_update(p2, t2, C, thr_t, avg)
+            if kind == "logits" and avg is None:
+                out["formatted_preds"] = p2
+        kw = dict(num_classes=C, thresholds=T, ignore_index=ignore_index, validate_args=False)
+        for avg in ["macro", "weighted", "none"]:
+            out["auroc_" + avg] = F.multiclass_auroc(preds, target, average=avg, **kw)
+            out["ap_" + avg] = F.multiclass_average_precision(preds, target, average=avg, **kw)
+        b.add({"kind": "multiclass_" + kind, "num_classes": C, "ignore_index": ignore_index, "thresholds_arg": T},
+              preds=preds, target=target, thresholds=thr_t, **out)
+    # multilabel
+    for kind, shape, T, ignore_index in [("probs", (400, 5), 50, None), ("logits", (300, 4, 3), 20, -1),
+                                         ("probs", (2000, 100), 11, None)]:
+        seed += 1
+        g = rng(seed)
+        L = shape[1]
+        preds = torch.rand(*shape, generator=g) if kind == "probs" else torch.randn(*shape, generator=g) * 2
+        target = torch.randint(0, 2, shape, generator=g)
+        if ignore_index is not None:
+            target = torch.where(torch.rand(*shape, generator=g) < 0.1, torch.tensor(ignore_index), target)
+        p2, t2, thr_t = Fprc._multilabel_precision_recall_curve_format(preds, target, L, T, ignore_index)
+        state = Fprc._multilabel_precision_recall_curve_update(p2, t2, L, thr_t)
+        out = {}
+        kw = dict(num_labels=L, thresholds=T, ignore_index=ignore_index, validate_args=False)
+        for avg in ["micro", "macro", "weighted", "none"]:
+            out["auroc_" + avg] = F.multilabel_auroc(preds, target, average=avg, **kw)
+            out["ap_" + avg] = F.multilabel_average_precision(preds, target, average=avg, **kw)
+        b.add({"kind": "multilabel_" + kind, "num_labels": L, "ignore_index": ignore_index, "thresholds_arg": T},
+              preds=preds, target=target, thresholds=thr_t, confmat=state, **out)
+    b.save()
+
+
+# ------------------------------------------------------------------ exact curves
+def make_exact():
+    b = Book("exact_curve")
+    seed = 1300
+    for kind, N, ignore_index in [("probs", 1000, None), ("ties", 5000, None), ("logits", 3000, -1),
+                                  ("probs", 70_000, None), ("allpos", 50, None), ("allneg", 50, None),
+                                  ("probs", 1, None), ("ties", 40_000, -1)]:
+        seed += 1
+        g = rng(seed)
+        if kind == "ties":
+            preds = torch.randint(0, 64, (N,), generator=g).float() / 63
+        elif kind == "logits":
+            preds = torch.randn(N, generator=g) * 3
+        else:
+            preds = torch.rand(N, generator=g)
+        target = (torch.rand(N, generator=g) < 0.3 + 0.4 * preds.clamp(0, 1)).long()
+        if kind == "allpos":
+            target = torch.ones(N, dtype=torch.long)
+        if kind == "allneg":
+            target = torch.zeros(N, dtype=torch.long)
+        if ignore_index is not None:
+            target = torch.where(torch.rand(N, generator=g) < 0.1, torch.tensor(ignore_index), target)
+        p2, t2, _ = Fprc._binary_precision_recall_curve_format(preds, target, None, ignore_index)
+        fps, tps, thr = Fprc._binary_clf_curve(p2, t2)
+        kw = dict(thresholds=None, ignore_index=ignore_index, validate_args=False)
+        prec, rec, pthr = F.binary_precision_recall_curve(preds, target, **kw)
+        fpr, tpr, rthr = F.binary_roc(preds, target, **kw)
+        b.add({"kind": "binary_" + kind, "ignore_index": ignore_index}, preds=preds, target=target,
+              fps=fps, tps=tps, thr=thr,
+              auroc=F.binary_auroc(preds, target, **kw), ap=F.binary_average_precision(preds, target, **kw),
+              auroc_maxfpr=F.binary_auroc(preds, target, max_fpr=0.25, **kw),
+              precision=prec, recall=rec, pr_thresholds=pthr, fpr=fpr, tpr=tpr, roc_thresholds=rthr)
+    # multiclass / multilabel exact scalars
+    for C, N, ignore_index in [(5, 600, None), (4, 900, -1)]:
+        seed += 1
+        g = rng(seed)
+        preds = torch.randn(N, C, generator=g).softmax(1)
+        target = torch.randint(0, C, (N,), generator=g)
+        if ignore_index is not None:
+            target = torch.where(torch.rand(N, generator=g) < 0.1, torch.tensor(ignore_index), target)
+        out = {}
+        kw = dict(num_classes=C, thresholds=None, ignore_index=ignore_index, validate_args=False)
+        for avg in ["macro", "weighted", "none"]:
+            out["auroc_" + avg] = F.multiclass_auroc(preds, target, average=avg, **kw)
+            out["ap_" + avg] = F.multiclass_average_precision(preds, target, average=avg, **kw)
+        b.add({"kind": "multiclass", "num_classes": C, "ignore_index": ignore_index}, preds=preds, target=target,
+              **out)
+    for L, N, ignore_index in [(5, 600, None), (3, 900, -1)]:
+        seed += 1
+        g = rng(seed)
+        preds = torch.rand(N, L, generator=g)
+        target = torch.randint(0, 2, (N, L), generator=g)
+        if ignore_index is not None:
+            target = torch.where(torch.rand(N, L, generator=g) < 0.1, torch.tensor(ignore_index), target)
+        out = {}
+        kw = dict(num_labels=L, thresholds=None, ignore_index=ignore_index, validate_args=False)
+        for avg in ["micro", "macro", "weighted", "none"]:
+            out["auroc_" + avg] = F.multilabel_auroc(preds, target, average=avg, **kw)
+            out["ap_" + avg] = F.multilabel_average_precision(preds, target, average=avg, **kw)
+        b.add({"kind": "multilabel", "num_labels": L, "ignore_index": ignore_index}, preds=preds, target=target,
+              **out)
+    b.save()
+
+
+# ------------------------------------------------------------------ doctest known answers (reference docstrings)
+def make_doctests():
+    b = Book("doctest_known_answers")
+    # functional/classification/confusion_matrix.py:388-408
+    t = torch.tensor([2, 1, 0, 0]); p = torch.tensor([2, 1, 0, 1])
+    b.add({"fn": "multiclass_confusion_matrix", "num_classes": 3}, preds=p, target=t,
+          out=F.multiclass_confusion_matrix(p, t, num_classes=3))
+    # functional/classification/confusion_matrix.py:204-219
+    t = torch.tensor([1, 1, 0, 0]); p = torch.tensor([0.35, 0.85, 0.48, 0.01])
+    b.add({"fn": "binary_confusion_matrix"}, preds=p, target=t, out=F.binary_confusion_matrix(p, t))
+    # functional/classification/confusion_matrix.py:579-596
+    t = torch.tensor([[0, 1, 0], [1, 0, 1]]); p = torch.tensor([[0.11, 0.22, 0.84], [0.73, 0.33, 0.92]])
+    b.add({"fn": "multilabel_confusion_matrix", "num_labels": 3}, preds=p, target=t,
+          out=F.multilabel_confusion_matrix(p, t, num_labels=3))
+    # functional/classification/precision_recall_curve.py:340-351
+    p = torch.tensor([0, 0.5, 0.7, 0.8]); t = torch.tensor([0, 1, 1, 0])
+    for thr in [None, 5]:
+        pr, rc, th = F.binary_precision_recall_curve(p, t, thresholds=thr)
+        b.add({"fn": "binary_precision_recall_curve", "thresholds": thr}, preds=p, target=t, precision=pr, recall=rc,
+              thresholds=th)
+        b.add({"fn": "binary_auroc", "thresholds": thr}, preds=p, target=t, out=F.binary_auroc(p, t, thresholds=thr))
+    # functional/classification/stat_scores.py:772-809
+    t = torch.tensor([[0, 1, 0], [1, 0, 1]]); p = torch.tensor([[0, 0, 1], [1, 0, 1]])
+    b.add({"fn": "multilabel_stat_scores", "num_labels": 3}, preds=p, target=t,
+          out=F.multilabel_stat_scores(p, t, num_labels=3),
+          out_none=F.multilabel_stat_scores(p, t, num_labels=3, average=None))
+    b.save()
+
+
+if __name__ == "__main__":
+    make_readme()
+    make_confmat()
+    make_stat_scores()
+    make_binned()
+    make_exact()
+    make_doctests()
