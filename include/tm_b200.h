@@ -1,0 +1,137 @@
+/*
+ * tm_b200.h — C ABI of the B200-native metric-state hot path (libtm_b200.so).
+ *
+ * The reference (torchmetrics 1.4.0dev) is pure Python: its "FFI" for this path is the set of private
+ * `_*_update` functions in src/torchmetrics/functional/classification/ that the Metric classes call.
+ * Each entry point below replaces the device work of one of those functions; the citation names it
+ * (paths relative to /root/reference/src/torchmetrics).  INTEGRATION.md shows the ctypes binding a
+ * maintainer of the reference would add at each call site.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch types.  `stream` is a cudaStream_t passed as void*
+ *     (NULL = the legacy default stream).  All work is enqueued on `stream`; nothing synchronises
+ *     unless the function name ends in `_host`.
+ *   - every pointer named *_dev is device memory of the CURRENT device (cudaSetDevice by the caller).
+ *   - count outputs are int64 and are ACCUMULATED INTO (state += update), never overwritten, so a
+ *     metric state can be passed directly; pass a zeroed buffer to get the bare update.
+ *   - return value: TMB_OK or a negative TMB_ERR_* (argument / launch errors, detected on the host).
+ *     Data errors (labels out of range, unsorted thresholds) are detected on the device and reported
+ *     through the int32 `status_dev[0]` word as TMB_STATUS_* bits, which the caller reads when it wants
+ *     to pay for the synchronisation (the Python layer does so lazily, on compute()).
+ *   - vector loads need natural alignment of the element type times the vector width: every data
+ *     pointer must be 32-byte aligned (torch allocations are; offset views must be copied first).
+ */
+#ifndef TM_B200_H
+#define TM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TMB_ABI_VERSION 1
+
+/* the library is built with -fvisibility=hidden; only these entry points are exported */
+#if defined(__GNUC__)
+#define TMB_API __attribute__((visibility("default")))
+#else
+#define TMB_API
+#endif
+
+/* return codes */
+#define TMB_OK 0
+#define TMB_ERR_ARG (-1)        /* bad size / null pointer / unsupported dtype            */
+#define TMB_ERR_ALIGN (-2)      /* a data pointer is not 32-byte aligned                  */
+#define TMB_ERR_CUDA (-3)       /* a CUDA runtime call failed; see tmb_last_cuda_error()  */
+#define TMB_ERR_TOO_LARGE (-4)  /* problem does not fit this entry point's stated limits  */
+
+/* bits written (OR-ed) into status_dev[0] by kernels */
+#define TMB_STATUS_LABEL_RANGE 1      /* key = target*C + pred outside [0, C*C): the reference raises here */
+#define TMB_STATUS_THRESHOLD_ORDER 2  /* thresholds not ascending                                         */
+#define TMB_STATUS_OUT_OF_UNIT_RANGE 4 /* TMB_PROB_CHECK: a score outside [0,1] was seen, update discarded   */
+
+/* element types (labels: I64, I32, U8; scores: F32, F16, BF16, F64 — cast anything else first) */
+#define TMB_I64 0
+#define TMB_I32 1
+#define TMB_U8 4  /* also torch.bool */
+#define TMB_F32 8
+#define TMB_F16 9
+#define TMB_BF16 10
+#define TMB_F64 11
+
+/* how float scores are mapped to probabilities before thresholding */
+#define TMB_PROB_AS_IS 0 /* use the scores unchanged                                                              */
+#define TMB_PROB_AUTO 1  /* reference rule: sigmoid the whole batch iff any (non-ignored) score lies outside [0,1] */
+#define TMB_PROB_SIGMOID 2 /* always apply sigmoid                                                                 */
+#define TMB_PROB_CHECK 3 /* as-is, but if any score lies outside [0,1] discard the update and set
+                            TMB_STATUS_OUT_OF_UNIT_RANGE (multiclass: the caller then applies softmax itself)     */
+
+TMB_API int tmb_abi_version(void);
+TMB_API const char* tmb_last_cuda_error(void);
+/* number of SMs of the current device (grid sizing; 148 on B200) */
+TMB_API int tmb_sm_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * K1  confusion-matrix update from label tensors.
+ * Replaces: functional/classification/confusion_matrix.py:333-337 `_multiclass_confusion_matrix_update`
+ *           (key = target*C + pred; `_bincount`, utilities/data.py:179-207) fused with the ignore_index
+ *           filter of `_multiclass_confusion_matrix_format` (:325-328); same kernel serves the
+ *           confusion-matrix branch of `_multiclass_stat_scores_update` (stat_scores.py:405-418) and
+ *           `_binary_confusion_matrix_update` (:149-153, C = 2).
+ * preds_dev/target_dev: n labels of the given integer dtype.  confmat_dev: C*C int64, row = target.
+ * Keys outside [0, C*C) set TMB_STATUS_LABEL_RANGE and are not counted (the reference raises).
+ * algo: 0 = choose by C; 1 = global 64-bit RED straight into confmat_dev; 2 = shared-memory privatised.
+ * ------------------------------------------------------------------------------------------- */
+TMB_API int tmb_confmat_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype, int64_t n,
+                       int64_t num_classes, int has_ignore, int64_t ignore_index, int64_t* confmat_dev,
+                       int32_t* status_dev, int algo, void* stream);
+
+/* Multiclass micro statistics: n_valid and n_equal (tp = n_equal, fp = fn = n_valid - n_equal).
+ * Replaces: stat_scores.py:394-404 (the `average="micro"` branch).  out2_dev: int64[2] += {n_valid, n_equal}. */
+TMB_API int tmb_match_count_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype, int64_t n,
+                           int has_ignore, int64_t ignore_index, int64_t* out2_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K3  binned (multi-threshold) curve state update.
+ * Replaces: functional/classification/precision_recall_curve.py:190-250
+ *           `_binary_precision_recall_curve_update` (+ `_update_vectorized`, `_update_loop`) fused with the
+ *           per-element steps of `_binary_precision_recall_curve_format` (:176-184: ignore filter and the
+ *           all-or-nothing sigmoid), and, with num_columns > 1, `_multilabel_..._update` (:769-793) /
+ *           `_multiclass_..._update` (:458-527).
+ * preds_dev: n_rows*num_columns scores, row-major.  target_dev: num_columns == 1 or !target_is_class_index:
+ * same shape, positive iff == 1; target_is_class_index: n_rows class ids (one-hot on the fly, multiclass).
+ * thresholds_dev: T ascending float32 values (the caller's own tensor: never recomputed).
+ * confmat_dev: (T, num_columns, 2, 2) int64, [t][c][target][pred] as in the reference, accumulated.
+ * workspace_dev: tmb_binned_curve_workspace_bytes() bytes, ZERO on first use; the kernels leave it zero.
+ * One workspace must not be shared by calls that may overlap on the GPU.
+ * ------------------------------------------------------------------------------------------- */
+TMB_API size_t tmb_binned_curve_workspace_bytes(int num_thresholds, int64_t num_columns);
+TMB_API int tmb_binned_curve_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
+                            int64_t n_rows, int64_t num_columns, int target_is_class_index,
+                            const float* thresholds_dev, int num_thresholds, int has_ignore, int64_t ignore_index,
+                            int prob_mode, int64_t* confmat_dev, void* workspace_dev, size_t workspace_bytes,
+                            int32_t* status_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K2  tp / fp / tn / fn per label.
+ * Replaces: functional/classification/stat_scores.py:120-131 `_binary_stat_scores_update` and :672-681
+ *           `_multilabel_stat_scores_update` (multidim_average="global"), fused with `_format`
+ *           (:90-117, :647-669: all-or-nothing sigmoid, strict `preds > threshold`, ignore_index -> no count).
+ * preds_dev/target_dev: (n_rows, num_labels) row-major (binary: num_labels = 1, n_rows = numel).
+ * Float preds are thresholded (strict >, threshold rounded to the preds dtype as torch does for a Python
+ * scalar); integer preds are compared to target as labels.
+ * out_dev: int64[4 * num_labels] laid out [tp | fp | tn | fn], accumulated.
+ * workspace_dev: tmb_stat_scores_workspace_bytes() bytes, zero on first use, left zero.
+ * ------------------------------------------------------------------------------------------- */
+TMB_API size_t tmb_stat_scores_workspace_bytes(int64_t num_labels);
+TMB_API int tmb_stat_scores_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
+                           int64_t n_rows, int64_t num_labels, double threshold, int prob_mode, int has_ignore,
+                           int64_t ignore_index, int64_t* out_dev, void* workspace_dev, size_t workspace_bytes,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TM_B200_H */

@@ -1,0 +1,438 @@
+"""Parity of the CUDA kernels (called through the C ABI via torchmetrics_b200._native) with the oracle and
+with golden vectors from the reference. Integer states must be bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import case_id, load_golden
+from oracle import oracle_np as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def _native():
+    from torchmetrics_b200 import _native
+
+    return _native
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+# =========================================================================== K1 confusion matrix
+@pytest.mark.parametrize("c", [c for c in load_golden("confusion_matrix") if c.meta["kind"] == "multiclass_labels"],
+                         ids=case_id)
+@pytest.mark.parametrize("algo", [0, 1, 2])
+def test_confmat_golden(c, algo):
+    N = _native()
+    C = c.meta["num_classes"]
+    if algo == 2 and C * C * 4 > 200 * 1024:
+        pytest.skip("does not fit shared memory")
+    cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+    N.confmat_update_(cm, torch.from_numpy(c["preds"]).to(DEV), torch.from_numpy(c["target"]).to(DEV), C,
+                      c.meta["ignore_index"], algo=algo)
+    assert np.array_equal(_np(cm), c["confmat"])
+    assert N.read_status(torch.device(DEV)) == 0
+
+
+@pytest.mark.parametrize("C,n", [(2, 1), (2, 3), (3, 4), (5, 1023), (10, 65537), (64, 1 << 20), (1000, 1 << 22),
+                                 (1000, (1 << 22) + 3), (3000, 1 << 20)])
+@pytest.mark.parametrize("dt", [torch.int64, torch.int32, torch.uint8])
+def test_confmat_seeded_vs_oracle(C, n, dt):
+    if dt == torch.uint8 and C > 255:
+        pytest.skip("labels do not fit")
+    N = _native()
+    g = torch.Generator().manual_seed(C * 31 + n)
+    p = torch.randint(0, C, (n,), generator=g).to(dt)
+    t = torch.randint(0, C, (n,), generator=g).to(dt)
+    cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+    N.confmat_update_(cm, p.to(DEV), t.to(DEV), C)
+    N.confmat_update_(cm, p.to(DEV), t.to(DEV), C)  # accumulates
+    want = O.multiclass_confusion_matrix_update(p.numpy(), t.numpy(), C) * 2
+    assert np.array_equal(_np(cm), want)
+    assert int(cm.sum()) == 2 * n
+
+
+def test_confmat_diagonal_heavy_and_single_cell():
+    N = _native()
+    C, n = 1000, 1 << 21
+    g = torch.Generator().manual_seed(5)
+    t = torch.randint(0, C, (n,), generator=g)
+    p = torch.where(torch.rand(n, generator=g) < 0.8, t, torch.randint(0, C, (n,), generator=g))
+    for pp, tt in [(p, t), (torch.full((n,), 7), torch.full((n,), 7))]:
+        for algo, CC in [(1, C), (2, 16)]:
+            pp2, tt2 = pp % CC, tt % CC
+            cm = torch.zeros(CC, CC, dtype=torch.int64, device=DEV)
+            N.confmat_update_(cm, pp2.to(DEV), tt2.to(DEV), CC, algo=algo)
+            assert np.array_equal(_np(cm), O.multiclass_confusion_matrix_update(pp2.numpy(), tt2.numpy(), CC))
+
+
+def test_confmat_out_of_range_sets_status():
+    N = _native()
+    dev = torch.device(DEV)
+    C = 5
+    p = torch.tensor([0, 1, 2, 3, 4, 1, 1, 1, 2], device=DEV)
+    t = torch.tensor([0, 1, 2, 3, 5, 1, -1, 1, 2], device=DEV)  # 5 and -1 are out of range
+    cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+    N.confmat_update_(cm, p, t, C)
+    with pytest.raises(RuntimeError, match="outside the expected range"):
+        N.raise_on_status(dev, C)
+    assert N.read_status(dev) == 0  # cleared
+    # like the reference, a too-large pred whose key still lands inside C*C is counted at the aliased cell
+    cm.zero_()
+    N.confmat_update_(cm, torch.tensor([0, 5], device=DEV), torch.tensor([1, 1], device=DEV), C)
+    assert np.array_equal(_np(cm), O.multiclass_confusion_matrix_update(np.array([0, 5]), np.array([1, 1]), C))
+    assert N.read_status(dev) == 0
+
+
+def test_confmat_empty_and_unaligned():
+    N = _native()
+    cm = torch.zeros(3, 3, dtype=torch.int64, device=DEV)
+    e = torch.zeros(0, dtype=torch.int64, device=DEV)
+    N.confmat_update_(cm, e, e, 3)
+    assert int(cm.sum()) == 0
+    base = torch.randint(0, 3, (1001,), device=DEV)
+    p, t = base[1:], base[:-1]  # p is an 8-byte-offset view: the binding must realign it
+    N.confmat_update_(cm, p, t, 3)
+    assert np.array_equal(_np(cm), O.multiclass_confusion_matrix_update(_np(p), _np(t), 3))
+
+
+def test_match_count():
+    N = _native()
+    g = torch.Generator().manual_seed(3)
+    for n in [1, 5, 1000, (1 << 20) + 1]:
+        p = torch.randint(0, 7, (n,), generator=g)
+        t = torch.randint(-1, 7, (n,), generator=g)
+        out = torch.zeros(2, dtype=torch.int64, device=DEV)
+        N.match_count_update_(out, p.to(DEV), t.to(DEV), ignore_index=-1)
+        valid = t != -1
+        assert out.tolist() == [int(valid.sum()), int(((p == t) & valid).sum())]
+
+
+# =========================================================================== K3 binned curve
+def _binned(N, preds, target, thr, ignore_index=None, prob_mode=None, num_columns=1, class_index=False):
+    T = thr.numel()
+    shape = (T, 2, 2) if num_columns == 1 else (T, num_columns, 2, 2)
+    state = torch.zeros(shape, dtype=torch.int64, device=DEV)
+    N.binned_curve_update_(state, preds.to(DEV), target.to(DEV), thr.to(DEV), num_columns=num_columns,
+                           target_is_class_index=class_index, ignore_index=ignore_index,
+                           prob_mode=N.PROB_AUTO if prob_mode is None else prob_mode)
+    return state
+
+
+@pytest.mark.parametrize("c", [c for c in load_golden("binned_curve") if c.meta["kind"].startswith("binary")],
+                         ids=case_id)
+def test_binned_binary_golden(c):
+    N = _native()
+    thr = torch.from_numpy(c["thresholds"])
+    sthr, order = torch.sort(thr)
+    preds, target = torch.from_numpy(c["preds"]), torch.from_numpy(c["target"])
+    state = _binned(N, preds, target, sthr, c.meta["ignore_index"])
+    got = torch.empty_like(state)
+    got[order.to(DEV)] = state
+    if "formatted_preds" in c:
+        # logits: the golden state used ATen's CPU sigmoid; ours must equal ATen's CUDA sigmoid bit for bit,
+        # so rebuild the expectation from torch.sigmoid on the device and the (pinned) oracle
+        keep = c["target"] != c.meta["ignore_index"] if c.meta["ignore_index"] is not None else slice(None)
+        sp = _np(torch.from_numpy(c["preds"][keep]).to(DEV).sigmoid())
+        want = O.binary_precision_recall_curve_update_loop(sp, c["target"][keep], c["thresholds"])
+        assert np.array_equal(_np(got), want)
+        # and it can differ from the CPU-sigmoid golden only where a score sits within an ulp of a threshold
+        assert np.abs(_np(got) - c["confmat"]).max() <= 2
+    else:
+        assert np.array_equal(_np(got), c["confmat"])
+    assert N.read_status(torch.device(DEV)) == 0
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 4, 5, 2047, 2048, 2049, 100_000, (1 << 22) + 1])
+@pytest.mark.parametrize("T", [1, 2, 5, 200, 427, 428, 1000, 3000])
+def test_binned_binary_seeded(n, T):
+    N = _native()
+    g = torch.Generator().manual_seed(n * 7 + T)
+    preds = torch.rand(n, generator=g)
+    target = (torch.rand(n, generator=g) < 0.3 + 0.4 * preds).long()
+    thr = torch.linspace(0, 1, T) if T > 1 else torch.tensor([0.5])
+    state = _binned(N, preds, target, thr)
+    want = O.binary_precision_recall_curve_update_hist(preds.numpy(), target.numpy(), thr.numpy())
+    assert np.array_equal(_np(state), want)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16, torch.bfloat16, torch.float64])
+@pytest.mark.parametrize("tdt", [torch.int64, torch.int32, torch.uint8, torch.bool])
+def test_binned_binary_dtypes(dt, tdt):
+    N = _native()
+    g = torch.Generator().manual_seed(11)
+    n = 50_001
+    preds = torch.rand(n, generator=g, dtype=torch.float64).to(dt)
+    target = (torch.rand(n, generator=g) < 0.5).to(tdt)
+    thr = torch.linspace(0, 1, 200)
+    state = _binned(N, preds, target, thr)
+    # type promotion: half/bfloat16 compare in float32, float64 in float64
+    pn = preds.double().numpy() if dt == torch.float64 else preds.float().numpy()
+    want = O.binary_precision_recall_curve_update_hist(pn, target.long().numpy(), thr.numpy())
+    assert np.array_equal(_np(state), want)
+
+
+def test_binned_special_values_and_sigmoid_rule():
+    N = _native()
+    thr = torch.linspace(0, 1, 200)
+    nan, inf = float("nan"), float("inf")
+    target = torch.tensor([1, 0, 1, 0, 1, 0, 1, 0])
+    # in range: -0.0, 0, 1, denormal
+    p = torch.tensor([-0.0, 0.0, 1.0, 1e-45, 0.5, thr[100].item(), thr[199].item(), thr[1].item()])
+    want = O.binary_precision_recall_curve_update_loop(p.numpy(), target.numpy(), thr.numpy())
+    assert np.array_equal(_np(_binned(N, p, target, thr)), want)
+    # one NaN / inf / value > 1 anywhere flips the WHOLE batch to sigmoid (precision_recall_curve.py:183-184)
+    for bad in [nan, inf, -inf, 1.0000001, -1e-30]:
+        p2 = p.clone()
+        p2[3] = bad
+        sp = _np(p2.to(DEV).sigmoid())
+        want = O.binary_precision_recall_curve_update_loop(sp, target.numpy(), thr.numpy())
+        assert np.array_equal(_np(_binned(N, p2, target, thr)), want), bad
+    # ... unless that sample is ignored (binary format drops ignored samples before the range check)
+    p2 = p.clone()
+    p2[3] = 7.0
+    t2 = target.clone()
+    t2[3] = -1
+    want = O.binary_precision_recall_curve_update_loop(np.delete(p2.numpy(), 3), np.delete(t2.numpy(), 3), thr.numpy())
+    assert np.array_equal(_np(_binned(N, p2, t2, thr, ignore_index=-1)), want)
+    # AS_IS never applies it; NaN compares false with every threshold
+    p3 = torch.tensor([nan, 2.0, -1.0, 0.5])
+    t3 = torch.tensor([1, 1, 0, 0])
+    want = O.binary_precision_recall_curve_update_loop(p3.numpy(), t3.numpy(), thr.numpy())
+    assert np.array_equal(_np(_binned(N, p3, t3, thr, prob_mode=N.PROB_AS_IS)), want)
+
+
+def test_binned_logits_large_matches_device_sigmoid():
+    N = _native()
+    g = torch.Generator().manual_seed(2)
+    n = 1 << 20
+    logits = torch.randn(n, generator=g) * 4
+    target = (torch.rand(n, generator=g) < 0.5).long()
+    thr = torch.linspace(0, 1, 200)
+    sp = _np(logits.to(DEV).sigmoid())
+    want = O.binary_precision_recall_curve_update_hist(sp, target.numpy(), thr.numpy())
+    assert np.array_equal(_np(_binned(N, logits, target, thr)), want)
+    # the workspace is left clean: a probability batch right after gives the plain result
+    probs = torch.rand(n, generator=g)
+    want = O.binary_precision_recall_curve_update_hist(probs.numpy(), target.numpy(), thr.numpy())
+    assert np.array_equal(_np(_binned(N, probs, target, thr)), want)
+
+
+def test_binned_unsorted_thresholds_flagged_and_arbitrary_sorted_ok():
+    N = _native()
+    dev = torch.device(DEV)
+    p = torch.rand(1000)
+    t = torch.randint(0, 2, (1000,))
+    _binned(N, p, t, torch.tensor([0.5, 0.1, 0.9]))
+    with pytest.raises(RuntimeError, match="sorted ascending"):
+        N.raise_on_status(dev)
+    thr = torch.tensor([-3.0, 0.1, 0.1, 0.10000001, 0.5, 0.5, 7.0])  # duplicates, outside [0,1]
+    want = O.binary_precision_recall_curve_update_loop(p.numpy(), t.numpy(), thr.numpy())
+    assert np.array_equal(_np(_binned(N, p, t, thr)), want)
+    assert N.read_status(dev) == 0
+
+
+def test_binned_accumulates_in_place():
+    N = _native()
+    g = torch.Generator().manual_seed(9)
+    thr = torch.linspace(0, 1, 200).to(DEV)
+    state = torch.zeros(200, 2, 2, dtype=torch.int64, device=DEV)
+    total = np.zeros((200, 2, 2), dtype=np.int64)
+    for n in [1000, 77, 123_456]:
+        p = torch.rand(n, generator=g)
+        t = torch.randint(0, 2, (n,), generator=g)
+        N.binned_curve_update_(state, p.to(DEV), t.to(DEV), thr)
+        total += O.binary_precision_recall_curve_update_hist(p.numpy(), t.numpy(), _np(thr))
+    assert np.array_equal(_np(state), total)
+
+
+@pytest.mark.parametrize("c", [c for c in load_golden("binned_curve") if c.meta["kind"].startswith("multilabel")],
+                         ids=case_id)
+def test_binned_multilabel_golden(c):
+    N = _native()
+    L = c.meta["num_labels"]
+    preds = torch.from_numpy(c["preds"])
+    target = torch.from_numpy(c["target"])
+    # host-side layout step of the reference's _format (precision_recall_curve.py:754-755)
+    p2 = preds.transpose(0, 1).reshape(L, -1).T.contiguous()
+    t2 = target.transpose(0, 1).reshape(L, -1).T.contiguous()
+    state = _binned(N, p2, t2, torch.from_numpy(c["thresholds"]), c.meta["ignore_index"], num_columns=L)
+    if c.meta["kind"].endswith("logits"):
+        sp = _np(p2.to(DEV).sigmoid())
+        ign = _np(t2) == c.meta["ignore_index"] if c.meta["ignore_index"] is not None else np.zeros(t2.shape, bool)
+        want = O.multilabel_precision_recall_curve_update(sp, _np(t2), ign, L, c["thresholds"])
+        assert np.array_equal(_np(state), want)
+        assert np.abs(_np(state) - c["confmat"]).max() <= 2
+    else:
+        assert np.array_equal(_np(state), c["confmat"])
+
+
+@pytest.mark.parametrize("c", [c for c in load_golden("binned_curve") if c.meta["kind"] == "multiclass_probs"],
+                         ids=case_id)
+def test_binned_multiclass_golden(c):
+    N = _native()
+    C = c.meta["num_classes"]
+    state = _binned(N, torch.from_numpy(c["preds"]), torch.from_numpy(c["target"]), torch.from_numpy(c["thresholds"]),
+                    c.meta["ignore_index"], prob_mode=N.PROB_CHECK, num_columns=C, class_index=True)
+    assert np.array_equal(_np(state), c["confmat_None"])
+    assert N.read_status(torch.device(DEV)) == 0
+
+
+def test_binned_multiclass_check_mode_reports_logits():
+    N = _native()
+    dev = torch.device(DEV)
+    p = torch.randn(100, 4)
+    t = torch.randint(0, 4, (100,))
+    state = _binned(N, p, t, torch.linspace(0, 1, 10), prob_mode=N.PROB_CHECK, num_columns=4, class_index=True)
+    assert int(state.abs().sum()) == 0  # discarded
+    assert N.read_status(dev) == N.STATUS_OUT_OF_UNIT_RANGE
+
+
+def test_binned_large_columns_global_bins():
+    N = _native()
+    g = torch.Generator().manual_seed(4)
+    L, T, n = 300, 200, 2000  # 300 * 2 * 201 bins do not fit shared memory -> global scratch path
+    p = torch.rand(n, L, generator=g)
+    t = torch.randint(0, 2, (n, L), generator=g)
+    thr = torch.linspace(0, 1, T)
+    state = _binned(N, p, t, thr, num_columns=L)
+    want = O.multilabel_precision_recall_curve_update(p.numpy(), t.numpy(), np.zeros((n, L), bool), L, thr.numpy())
+    assert np.array_equal(_np(state), want)
+
+
+# =========================================================================== K2 stat scores
+def _stat(N, preds, target, L, threshold=0.5, ignore_index=None, prob_mode=None):
+    out = torch.zeros(4, L, dtype=torch.int64, device=DEV)
+    N.stat_scores_update_(out, preds.to(DEV), target.to(DEV), L, threshold, ignore_index,
+                          N.PROB_AUTO if prob_mode is None else prob_mode)
+    return _np(out)
+
+
+@pytest.mark.parametrize("c", [c for c in load_golden("stat_scores")
+                               if c.meta["multidim_average"] == "global" and not c.meta["kind"].startswith("multiclass")],
+                         ids=case_id)
+def test_stat_scores_golden(c):
+    N = _native()
+    kind, ii = c.meta["kind"], c.meta["ignore_index"]
+    preds, target = torch.from_numpy(c["preds"]), torch.from_numpy(c["target"])
+    if kind.startswith("binary"):
+        got = _stat(N, preds.reshape(-1), target.reshape(-1), 1, c.meta["threshold"], ii)
+        tp, fp, tn, fn = got[:, 0]
+        want = c["stat_scores"]
+        ours = np.array([tp, fp, tn, fn, tp + fn])
+    else:
+        L = c.meta["num_labels"]
+        # (N, L, X) -> (N*X, L): host-side layout step
+        p2 = preds.reshape(preds.shape[0], L, -1).movedim(1, -1).reshape(-1, L).contiguous()
+        t2 = target.reshape(target.shape[0], L, -1).movedim(1, -1).reshape(-1, L).contiguous()
+        got = _stat(N, p2, t2, L, c.meta["threshold"], ii)
+        ours = np.stack([got[0], got[1], got[2], got[3], got[0] + got[3]], axis=-1)
+        want = c["stat_scores_none"]
+    if kind.endswith("logits"):
+        # rebuild the expectation with the device sigmoid (bit-exact target), then compare with the golden loosely
+        if kind.startswith("binary"):
+            sp = preds.to(DEV).sigmoid().cpu().numpy()
+            p, t = O.binary_stat_scores_format(sp, c["target"], c.meta["threshold"], ii)
+            tp, fp, tn, fn = O.binary_stat_scores_update(p, t)
+            exp = np.array([tp, fp, tn, fn, tp + fn])
+        else:
+            sp = preds.to(DEV).sigmoid().cpu().numpy()
+            p, t = O.multilabel_stat_scores_format(sp, c["target"], c.meta["num_labels"], c.meta["threshold"], ii)
+            tp, fp, tn, fn = O.multilabel_stat_scores_update(p, t)
+            exp = np.stack([tp, fp, tn, fn, tp + fn], axis=-1)
+        assert np.array_equal(ours, exp)
+        assert np.abs(ours - want).max() <= 1
+    else:
+        assert np.array_equal(ours, want)
+
+
+@pytest.mark.parametrize("L", [1, 2, 3, 4, 5, 7, 8, 100, 513, 2048, 2052])
+@pytest.mark.parametrize("n", [1, 3, 1000, 40_003])
+def test_stat_scores_seeded(L, n):
+    N = _native()
+    g = torch.Generator().manual_seed(L * 1000 + n)
+    p = torch.rand(n, L, generator=g)
+    t = torch.randint(-1, 2, (n, L), generator=g)
+    got = _stat(N, p, t, L, 0.37, ignore_index=-1)
+    fp_, ft_ = O.multilabel_stat_scores_format(p.numpy()[:, :, None], t.numpy()[:, :, None], L, 0.37, -1)
+    tp, fp, tn, fn = O.multilabel_stat_scores_update(fp_, ft_)
+    assert np.array_equal(got, np.stack([tp, fp, tn, fn]))
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16, torch.bfloat16, torch.float64, torch.int64, torch.int32,
+                                torch.uint8])
+def test_stat_scores_dtypes(dt):
+    N = _native()
+    g = torch.Generator().manual_seed(21)
+    n, L = 5000, 12
+    if dt.is_floating_point:
+        p = torch.rand(n, L, generator=g, dtype=torch.float64).to(dt)
+    else:
+        p = torch.randint(0, 2, (n, L), generator=g).to(dt)
+    t = torch.randint(0, 2, (n, L), generator=g)
+    got = _stat(N, p, t, L, 0.3)
+    if dt.is_floating_point:
+        pb = (p > 0.3).long()  # torch's own scalar-comparison semantics for this dtype
+    else:
+        pb = p.long()
+    tp, fp, tn, fn = O.multilabel_stat_scores_update(pb.numpy()[:, :, None], t.numpy()[:, :, None])
+    assert np.array_equal(got, np.stack([tp, fp, tn, fn]))
+
+
+def test_stat_scores_sigmoid_rule_counts_ignored_positions():
+    N = _native()
+    # stat-scores format range-checks the whole tensor, ignored positions included (stat_scores.py:104)
+    p = torch.tensor([[0.2, 0.9], [5.0, 0.4], [0.6, 0.1]])
+    t = torch.tensor([[1, 0], [-1, 1], [0, 1]])
+    got = _stat(N, p, t, 2, 0.5, ignore_index=-1)
+    sp = p.to(DEV).sigmoid().cpu().numpy()
+    fp_, ft_ = O.multilabel_stat_scores_format(sp[:, :, None], t.numpy()[:, :, None], 2, 0.5, -1)
+    tp, fp, tn, fn = O.multilabel_stat_scores_update(fp_, ft_)
+    assert np.array_equal(got, np.stack([tp, fp, tn, fn]))
+    # followed by a clean batch: flag and scratch were reset
+    p2 = torch.rand(1000, 2)
+    t2 = torch.randint(0, 2, (1000, 2))
+    got = _stat(N, p2, t2, 2)
+    tp, fp, tn, fn = O.multilabel_stat_scores_update((p2 > 0.5).long().numpy()[:, :, None], t2.numpy()[:, :, None])
+    assert np.array_equal(got, np.stack([tp, fp, tn, fn]))
+
+
+# =========================================================================== full-size properties
+def test_full_size_properties():
+    """BASELINE.json sizes (scaled to fit the test budget): totals and linearity instead of an oracle pass."""
+    N = _native()
+    n = 1 << 24
+    g = torch.Generator(device=DEV).manual_seed(1)
+    C = 1000
+    p = torch.randint(0, C, (n,), device=DEV, generator=g)
+    t = torch.randint(0, C, (n,), device=DEV, generator=g)
+    cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+    N.confmat_update_(cm, p, t, C)
+    assert int(cm.sum()) == n
+    assert torch.equal(cm.sum(1), torch.bincount(t, minlength=C))
+    assert torch.equal(cm.sum(0), torch.bincount(p, minlength=C))
+    assert torch.equal(cm.diag(), torch.bincount(t[p == t], minlength=C))
+    # linearity: two halves add up to the whole
+    cm2 = torch.zeros_like(cm)
+    N.confmat_update_(cm2, p[: n // 2], t[: n // 2], C)
+    N.confmat_update_(cm2, p[n // 2:], t[n // 2:], C)
+    assert torch.equal(cm, cm2)
+
+    n = 1 << 26
+    preds = torch.rand(n, device=DEV, generator=g)
+    target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
+    thr = torch.linspace(0, 1, 200, device=DEV)
+    st = torch.zeros(200, 2, 2, dtype=torch.int64, device=DEV)
+    N.binned_curve_update_(st, preds, target, thr)
+    assert torch.all(st.sum((1, 2)) == n)
+    npos = int(target.sum())
+    assert torch.all(st[:, 1, :].sum(1) == npos)
+    assert torch.all(st[1:, 1, 1] <= st[:-1, 1, 1]) and torch.all(st[1:, 0, 1] <= st[:-1, 0, 1])
+    for i in [0, 1, 57, 100, 199]:
+        above = preds >= thr[i]
+        assert int(st[i, 1, 1]) == int((above & (target == 1)).sum())
+        assert int(st[i, 0, 1]) == int((above & (target == 0)).sum())

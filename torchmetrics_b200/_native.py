@@ -1,0 +1,276 @@
+"""ctypes binding of libtm_b200.so (C ABI declared in include/tm_b200.h).
+
+This is the only door from the Python host layer to the CUDA kernels.  There is no CPU or eager-torch
+fallback behind it: if the shared library is missing, or a tensor that reaches a kernel seam is not a CUDA
+tensor, the call raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+from typing import Dict, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libtm_b200.so")
+
+TMB_OK = 0
+ERR_NAMES = {-1: "TMB_ERR_ARG", -2: "TMB_ERR_ALIGN", -3: "TMB_ERR_CUDA", -4: "TMB_ERR_TOO_LARGE"}
+
+STATUS_LABEL_RANGE = 1
+STATUS_THRESHOLD_ORDER = 2
+STATUS_OUT_OF_UNIT_RANGE = 4
+
+PROB_AS_IS, PROB_AUTO, PROB_SIGMOID, PROB_CHECK = 0, 1, 2, 3
+
+_DTYPES = {
+    torch.int64: 0,
+    torch.int32: 1,
+    torch.uint8: 4,
+    torch.bool: 4,
+    torch.float32: 8,
+    torch.float16: 9,
+    torch.bfloat16: 10,
+    torch.float64: 11,
+}
+
+_c = ctypes
+_SIGNATURES = {
+    "tmb_abi_version": (_c.c_int, []),
+    "tmb_last_cuda_error": (_c.c_char_p, []),
+    "tmb_sm_count": (_c.c_int, []),
+    "tmb_confmat_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_int,
+                                      _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_void_p]),
+    "tmb_match_count_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int,
+                                          _c.c_int64, _c.c_void_p, _c.c_void_p]),
+    "tmb_binned_curve_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int64]),
+    "tmb_binned_curve_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
+                                           _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int64, _c.c_int,
+                                           _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p, _c.c_void_p]),
+    "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
+    "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
+                                          _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p,
+                                          _c.c_size_t, _c.c_void_p]),
+}
+
+_lib = None
+_lock = threading.Lock()
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def declared_symbols():
+    return sorted(_SIGNATURES)
+
+
+def load():
+    """dlopen libtm_b200.so once; raises NativeLibraryError (never falls back) when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(_LIB_PATH):
+            raise NativeLibraryError(
+                f"{_LIB_PATH} not found. Build it with `python -c 'import __graft_entry__ as g; g.build()'` or "
+                "`make -C torchmetrics_b200/csrc`. torchmetrics_b200 has no CPU or eager fallback for its kernels."
+            )
+        lib = ctypes.CDLL(_LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the .so is stale
+            fn.restype = res
+            fn.argtypes = args
+        if lib.tmb_abi_version() != 1:
+            raise NativeLibraryError(f"ABI version mismatch: library reports {lib.tmb_abi_version()}, binding expects 1")
+        _lib = lib
+    return _lib
+
+
+def _check(rc: int, what: str) -> None:
+    if rc == TMB_OK:
+        return
+    msg = ERR_NAMES.get(rc, str(rc))
+    if rc == -3:
+        msg += ": " + load().tmb_last_cuda_error().decode()
+    raise RuntimeError(f"{what} failed with {msg}")
+
+
+def require_cuda(*tensors: Tensor) -> torch.device:
+    dev = None
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError(
+                "torchmetrics_b200 kernels run on CUDA tensors only (there is no CPU fallback); got a tensor on "
+                f"{t.device}. Move preds/target and the metric to a CUDA device."
+            )
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"Expected all tensors on the same device, got {dev} and {t.device}")
+    return dev
+
+
+def dtype_code(t: Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype} at a kernel seam") from None
+
+
+def as_kernel_labels(t: Tensor) -> Tensor:
+    """Contiguous, 32-byte aligned label tensor in one of the dtypes the kernels read (int64/int32/uint8/bool)."""
+    if t.dtype in (torch.int16, torch.int8):
+        t = t.to(torch.int32)
+    elif t.dtype not in (torch.int64, torch.int32, torch.uint8, torch.bool):
+        t = t.to(torch.int64)
+    return _aligned(t)
+
+
+def as_kernel_scores(t: Tensor) -> Tensor:
+    if t.dtype not in (torch.float32, torch.float16, torch.bfloat16, torch.float64):
+        t = t.to(torch.float32)
+    return _aligned(t)
+
+
+def _aligned(t: Tensor) -> Tensor:
+    t = t.contiguous()
+    if t.data_ptr() % 32 != 0:
+        t = t.clone(memory_format=torch.contiguous_format)
+    return t
+
+
+def _stream_ptr(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+# ---------------------------------------------------------------------------------------------
+# per (device, stream) scratch: a status word and self-cleaning kernel workspaces
+# ---------------------------------------------------------------------------------------------
+class _Scratch:
+    def __init__(self, dev: torch.device) -> None:
+        self.status = torch.zeros(8, dtype=torch.int32, device=dev)
+        self.ws: Dict[str, Tensor] = {}
+
+    def workspace(self, kind: str, nbytes: int, dev: torch.device) -> Tensor:
+        w = self.ws.get(kind)
+        if w is None or w.numel() < nbytes:
+            # zero on first use; kernels leave it zero behind them
+            w = torch.zeros(max(nbytes, 4096), dtype=torch.uint8, device=dev)
+            self.ws[kind] = w
+        return w
+
+
+_scratch: Dict[Tuple[int, int], _Scratch] = {}
+
+
+def scratch(dev: torch.device) -> _Scratch:
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), _stream_ptr(dev))
+    s = _scratch.get(key)
+    if s is None:
+        s = _Scratch(dev)
+        _scratch[key] = s
+    return s
+
+
+def read_status(dev: torch.device) -> int:
+    """Synchronising read-and-clear of the device status word for the current stream."""
+    s = scratch(dev)
+    v = int(s.status[0].item())
+    if v:
+        s.status.zero_()
+    return v
+
+
+def raise_on_status(dev: torch.device, num_classes: Optional[int] = None) -> None:
+    v = read_status(dev)
+    if v & STATUS_LABEL_RANGE:
+        raise RuntimeError(
+            "Detected label values outside the expected range in `preds`/`target`"
+            + (f" (expected values in [0, {num_classes - 1}])" if num_classes else "")
+            + "; the reference raises on the same input when it reshapes its bincount."
+        )
+    if v & STATUS_THRESHOLD_ORDER:
+        raise RuntimeError("thresholds handed to the binned-curve kernel must be sorted ascending")
+
+
+# ---------------------------------------------------------------------------------------------
+# thin typed wrappers (tensor in, state tensor updated in place)
+# ---------------------------------------------------------------------------------------------
+def confmat_update_(confmat: Tensor, preds: Tensor, target: Tensor, num_classes: int,
+                    ignore_index: Optional[int] = None, algo: int = 0) -> None:
+    """confmat (C, C) int64 += confusion matrix of the label tensors (K1)."""
+    dev = require_cuda(confmat, preds, target)
+    assert confmat.dtype == torch.int64 and confmat.is_contiguous() and confmat.numel() == num_classes * num_classes
+    preds, target = as_kernel_labels(preds.reshape(-1)), as_kernel_labels(target.reshape(-1))
+    assert preds.numel() == target.numel()
+    with torch.cuda.device(dev):
+        rc = load().tmb_confmat_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                       preds.numel(), num_classes, ignore_index is not None,
+                                       0 if ignore_index is None else int(ignore_index), confmat.data_ptr(),
+                                       scratch(dev).status.data_ptr(), algo, _stream_ptr(dev))
+    _check(rc, "tmb_confmat_update")
+
+
+def match_count_update_(out2: Tensor, preds: Tensor, target: Tensor, ignore_index: Optional[int] = None) -> None:
+    dev = require_cuda(out2, preds, target)
+    assert out2.dtype == torch.int64 and out2.numel() == 2 and out2.is_contiguous()
+    preds, target = as_kernel_labels(preds.reshape(-1)), as_kernel_labels(target.reshape(-1))
+    with torch.cuda.device(dev):
+        rc = load().tmb_match_count_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                           preds.numel(), ignore_index is not None,
+                                           0 if ignore_index is None else int(ignore_index), out2.data_ptr(),
+                                           _stream_ptr(dev))
+    _check(rc, "tmb_match_count_update")
+
+
+def binned_curve_update_(confmat: Tensor, preds: Tensor, target: Tensor, thresholds: Tensor, num_columns: int = 1,
+                         target_is_class_index: bool = False, ignore_index: Optional[int] = None,
+                         prob_mode: int = PROB_AUTO) -> None:
+    """confmat (T[, C], 2, 2) int64 += multi-threshold confusion matrix (K3). thresholds must be ascending."""
+    dev = require_cuda(confmat, preds, target, thresholds)
+    T = thresholds.numel()
+    assert confmat.dtype == torch.int64 and confmat.is_contiguous() and confmat.numel() == T * num_columns * 4
+    assert thresholds.dtype == torch.float32 and thresholds.is_contiguous()
+    preds = as_kernel_scores(preds.reshape(-1))
+    target = as_kernel_labels(target.reshape(-1))
+    n_rows = preds.numel() // num_columns
+    lib = load()
+    nbytes = lib.tmb_binned_curve_workspace_bytes(T, num_columns)
+    sc = scratch(dev)
+    ws = sc.workspace("binned", nbytes, dev)
+    with torch.cuda.device(dev):
+        rc = lib.tmb_binned_curve_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                         n_rows, num_columns, bool(target_is_class_index), thresholds.data_ptr(), T,
+                                         ignore_index is not None, 0 if ignore_index is None else int(ignore_index),
+                                         prob_mode, confmat.data_ptr(), ws.data_ptr(), ws.numel(),
+                                         sc.status.data_ptr(), _stream_ptr(dev))
+    _check(rc, "tmb_binned_curve_update")
+
+
+def stat_scores_update_(out: Tensor, preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
+                        ignore_index: Optional[int] = None, prob_mode: int = PROB_AUTO) -> None:
+    """out (4, L) int64 [tp|fp|tn|fn] += per-label statistics of (n_rows, L) preds/target (K2)."""
+    dev = require_cuda(out, preds, target)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == 4 * num_labels
+    preds = as_kernel_scores(preds.reshape(-1)) if preds.is_floating_point() else as_kernel_labels(preds.reshape(-1))
+    target = as_kernel_labels(target.reshape(-1))
+    n_rows = preds.numel() // num_labels
+    lib = load()
+    nbytes = lib.tmb_stat_scores_workspace_bytes(num_labels)
+    sc = scratch(dev)
+    ws = sc.workspace("stat", nbytes, dev)
+    with torch.cuda.device(dev):
+        rc = lib.tmb_stat_scores_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                        n_rows, num_labels, float(threshold), prob_mode, ignore_index is not None,
+                                        0 if ignore_index is None else int(ignore_index), out.data_ptr(),
+                                        ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _check(rc, "tmb_stat_scores_update")

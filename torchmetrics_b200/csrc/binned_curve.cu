@@ -1,0 +1,526 @@
+// K3 — binned (multi-threshold) curve state update (contract in include/tm_b200.h).
+//
+// The reference makes 3*T reduction passes over the scores (precision_recall_curve.py:228-250).  Here the
+// batch is read ONCE: each score is mapped to bin = #{i : thr[i] <= p} (exactly, against the caller's own
+// float32 threshold values), a histogram over (T+1) x {neg,pos} bins is accumulated on chip, and a suffix
+// sum over bins in the last CTA turns it into the (T,2,2) state, which is added in place.
+//
+// Two accumulation strategies:
+//   * private  (one column, small T — the BinaryAUROC/AP(thresholds=200) case): every THREAD owns a
+//     private histogram of 8-bit counters in shared memory, word-interleaved so that lane l always hits
+//     bank l (address = word*NT + tid).  An increment is LDS + IADD + STS without any atomic and without
+//     bank conflicts; counters are folded into per-CTA 64-bit totals every <=252 samples per thread.
+//     Shared-memory atomics top out near 0.5 samples/clk/SM, this path needs ~2.5 to keep up with HBM.
+//   * atomic   (any number of columns / large T): u32 bins in shared memory (or u64 in global scratch when
+//     they do not fit) updated with atomics.
+//
+// The all-or-nothing sigmoid of the reference's `_format` step (":183-184: if not torch.all((preds >= 0) *
+// (preds <= 1)): preds = preds.sigmoid()") is resolved on the device without a host round trip: pass 1
+// bins the raw scores and raises a flag on the first score outside [0,1]; pass 2 is always enqueued but
+// exits at once unless the flag is up, in which case it redoes the batch with sigmoid(p) and pass 1's
+// partial histogram is discarded.
+#include "common.cuh"
+
+namespace tmb {
+
+struct BinnedWs {
+  int flag_oor;  // pass 1 saw a score outside [0,1]
+  int ticket;    // CTAs finished (last one finalises)
+  int pad[6];
+  // followed by u64 hist[num_columns * 2 * (T+1)], layout [column][pos][bin]
+};
+static_assert(sizeof(BinnedWs) == 32, "workspace header");
+
+constexpr int kLutCells = 1024;
+
+struct BinnedParams {
+  const void* preds;
+  const void* target;
+  long long n_rows;
+  long long num_columns;
+  int target_is_class_index;
+  const float* thr;
+  int T;
+  int has_ignore;
+  long long ignore;
+  int check_range;    // raise ws->flag_oor on scores outside [0,1] and stop early
+  int only_if_flag;   // run only when ws->flag_oor is already up (auto pass 2)
+  int oor_counts_ignored;  // range check also looks at ignored entries (multilabel _format order)
+  u64* confmat;       // (T, C, 2, 2) int64
+  BinnedWs* ws;
+  int* status;
+  int status_bit_on_oor;  // TMB_PROB_CHECK semantics: report instead of redoing
+};
+
+// ---- exact binning ------------------------------------------------------------------------------
+// cell() is a monotone map of a score onto kLutCells uniform cells spanning [thr[0], thr[T-1]].  lut[c] is
+// the number of thresholds whose cell is < c: all of those are <= any score that falls in cell c, the ones
+// in the same cell are compared one by one, the ones in later cells are larger.  Monotonicity of cell() is
+// all that exactness needs, so float rounding inside it is harmless.
+struct BinMap {
+  float lo, scale;
+};
+
+__device__ __forceinline__ int cell_of(float p, const BinMap& m) {
+  if (!(p >= m.lo)) return 0;  // also NaN
+  float x = (p - m.lo) * m.scale;
+  int c = (int)x;  // cvt.rzi saturates, NaN -> 0
+  return c < kLutCells - 1 ? c : kLutCells - 1;
+}
+__device__ __forceinline__ int cell_of(double p, const BinMap& m) { return cell_of((float)p, m); }
+
+template <typename CT>
+__device__ __forceinline__ int bin_of(CT p, const BinMap& m, const float* __restrict__ s_thr,
+                                      const unsigned short* __restrict__ s_lut) {
+  int b = s_lut[cell_of(p, m)];
+  // s_thr[T] is NaN, so the walk stops there
+  while (p >= (CT)s_thr[b]) ++b;
+  return b;
+}
+
+// builds s_thr (T+1 floats, NaN sentinel) and s_lut for the calling CTA; returns false if unsorted
+__device__ __forceinline__ bool build_binning(const float* __restrict__ thr, int T, float* s_thr,
+                                              unsigned short* s_lut, BinMap& m) {
+  int unsorted = 0;
+  for (int i = threadIdx.x; i <= T; i += blockDim.x) {
+    float v = i < T ? thr[i] : __int_as_float(0x7fc00000);
+    s_thr[i] = v;
+    if (i > 0 && i < T && !(thr[i - 1] <= v)) unsorted = 1;
+  }
+  unsorted = __syncthreads_or(unsorted);
+  float lo = s_thr[0], hi = s_thr[T - 1];
+  float range = hi - lo;
+  m.lo = lo;
+  m.scale = (range > 0.f && range < 3.0e38f) ? (float)kLutCells / range : 0.f;
+  if (!(m.scale < 3.0e38f)) m.scale = 0.f;
+  for (int c = threadIdx.x; c < kLutCells; c += blockDim.x) {
+    // lower_bound over the non-decreasing sequence cell_of(thr[i]) for value c
+    int l = 0, r = T;
+    while (l < r) {
+      int mid = (l + r) >> 1;
+      if (cell_of(s_thr[mid], m) < c) l = mid + 1; else r = mid;
+    }
+    s_lut[c] = (unsigned short)l;
+  }
+  __syncthreads();
+  return !unsorted;
+}
+
+template <typename CT>
+__device__ __forceinline__ bool out_of_unit(CT p) { return !(p >= (CT)0 && p <= (CT)1); }
+
+// last CTA: hist -> suffix sums -> confmat += ; leaves the workspace zeroed.  s_scan: 2*(T+1) u64 of smem.
+__device__ void finalize_columns(const BinnedParams& P, u64* hist, u64* s_scan, bool discard) {
+  const int NB = P.T + 1;
+  for (long long c = 0; c < P.num_columns; ++c) {
+    u64* h = hist + c * 2 * NB;
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * NB; i += blockDim.x) {
+      s_scan[i] = __ldcg(h + i);
+      h[i] = 0;
+    }
+    __syncthreads();
+    if (!discard) {
+      // one lane per class: serial suffix sum (NB is at most a few thousand)
+      if (threadIdx.x == 0 || threadIdx.x == 32) {
+        u64* s = s_scan + (threadIdx.x ? NB : 0);
+        u64 run = 0;
+        for (int b = NB - 1; b >= 0; --b) {
+          run += s[b];
+          s[b] = run;
+        }
+      }
+      __syncthreads();
+      const u64 totneg = s_scan[0], totpos = s_scan[NB];
+      for (int i = threadIdx.x; i < P.T; i += blockDim.x) {
+        u64 fp = s_scan[i + 1], tp = s_scan[NB + i + 1];
+        u64* o = P.confmat + ((long long)i * P.num_columns + c) * 4;
+        o[0] += totneg - fp;  // [0][0] tn
+        o[1] += fp;           // [0][1]
+        o[2] += totpos - tp;  // [1][0] fn
+        o[3] += tp;           // [1][1]
+      }
+    }
+  }
+}
+
+// =================================================================================================
+// private-histogram kernel (num_columns == 1)
+// =================================================================================================
+constexpr int kFlushEvery = 63;  // tiles of 4 samples per thread between folds: 252 <= 255
+
+template <typename PT, typename TT, bool SIGMOID>
+__global__ void __launch_bounds__(1024, 1) binned_private_kernel(const BinnedParams P) {
+  using CT = typename CmpType<PT>::type;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BinnedWs* ws = P.ws;
+  if (P.only_if_flag && ws->flag_oor == 0) return;
+
+  const int NT = blockDim.x, tid = threadIdx.x;
+  const int T = P.T, NB = T + 1, NB2 = 2 * NB;
+  const int W = (NB2 + 3) >> 2;  // 32-bit words of 4 byte-counters per thread
+  u32* s_hist = reinterpret_cast<u32*>(smem_raw);
+  u64* s_acc = reinterpret_cast<u64*>(smem_raw + (size_t)W * NT * 4);
+  float* s_thr = reinterpret_cast<float*>(s_acc + NB2);
+  unsigned short* s_lut = reinterpret_cast<unsigned short*>(s_thr + NB);
+  __shared__ int s_last;
+
+  for (int i = tid; i < W * NT; i += NT) s_hist[i] = 0;
+  for (int i = tid; i < NB2; i += NT) s_acc[i] = 0;
+  BinMap m;
+  const bool sorted = build_binning(P.thr, T, s_thr, s_lut, m);
+  if (!sorted) {
+    if (blockIdx.x == 0 && tid == 0) atomicOr(P.status, TMB_STATUS_THRESHOLD_ORDER);
+    return;  // uniform over the grid; workspace untouched
+  }
+
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  const long long n = P.n_rows;
+  const long long tile_elems = (long long)NT * 4;
+  const long long ntiles = (n + tile_elems - 1) / tile_elems;
+  u32* my = s_hist + tid;
+  int oor = 0;
+
+  // bin index of one sample (or -1 when it is ignored); reads only the threshold tables, so the four lookups
+  // of a vector are independent of the counter updates that follow and can overlap
+  auto index_of = [&](PT pv, TT tv) -> int {
+    long long tl = as_i64(tv);
+    const bool ign = P.has_ignore && tl == P.ignore;
+    CT p = to_cmp(pv);
+    if (P.check_range && (!ign || P.oor_counts_ignored)) oor |= out_of_unit(p);
+    if (ign) return -1;
+    if constexpr (SIGMOID) p = round_to_storage<PT>(sigmoid_ref(p));
+    return bin_of(p, m, s_thr, s_lut) + (tl == 1 ? NB : 0);
+  };
+  auto bump = [&](int idx) {
+    if (idx < 0) return;
+    u32* w = my + (idx >> 2) * NT;
+    *w += 1u << ((idx & 3) << 3);
+  };
+
+  // fold every thread's byte counters into the CTA's 64-bit totals and clear them
+  auto fold = [&]() {
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31, nwarps = NT >> 5;
+    for (int r = warp; r < W; r += nwarps) {
+      u32* row = s_hist + r * NT;
+      u32 lo = 0, hi = 0;  // 2 x 16-bit fields each: bytes 0,2 and bytes 1,3
+      for (int j = lane; j < NT; j += 32) {
+        u32 v = row[j];
+        row[j] = 0;
+        lo += v & 0x00ff00ffu;
+        hi += (v >> 8) & 0x00ff00ffu;
+      }
+      u32 c0 = __reduce_add_sync(0xffffffffu, lo & 0xffffu);
+      u32 c2 = __reduce_add_sync(0xffffffffu, lo >> 16);
+      u32 c1 = __reduce_add_sync(0xffffffffu, hi & 0xffffu);
+      u32 c3 = __reduce_add_sync(0xffffffffu, hi >> 16);
+      if (lane < 4) {
+        int b = 4 * r + lane;
+        u32 c = lane == 0 ? c0 : lane == 1 ? c1 : lane == 2 ? c2 : c3;
+        if (b < NB2) s_acc[b] += c;
+      }
+    }
+    __syncthreads();
+  };
+
+  int since_fold = 0;
+  bool stop = false;
+  long long tile = blockIdx.x;
+  // software prefetch: the next tile's vectors are in flight while this one is binned
+  Vec4<PT> pn;
+  Vec4<TT> tn;
+  auto fetch = [&](long long tl_) {
+    long long base = tl_ * tile_elems + (long long)tid * 4;
+    if (tl_ < ntiles && base + 4 <= n) {
+      pn = load4(preds + base);
+      tn = load4(target + base);
+    }
+  };
+  fetch(tile);
+  while (tile < ntiles && !stop) {
+    Vec4<PT> pc = pn;
+    Vec4<TT> tc = tn;
+    const long long base = tile * tile_elems + (long long)tid * 4;
+    fetch(tile + gridDim.x);
+    if (base + 4 <= n) {
+      int idx[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) idx[j] = index_of(pc.v[j], tc.v[j]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bump(idx[j]);
+    } else {
+      for (long long i = base; i < n && i < base + 4; ++i) bump(index_of(preds[i], target[i]));
+    }
+    tile += gridDim.x;
+    if (++since_fold == kFlushEvery) {
+      since_fold = 0;
+      if (P.check_range) {
+        if (oor) atomicOr(&ws->flag_oor, 1);
+        // a raised flag makes the rest of this pass useless: every CTA bails out at its next fold
+        stop = __syncthreads_or(oor | *(volatile int*)&ws->flag_oor) != 0;
+      }
+      fold();
+    }
+  }
+  if (P.check_range && oor) atomicOr(&ws->flag_oor, 1);
+  fold();
+
+  u64* hist = reinterpret_cast<u64*>(ws + 1);
+  for (int i = tid; i < NB2; i += NT) {
+    u64 c = s_acc[i];
+    if (c) atomicAdd(hist + i, c);
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(&ws->ticket, 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int flag = *(volatile int*)&ws->flag_oor;
+  const bool discard = P.check_range && flag != 0;
+  finalize_columns(P, hist, s_acc, discard);
+  if (tid == 0) {
+    ws->ticket = 0;
+    if (P.check_range) {
+      if (discard && P.status_bit_on_oor) {
+        atomicOr(P.status, P.status_bit_on_oor);
+        ws->flag_oor = 0;
+      }
+      // otherwise the flag stays up for pass 2, which lowers it
+    } else if (P.only_if_flag) {
+      ws->flag_oor = 0;
+    }
+  }
+}
+
+// =================================================================================================
+// atomic kernel (any number of columns, any T)
+// =================================================================================================
+constexpr int kAtomicThreads = 512;
+
+template <typename PT, typename TT, bool SIGMOID, bool SMEM_BINS>
+__global__ void __launch_bounds__(kAtomicThreads) binned_atomic_kernel(const BinnedParams P) {
+  using CT = typename CmpType<PT>::type;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BinnedWs* ws = P.ws;
+  if (P.only_if_flag && ws->flag_oor == 0) return;
+
+  const int NT = blockDim.x, tid = threadIdx.x;
+  const int T = P.T, NB = T + 1;
+  const long long C = P.num_columns;
+  const long long nbins = C * 2 * NB;
+  float* s_thr = reinterpret_cast<float*>(smem_raw);
+  unsigned short* s_lut = reinterpret_cast<unsigned short*>(s_thr + NB);
+  // scan buffer for finalize (2*NB u64), 8-byte aligned after the LUT
+  size_t off = ((size_t)NB * 4 + kLutCells * 2 + 7) & ~(size_t)7;
+  u64* s_scan = reinterpret_cast<u64*>(smem_raw + off);
+  u32* s_bins = reinterpret_cast<u32*>(s_scan + 2 * NB);
+  __shared__ int s_last;
+
+  if constexpr (SMEM_BINS)
+    for (long long i = tid; i < nbins; i += NT) s_bins[i] = 0;
+  BinMap m;
+  const bool sorted = build_binning(P.thr, T, s_thr, s_lut, m);
+  if (!sorted) {
+    if (blockIdx.x == 0 && tid == 0) atomicOr(P.status, TMB_STATUS_THRESHOLD_ORDER);
+    return;
+  }
+  u64* hist = reinterpret_cast<u64*>(ws + 1);
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  const long long total = P.n_rows * C;
+  const long long nvec = total >> 2;
+  const long long stride = (long long)gridDim.x * NT;
+  int oor = 0;
+
+  auto count = [&](PT pv, long long tl, long long col) {
+    // tl: multilabel -> the element's own target; class-index mode -> the row's class id
+    const bool ign = P.has_ignore && tl == P.ignore;
+    CT p = to_cmp(pv);
+    if (P.check_range && (!ign || P.oor_counts_ignored)) oor |= out_of_unit(p);
+    if (ign) return;
+    if constexpr (SIGMOID) p = round_to_storage<PT>(sigmoid_ref(p));
+    const bool pos = P.target_is_class_index ? (tl == col) : (tl == 1);
+    long long idx = (col * 2 + (pos ? 1 : 0)) * NB + bin_of(p, m, s_thr, s_lut);
+    if constexpr (SMEM_BINS) atomicAdd(s_bins + idx, 1u); else atomicAdd(hist + idx, 1ULL);
+  };
+
+  long long it = 0;
+  for (long long g = (long long)blockIdx.x * NT + tid; g < nvec; g += stride, ++it) {
+    const long long e = g << 2;
+    Vec4<PT> p = load4(preds + e);
+    long long row = e / C, col = e - row * C;
+    if (P.target_is_class_index) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        count(p.v[j], as_i64(target[row]), col);
+        if (++col == C) { col = 0; ++row; }
+      }
+    } else {
+      Vec4<TT> t = load4(target + e);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        count(p.v[j], as_i64(t.v[j]), col);
+        if (++col == C) col = 0;
+      }
+    }
+    if (P.check_range && (it & 63) == 63) {
+      if (oor) atomicOr(&ws->flag_oor, 1);
+      if (*(volatile int*)&ws->flag_oor) break;
+    }
+  }
+  if (blockIdx.x == 0 && tid < (total & 3)) {
+    long long e = (nvec << 2) + tid;
+    long long row = e / C, col = e - row * C;
+    count(preds[e], as_i64(P.target_is_class_index ? target[row] : target[e]), col);
+  }
+  if (P.check_range && oor) atomicOr(&ws->flag_oor, 1);
+  __syncthreads();
+  if constexpr (SMEM_BINS) {
+    for (long long i = tid; i < nbins; i += NT) {
+      u32 c = s_bins[i];
+      if (c) atomicAdd(hist + i, (u64)c);
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(&ws->ticket, 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int flag = *(volatile int*)&ws->flag_oor;
+  const bool discard = P.check_range && flag != 0;
+  finalize_columns(P, hist, s_scan, discard);
+  if (tid == 0) {
+    ws->ticket = 0;
+    if (P.check_range) {
+      if (discard && P.status_bit_on_oor) {
+        atomicOr(P.status, P.status_bit_on_oor);
+        ws->flag_oor = 0;
+      }
+    } else if (P.only_if_flag) {
+      ws->flag_oor = 0;
+    }
+  }
+}
+
+// ---- host -----------------------------------------------------------------------------------------
+static size_t private_smem_bytes(int T, int NT) {
+  const int NB = T + 1, NB2 = 2 * NB, W = (NB2 + 3) >> 2;
+  return (size_t)W * NT * 4 + (size_t)NB2 * 8 + (size_t)NB * 4 + kLutCells * 2 + 16;
+}
+
+// largest CTA (multiple of 32 threads) whose private histograms fit; 0 if fewer than 128 threads would
+static int private_threads(int T) {
+  const size_t budget = (size_t)max_optin_smem() - 64;  // static __shared__ s_last rides along
+  for (int nt = 1024; nt >= 128; nt -= 32)
+    if (private_smem_bytes(T, nt) <= budget) return nt;
+  return 0;
+}
+
+template <typename PT, typename TT>
+static int launch_binned(BinnedParams P, int prob_mode, cudaStream_t st) {
+  const long long total = P.n_rows * P.num_columns;
+  const int NB = P.T + 1;
+  const long long nbins = P.num_columns * 2 * NB;
+  const int nt_private = (P.num_columns == 1 && !P.target_is_class_index) ? private_threads(P.T) : 0;
+
+  auto run = [&](bool sigmoid) -> int {
+    if (nt_private) {
+      const size_t smem = private_smem_bytes(P.T, nt_private);
+      const long long tile = (long long)nt_private * 4;
+      long long ntiles = (total + tile - 1) / tile;
+      int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
+      auto k = sigmoid ? binned_private_kernel<PT, TT, true> : binned_private_kernel<PT, TT, false>;
+      TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, nt_private, smem, st>>>(P);
+    } else {
+      const size_t fixed = (((size_t)NB * 4 + kLutCells * 2 + 7) & ~(size_t)7) + (size_t)2 * NB * 8;
+      const size_t with_bins = fixed + (size_t)nbins * 4;
+      const bool smem_bins = with_bins <= (size_t)max_optin_smem() - 256;
+      const size_t smem = smem_bins ? with_bins : fixed;
+      if (fixed > (size_t)max_optin_smem() - 256) return TMB_ERR_TOO_LARGE;
+      long long nvec = total >> 2;
+      long long want = (nvec + kAtomicThreads - 1) / kAtomicThreads;
+      int per_sm = smem > 100 * 1024 ? 1 : smem > 48 * 1024 ? 2 : 4;
+      long long cap = (long long)sm_count() * per_sm;
+      int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
+      void (*k)(const BinnedParams);
+      if (smem_bins) k = sigmoid ? binned_atomic_kernel<PT, TT, true, true> : binned_atomic_kernel<PT, TT, false, true>;
+      else k = sigmoid ? binned_atomic_kernel<PT, TT, true, false> : binned_atomic_kernel<PT, TT, false, false>;
+      TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, kAtomicThreads, smem, st>>>(P);
+    }
+    TMB_CUDA_CHECK(cudaGetLastError());
+    return TMB_OK;
+  };
+
+  int rc;
+  switch (prob_mode) {
+    case TMB_PROB_AS_IS:
+      P.check_range = 0; P.only_if_flag = 0; P.status_bit_on_oor = 0;
+      return run(false);
+    case TMB_PROB_SIGMOID:
+      P.check_range = 0; P.only_if_flag = 0; P.status_bit_on_oor = 0;
+      return run(true);
+    case TMB_PROB_AUTO:
+      P.check_range = 1; P.only_if_flag = 0; P.status_bit_on_oor = 0;
+      rc = run(false);
+      if (rc != TMB_OK) return rc;
+      P.check_range = 0; P.only_if_flag = 1;
+      return run(true);
+    case TMB_PROB_CHECK:
+      P.check_range = 1; P.only_if_flag = 0; P.status_bit_on_oor = TMB_STATUS_OUT_OF_UNIT_RANGE;
+      return run(false);
+    default:
+      return TMB_ERR_ARG;
+  }
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" size_t tmb_binned_curve_workspace_bytes(int num_thresholds, int64_t num_columns) {
+  if (num_thresholds < 1 || num_columns < 1) return 0;
+  return sizeof(BinnedWs) + (size_t)num_columns * 2 * ((size_t)num_thresholds + 1) * sizeof(u64);
+}
+
+extern "C" int tmb_binned_curve_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                       int64_t n_rows, int64_t num_columns, int target_is_class_index,
+                                       const float* thresholds, int num_thresholds, int has_ignore,
+                                       int64_t ignore_index, int prob_mode, int64_t* confmat, void* workspace,
+                                       size_t workspace_bytes, int32_t* status, void* stream) {
+  if (n_rows < 0 || num_columns < 1 || num_thresholds < 1 || num_thresholds > 65000 || !thresholds || !confmat ||
+      !workspace || !status)
+    return TMB_ERR_ARG;
+  if (workspace_bytes < tmb_binned_curve_workspace_bytes(num_thresholds, num_columns)) return TMB_ERR_ARG;
+  if (n_rows == 0) return TMB_OK;
+  if (!preds || !target) return TMB_ERR_ARG;
+  if (!aligned32(preds) || !aligned32(target) || !aligned32(workspace)) return TMB_ERR_ALIGN;
+  // multiclass scores are normalised by a row softmax, not a sigmoid: only AS_IS / CHECK make sense there
+  if (target_is_class_index && (prob_mode == TMB_PROB_AUTO || prob_mode == TMB_PROB_SIGMOID)) return TMB_ERR_ARG;
+  BinnedParams P{};
+  P.preds = preds;
+  P.target = target;
+  P.n_rows = n_rows;
+  P.num_columns = num_columns;
+  P.target_is_class_index = target_is_class_index ? 1 : 0;
+  P.thr = thresholds;
+  P.T = num_thresholds;
+  P.has_ignore = has_ignore ? 1 : 0;
+  P.ignore = ignore_index;
+  // the multilabel _format step range-checks before masking ignored entries (precision_recall_curve.py:756-766),
+  // the binary and multiclass ones after dropping them (:176-184, :441-448)
+  P.oor_counts_ignored = (num_columns > 1 && !target_is_class_index) ? 1 : 0;
+  P.confmat = (u64*)confmat;
+  P.ws = (BinnedWs*)workspace;
+  P.status = status;
+  cudaStream_t st = (cudaStream_t)stream;
+  TMB_DISPATCH_FLOAT(preds_dtype, PT, {
+    TMB_DISPATCH_INT(target_dtype, TT, { return launch_binned<PT, TT>(P, prob_mode, st); })
+  })
+  return TMB_ERR_ARG;
+}

@@ -1,0 +1,281 @@
+// K1 — confusion-matrix update from label tensors (see include/tm_b200.h for the contract).
+//
+// HBM-bound streaming histogram: every (pred, target) pair is read once with 128/256-bit loads and turned
+// into one integer increment of confmat[target*C + pred].
+//   * large C (C*C bins do not fit shared memory; C = 1000 -> 10^6 bins = 8 MB, L2-resident on B200):
+//     one 64-bit RED (fire-and-forget atomic) per sample straight into the int64 state. No key tensor,
+//     no scratch, no second pass.
+//   * small C: bins privatised in shared memory as u32 (one copy per CTA), warp-level match-any
+//     aggregation when C is tiny (heavy same-address contention), one global RED per non-zero bin per CTA.
+#include "common.cuh"
+
+namespace tmb {
+
+constexpr int kConfmatThreads = 256;
+
+template <typename PT, typename TT>
+__device__ __forceinline__ bool make_key(PT p, TT t, long long C, long long CC, bool has_ignore, long long ignore,
+                                         long long& key, int& bad) {
+  long long tl = as_i64(t);
+  if (has_ignore && tl == ignore) return false;
+  key = tl * C + as_i64(p);
+  if (key < 0 || key >= CC) {
+    bad = 1;
+    return false;
+  }
+  return true;
+}
+
+// ---- large C: global RED ---------------------------------------------------------------------
+// one RED per sample; AGG: lanes of a warp holding the same key are merged first (match.any), which pays when
+// the data are concentrated on few cells (diagonal-heavy confusion matrices) and costs ~10% when they are not
+template <bool AGG>
+__device__ __forceinline__ void global_count(u64* confmat, long long key, bool valid) {
+  if constexpr (AGG) {
+    unsigned active = __ballot_sync(0xffffffffu, valid);
+    if (valid) {
+      unsigned peers = __match_any_sync(active, (unsigned long long)key);
+      if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(confmat + key, (u64)__popc(peers));
+    }
+  } else {
+    if (valid) atomicAdd(confmat + key, 1ULL);
+  }
+}
+
+template <typename PT, typename TT, int UNROLL, int MINB, bool AGG>
+__global__ void __launch_bounds__(kConfmatThreads, MINB)
+confmat_global_kernel(const PT* __restrict__ preds, const TT* __restrict__ target, long long n, long long C,
+                      int has_ignore, long long ignore, u64* __restrict__ confmat, int* __restrict__ status) {
+  const long long CC = C * C;
+  const long long nvec = n >> 2;  // groups of 4 samples
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int bad = 0;
+  // every lane of a warp runs the same number of iterations (match.any needs converged warps)
+  const long long per = (long long)UNROLL * stride;
+  const long long iters = (nvec + per - 1) / per;
+  for (long long it = 0; it < iters; ++it, g += per) {
+    Vec4<PT> p[UNROLL];
+    Vec4<TT> t[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      if (g + u * stride < nvec) {
+        p[u] = load4(preds + 4 * (g + u * stride));
+        t[u] = load4(target + 4 * (g + u * stride));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const bool in = g + u * stride < nvec;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        long long key = 0;
+        const bool valid = in && make_key(p[u].v[j], t[u].v[j], C, CC, has_ignore, ignore, key, bad);
+        global_count<AGG>(confmat, key, valid);
+      }
+    }
+  }
+  // ragged tail (< 4 samples)
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    long long i = (nvec << 2) + threadIdx.x;
+    long long key;
+    if (make_key(preds[i], target[i], C, CC, has_ignore, ignore, key, bad)) atomicAdd(confmat + key, 1ULL);
+  }
+  if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
+}
+
+// ---- small C: shared-memory privatised ----------------------------------------------------------
+template <bool AGG>
+__device__ __forceinline__ void smem_count(u32* hist, long long key, bool valid) {
+  if constexpr (AGG) {
+    // lanes with the same key elect a leader that adds the group size once
+    unsigned active = __ballot_sync(0xffffffffu, valid);
+    if (valid) {
+      unsigned peers = __match_any_sync(active, (int)key);
+      int leader = __ffs(peers) - 1;
+      if ((int)(threadIdx.x & 31) == leader) atomicAdd(hist + key, (u32)__popc(peers));
+    }
+  } else {
+    if (valid) atomicAdd(hist + key, 1u);
+  }
+}
+
+template <typename PT, typename TT, bool AGG>
+__global__ void __launch_bounds__(kConfmatThreads)
+confmat_smem_kernel(const PT* __restrict__ preds, const TT* __restrict__ target, long long n, long long C,
+                    int has_ignore, long long ignore, u64* __restrict__ confmat, int* __restrict__ status) {
+  extern __shared__ u32 hist[];
+  const int CC = (int)(C * C);
+  for (int i = threadIdx.x; i < CC; i += blockDim.x) hist[i] = 0;
+  __syncthreads();
+  const long long nvec = n >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  int bad = 0;
+  // every lane of a warp runs the same number of iterations (match_any needs converged warps)
+  const long long iters = (nvec + stride - 1) / stride;
+  long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (long long it = 0; it < iters; ++it, g += stride) {
+    const bool in = g < nvec;
+    Vec4<PT> p;
+    Vec4<TT> t;
+    if (in) {
+      p = load4(preds + 4 * g);
+      t = load4(target + 4 * g);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      long long key = 0;
+      bool valid = in && make_key(p.v[j], t.v[j], C, (long long)CC, has_ignore, ignore, key, bad);
+      smem_count<AGG>(hist, key, valid);
+    }
+  }
+  {
+    const bool in = blockIdx.x == 0 && threadIdx.x < (n & 3);
+    long long key = 0;
+    bool valid = false;
+    if (in) {
+      long long i = (nvec << 2) + threadIdx.x;
+      valid = make_key(preds[i], target[i], C, (long long)CC, has_ignore, ignore, key, bad);
+    }
+    if (threadIdx.x < 32) smem_count<AGG>(hist, key, valid);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < CC; i += blockDim.x) {
+    u32 c = hist[i];
+    if (c) atomicAdd(confmat + i, (u64)c);
+  }
+  if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
+}
+
+// n_valid / n_equal (multiclass micro statistics)
+template <typename PT, typename TT>
+__global__ void __launch_bounds__(kConfmatThreads)
+match_count_kernel(const PT* __restrict__ preds, const TT* __restrict__ target, long long n, int has_ignore,
+                   long long ignore, u64* __restrict__ out2) {
+  const long long nvec = n >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  u32 valid = 0, equal = 0;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nvec; g += stride) {
+    Vec4<PT> p = load4(preds + 4 * g);
+    Vec4<TT> t = load4(target + 4 * g);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      long long tl = as_i64(t.v[j]);
+      bool ok = !(has_ignore && tl == ignore);
+      valid += ok;
+      equal += ok && (tl == as_i64(p.v[j]));
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    long long i = (nvec << 2) + threadIdx.x;
+    long long tl = as_i64(target[i]);
+    bool ok = !(has_ignore && tl == ignore);
+    valid += ok;
+    equal += ok && (tl == as_i64(preds[i]));
+  }
+  valid = __reduce_add_sync(0xffffffffu, valid);
+  equal = __reduce_add_sync(0xffffffffu, equal);
+  __shared__ u32 s[2];
+  if (threadIdx.x < 2) s[threadIdx.x] = 0;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&s[0], valid);
+    atomicAdd(&s[1], equal);
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 && s[threadIdx.x]) atomicAdd(out2 + threadIdx.x, (u64)s[threadIdx.x]);
+}
+
+static int grid_for(long long nvec, int threads, int ctas_per_sm) {
+  long long want = (nvec + threads - 1) / threads;
+  long long cap = (long long)sm_count() * ctas_per_sm;
+  if (want < 1) want = 1;
+  return (int)(want < cap ? want : cap);
+}
+
+template <typename PT, typename TT>
+static int launch_confmat(const PT* preds, const TT* target, long long n, long long C, int has_ignore,
+                          long long ignore, u64* confmat, int* status, int algo, cudaStream_t st) {
+  const long long CC = C * C;
+  const size_t smem = (size_t)CC * sizeof(u32);
+  const bool fits = smem <= (size_t)max_optin_smem() - 1024;
+  if (algo == 0) algo = (fits && CC <= 16384) ? 2 : 1;
+  if (algo == 2 && !fits) return TMB_ERR_TOO_LARGE;
+  const long long nvec = n >> 2;
+  if (algo == 1) {
+    // 4 resident CTAs of 256 threads per SM, 2 groups of 4 samples in flight per thread
+    int grid = grid_for((nvec + 1) / 2, kConfmatThreads, 4);
+    confmat_global_kernel<PT, TT, 2, 4, false><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+                                                                                 ignore, confmat, status);
+  } else if (algo == 3) {
+    int grid = grid_for((nvec + 3) / 4, kConfmatThreads, 3);
+    confmat_global_kernel<PT, TT, 4, 3, false><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+                                                                                 ignore, confmat, status);
+  } else if (algo == 4) {
+    int grid = grid_for(nvec, kConfmatThreads, 8);
+    confmat_global_kernel<PT, TT, 1, 8, false><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+                                                                                 ignore, confmat, status);
+  } else if (algo == 5) {
+    int grid = grid_for((nvec + 1) / 2, kConfmatThreads, 4);
+    confmat_global_kernel<PT, TT, 2, 4, true><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+                                                                                ignore, confmat, status);
+  } else if (algo != 2) {
+    return TMB_ERR_ARG;
+  } else {
+    int per_sm = smem > 0 ? (int)((size_t)(200 * 1024) / (smem + 1024)) : 8;
+    if (per_sm > 8) per_sm = 8;
+    if (per_sm < 1) per_sm = 1;
+    int grid = grid_for(nvec, kConfmatThreads, per_sm);
+    if (CC <= 1024) {
+      auto k = confmat_smem_kernel<PT, TT, true>;
+      TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, kConfmatThreads, smem, st>>>(preds, target, n, C, has_ignore, ignore, confmat, status);
+    } else {
+      auto k = confmat_smem_kernel<PT, TT, false>;
+      TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, kConfmatThreads, smem, st>>>(preds, target, n, C, has_ignore, ignore, confmat, status);
+    }
+  }
+  TMB_CUDA_CHECK(cudaGetLastError());
+  return TMB_OK;
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" int tmb_confmat_update(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n,
+                                  int64_t num_classes, int has_ignore, int64_t ignore_index, int64_t* confmat,
+                                  int32_t* status, int algo, void* stream) {
+  if (n < 0 || num_classes < 1 || num_classes > 3000000 || !confmat || !status) return TMB_ERR_ARG;
+  if (n == 0) return TMB_OK;
+  if (!preds || !target) return TMB_ERR_ARG;
+  if (!aligned32(preds) || !aligned32(target)) return TMB_ERR_ALIGN;
+  cudaStream_t st = (cudaStream_t)stream;
+  TMB_DISPATCH_INT(preds_dtype, PT, {
+    TMB_DISPATCH_INT(target_dtype, TT, {
+      return launch_confmat<PT, TT>((const PT*)preds, (const TT*)target, n, num_classes, has_ignore, ignore_index,
+                                    (u64*)confmat, status, algo, st);
+    })
+  })
+  return TMB_ERR_ARG;
+}
+
+extern "C" int tmb_match_count_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                      int64_t n, int has_ignore, int64_t ignore_index, int64_t* out2, void* stream) {
+  if (n < 0 || !out2) return TMB_ERR_ARG;
+  if (n == 0) return TMB_OK;
+  if (!preds || !target) return TMB_ERR_ARG;
+  if (!aligned32(preds) || !aligned32(target)) return TMB_ERR_ALIGN;
+  cudaStream_t st = (cudaStream_t)stream;
+  TMB_DISPATCH_INT(preds_dtype, PT, {
+    TMB_DISPATCH_INT(target_dtype, TT, {
+      int grid = grid_for(n >> 2, kConfmatThreads, 8);
+      match_count_kernel<PT, TT><<<grid, kConfmatThreads, 0, st>>>((const PT*)preds, (const TT*)target, n, has_ignore,
+                                                                   ignore_index, (u64*)out2);
+      TMB_CUDA_CHECK(cudaGetLastError());
+      return TMB_OK;
+    })
+  })
+  return TMB_ERR_ARG;
+}

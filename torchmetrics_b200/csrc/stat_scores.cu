@@ -1,0 +1,296 @@
+// K2 — tp / fp / tn / fn per label in one pass (contract in include/tm_b200.h).
+//
+// The reference runs ~20 elementwise / reduction kernels over bool and int64 temporaries
+// (stat_scores.py:90-131, :647-681).  Here each (pred, target) element is read once with 128/256-bit loads.
+// Threads are mapped so that a thread always sees the same 4 labels (its position in a row is invariant under
+// the grid stride), so the four statistics of each label live in registers for the whole kernel; they are
+// merged through shared memory once per CTA and through one 64-bit RED per (label, statistic) per CTA.
+//
+// The reference's all-or-nothing sigmoid is handled as in K3: pass 1 thresholds the raw scores and raises a
+// flag when a score lies outside [0,1]; pass 2 always launches, exits unless the flag is up, and then
+// recounts with sigmoid(p).  Partial counts of an abandoned pass 1 are dropped by the finalising CTA.
+#include "common.cuh"
+
+namespace tmb {
+
+struct StatWs {
+  int flag_oor;
+  int ticket;
+  int pad[6];
+  // followed by u64 acc[4 * L]  ([tp|fp|tn|fn][label])
+};
+static_assert(sizeof(StatWs) == 32, "workspace header");
+
+constexpr int kStatThreads = 512;
+
+struct StatParams {
+  const void* preds;
+  const void* target;
+  long long n_rows;
+  long long L;
+  double threshold;
+  int has_ignore;
+  long long ignore;
+  int check_range;
+  int only_if_flag;
+  u64* out;  // [4][L]
+  StatWs* ws;
+};
+
+template <typename PT>
+struct IsFloatScore {
+  static constexpr bool value = false;
+};
+template <> struct IsFloatScore<float> { static constexpr bool value = true; };
+template <> struct IsFloatScore<double> { static constexpr bool value = true; };
+template <> struct IsFloatScore<__half> { static constexpr bool value = true; };
+template <> struct IsFloatScore<__nv_bfloat16> { static constexpr bool value = true; };
+
+// the comparison `preds > threshold` happens in the preds dtype (a Python scalar does not promote a tensor)
+template <typename PT>
+__device__ __forceinline__ typename CmpType<PT>::type threshold_as(double thr) {
+  if constexpr (!IsFloatScore<PT>::value) return 0.f;
+  else if constexpr (sizeof(PT) == 8) return thr;
+  else if constexpr (sizeof(PT) == 4) return (float)thr;
+  else return to_cmp(PT((float)thr));
+}
+
+struct Counts {
+  u32 tp, fp, tn, fn;
+};
+
+template <typename PT, typename TT, bool SIGMOID>
+__device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typename CmpType<PT>::type thr, Counts& c,
+                                      int& oor) {
+  long long t = as_i64(tv);
+  if constexpr (IsFloatScore<PT>::value) {
+    using CT = typename CmpType<PT>::type;
+    CT p = to_cmp(pv);
+    // the reference range-checks the whole preds tensor, ignored positions included (stat_scores.py:104, :657)
+    if (P.check_range) oor |= !(p >= (CT)0 && p <= (CT)1);
+    if (P.has_ignore && t == P.ignore) return;
+    if constexpr (SIGMOID) p = round_to_storage<PT>(sigmoid_ref(p));
+    const bool pb = p > thr;
+    c.tp += (t == 1) & pb;
+    c.fn += (t == 1) & !pb;
+    c.fp += (t == 0) & pb;
+    c.tn += (t == 0) & !pb;
+  } else {
+    if (P.has_ignore && t == P.ignore) return;
+    long long p = as_i64(pv);
+    const bool eq = (t == p);
+    c.tp += (t == 1) & eq;
+    c.fn += (t == 1) & !eq;
+    c.fp += (t == 0) & !eq;
+    c.tn += (t == 0) & eq;
+  }
+}
+
+// V = 4: L % 4 == 0, a thread owns 4 consecutive labels.  V = 1: any L, a thread owns one label.
+// FLAT (L == 1): every element belongs to label 0 and is read 4 at a time.
+template <typename PT, typename TT, bool SIGMOID, int V, bool FLAT>
+__global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const StatParams P) {
+  using CT = typename CmpType<PT>::type;
+  StatWs* ws = P.ws;
+  if (P.only_if_flag && ws->flag_oor == 0) return;
+  extern __shared__ u32 s_cnt[];  // [4][CW*V] for this CTA's column tile
+  __shared__ int s_last;
+  const int NT = blockDim.x, tid = threadIdx.x;
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  const CT thr = threshold_as<PT>(P.threshold);
+  const long long L = P.L;
+  u64* acc = reinterpret_cast<u64*>(ws + 1);
+  int oor = 0;
+  Counts c[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) c[j] = Counts{0, 0, 0, 0};
+
+  const long long colgroups = FLAT ? 1 : L / V;
+  const int CW = (int)(colgroups < NT ? colgroups : NT);  // column groups per CTA tile
+  const int RP = FLAT ? NT : NT / CW;                     // rows per pass
+  const int ncols_smem = FLAT ? 1 : CW * V;
+  for (int i = tid; i < 4 * ncols_smem; i += NT) s_cnt[i] = 0;
+  __syncthreads();
+
+  long long cg = 0;
+  bool active;
+  if constexpr (FLAT) {
+    active = true;
+    const long long n = P.n_rows;
+    const long long nvec = n >> 2;
+    const long long stride = (long long)gridDim.x * NT;
+    long long it = 0;
+    for (long long g = (long long)blockIdx.x * NT + tid; g < nvec; g += stride, ++it) {
+      Vec4<PT> p = load4(preds + 4 * g);
+      Vec4<TT> t = load4(target + 4 * g);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[0], oor);
+      if (P.check_range && (it & 63) == 63) {
+        if (oor) atomicOr(&ws->flag_oor, 1);
+        if (*(volatile int*)&ws->flag_oor) break;
+      }
+    }
+    if (blockIdx.x == 0 && tid < (n & 3)) {
+      long long i = (nvec << 2) + tid;
+      tally<PT, TT, SIGMOID>(preds[i], target[i], P, thr, c[0], oor);
+    }
+  } else {
+    const int r0 = tid / CW;
+    cg = (long long)blockIdx.y * CW + (tid - r0 * CW);
+    active = r0 < RP && cg < colgroups;
+    if (active) {
+      const long long rstride = (long long)gridDim.x * RP;
+      long long it = 0;
+      for (long long r = (long long)blockIdx.x * RP + r0; r < P.n_rows; r += rstride, ++it) {
+        const long long e = r * L + cg * V;
+        if constexpr (V == 4) {
+          Vec4<PT> p = load4(preds + e);
+          Vec4<TT> t = load4(target + e);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[j], oor);
+        } else {
+          tally<PT, TT, SIGMOID>(preds[e], target[e], P, thr, c[0], oor);
+        }
+        if (P.check_range && (it & 63) == 63) {
+          if (oor) atomicOr(&ws->flag_oor, 1);
+          if (*(volatile int*)&ws->flag_oor) break;
+        }
+      }
+    }
+  }
+  if (P.check_range && oor) atomicOr(&ws->flag_oor, 1);
+
+  // merge: registers -> shared (per CTA) -> global scratch
+  if (active) {
+    const int lc = FLAT ? 0 : (int)(cg - (long long)blockIdx.y * CW) * V;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      if (c[j].tp) atomicAdd(&s_cnt[0 * ncols_smem + lc + j], c[j].tp);
+      if (c[j].fp) atomicAdd(&s_cnt[1 * ncols_smem + lc + j], c[j].fp);
+      if (c[j].tn) atomicAdd(&s_cnt[2 * ncols_smem + lc + j], c[j].tn);
+      if (c[j].fn) atomicAdd(&s_cnt[3 * ncols_smem + lc + j], c[j].fn);
+    }
+  }
+  __syncthreads();
+  const long long col0 = FLAT ? 0 : (long long)blockIdx.y * CW * V;
+  for (int i = tid; i < 4 * ncols_smem; i += NT) {
+    const int s = i / ncols_smem, lc = i - s * ncols_smem;
+    u32 v = s_cnt[i];
+    if (v && col0 + lc < L) atomicAdd(acc + s * L + col0 + lc, (u64)v);
+  }
+  __threadfence();
+  __syncthreads();
+  const int nblocks = gridDim.x * gridDim.y;
+  if (tid == 0) s_last = (atomicAdd(&ws->ticket, 1) == nblocks - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int flag = *(volatile int*)&ws->flag_oor;
+  const bool discard = P.check_range && flag != 0;
+  for (long long i = tid; i < 4 * L; i += NT) {
+    u64 v = __ldcg(acc + i);
+    acc[i] = 0;
+    if (!discard && v) P.out[i] += v;
+  }
+  if (tid == 0) {
+    ws->ticket = 0;
+    if (!P.check_range && P.only_if_flag) ws->flag_oor = 0;
+  }
+}
+
+template <typename PT, typename TT, bool SIGMOID>
+static int launch_one(const StatParams& P, cudaStream_t st) {
+  const long long L = P.L;
+  if (L == 1) {
+    long long nvec = P.n_rows >> 2;
+    long long want = (nvec + kStatThreads - 1) / kStatThreads;
+    long long cap = (long long)sm_count() * 2;
+    int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
+    stat_scores_kernel<PT, TT, SIGMOID, 1, true><<<grid, kStatThreads, 4 * sizeof(u32), st>>>(P);
+  } else {
+    const int V = (L % 4 == 0) ? 4 : 1;
+    const long long colgroups = L / V;
+    const int CW = (int)(colgroups < kStatThreads ? colgroups : kStatThreads);
+    const int RP = kStatThreads / CW;
+    const long long gy = (colgroups + CW - 1) / CW;
+    if (gy > 65535) return TMB_ERR_TOO_LARGE;
+    long long want = (P.n_rows + RP - 1) / RP;
+    long long cap = ((long long)sm_count() * 2 + gy - 1) / gy;
+    if (cap < 1) cap = 1;
+    int gx = (int)(want < 1 ? 1 : want < cap ? want : cap);
+    const size_t smem = (size_t)4 * CW * V * sizeof(u32);
+    dim3 grid(gx, (unsigned)gy);
+    if (V == 4) stat_scores_kernel<PT, TT, SIGMOID, 4, false><<<grid, kStatThreads, smem, st>>>(P);
+    else stat_scores_kernel<PT, TT, SIGMOID, 1, false><<<grid, kStatThreads, smem, st>>>(P);
+  }
+  TMB_CUDA_CHECK(cudaGetLastError());
+  return TMB_OK;
+}
+
+template <typename PT, typename TT>
+static int launch_stat(StatParams P, int prob_mode, cudaStream_t st) {
+  if constexpr (!IsFloatScore<PT>::value) {
+    P.check_range = 0; P.only_if_flag = 0;
+    return launch_one<PT, TT, false>(P, st);
+  } else {
+    int rc;
+    switch (prob_mode) {
+      case TMB_PROB_AS_IS:
+        P.check_range = 0; P.only_if_flag = 0;
+        return launch_one<PT, TT, false>(P, st);
+      case TMB_PROB_SIGMOID:
+        P.check_range = 0; P.only_if_flag = 0;
+        return launch_one<PT, TT, true>(P, st);
+      case TMB_PROB_AUTO:
+        P.check_range = 1; P.only_if_flag = 0;
+        rc = launch_one<PT, TT, false>(P, st);
+        if (rc != TMB_OK) return rc;
+        P.check_range = 0; P.only_if_flag = 1;
+        return launch_one<PT, TT, true>(P, st);
+      default:
+        return TMB_ERR_ARG;
+    }
+  }
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" size_t tmb_stat_scores_workspace_bytes(int64_t num_labels) {
+  if (num_labels < 1) return 0;
+  return sizeof(StatWs) + (size_t)4 * num_labels * sizeof(u64);
+}
+
+extern "C" int tmb_stat_scores_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                      int64_t n_rows, int64_t num_labels, double threshold, int prob_mode,
+                                      int has_ignore, int64_t ignore_index, int64_t* out, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+  if (n_rows < 0 || num_labels < 1 || !out || !workspace) return TMB_ERR_ARG;
+  if (workspace_bytes < tmb_stat_scores_workspace_bytes(num_labels)) return TMB_ERR_ARG;
+  if (n_rows == 0) return TMB_OK;
+  if (!preds || !target) return TMB_ERR_ARG;
+  if (!aligned32(preds) || !aligned32(target) || !aligned32(workspace)) return TMB_ERR_ALIGN;
+  StatParams P{};
+  P.preds = preds;
+  P.target = target;
+  P.n_rows = n_rows;
+  P.L = num_labels;
+  P.threshold = threshold;
+  P.has_ignore = has_ignore ? 1 : 0;
+  P.ignore = ignore_index;
+  P.out = (u64*)out;
+  P.ws = (StatWs*)workspace;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_float_dtype(preds_dtype)) {
+    TMB_DISPATCH_FLOAT(preds_dtype, PT, {
+      TMB_DISPATCH_INT(target_dtype, TT, { return launch_stat<PT, TT>(P, prob_mode, st); })
+    })
+  } else {
+    TMB_DISPATCH_INT(preds_dtype, PT, {
+      TMB_DISPATCH_INT(target_dtype, TT, { return launch_stat<PT, TT>(P, prob_mode, st); })
+    })
+  }
+  return TMB_ERR_ARG;
+}
