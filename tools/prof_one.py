@@ -1,0 +1,36 @@
+"""Run one kernel a few times (for ncu). Usage: python tools/prof_one.py binned|confmat|stat [log2n]"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from torchmetrics_b200 import _native as N  # noqa: E402
+
+DEV = torch.device("cuda:0")
+what = sys.argv[1]
+n = 1 << int(sys.argv[2]) if len(sys.argv) > 2 else 1 << 26
+g = torch.Generator(device=DEV).manual_seed(1)
+if what == "binned":
+    thr = torch.linspace(0, 1, 200, device=DEV)
+    preds = torch.rand(n, device=DEV, generator=g)
+    target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
+    st = torch.zeros(200, 2, 2, dtype=torch.int64, device=DEV)
+    for _ in range(4):
+        N.binned_curve_update_(st, preds, target, thr, prob_mode=N.PROB_AS_IS)
+elif what == "confmat":
+    C = 1000
+    p = torch.randint(0, C, (n,), device=DEV, generator=g)
+    t = torch.randint(0, C, (n,), device=DEV, generator=g)
+    cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+    for _ in range(4):
+        N.confmat_update_(cm, p, t, C)
+elif what == "stat":
+    L = 100
+    p = torch.rand(n // 128, L, device=DEV, generator=g)
+    t = torch.randint(0, 2, (n // 128, L), device=DEV, generator=g)
+    out = torch.zeros(4, L, dtype=torch.int64, device=DEV)
+    for _ in range(4):
+        N.stat_scores_update_(out, p, t, L, 0.5, None, N.PROB_AS_IS)
+torch.cuda.synchronize()
+print("done", what, n)

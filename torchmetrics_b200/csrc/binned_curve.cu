@@ -19,6 +19,9 @@
 // bins the raw scores and raises a flag on the first score outside [0,1]; pass 2 is always enqueued but
 // exits at once unless the flag is up, in which case it redoes the batch with sigmoid(p) and pass 1's
 // partial histogram is discarded.
+#include <cstdlib>
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace tmb {
@@ -145,13 +148,47 @@ __device__ void finalize_columns(const BinnedParams& P, u64* hist, u64* s_scan, 
 }
 
 // =================================================================================================
-// private-histogram kernel (num_columns == 1)
+// private-histogram kernel (one column, float32 scores)
 // =================================================================================================
-constexpr int kFlushEvery = 63;  // tiles of 4 samples per thread between folds: 252 <= 255
+constexpr int kTilesPerFold = 62;  // 4 samples per thread per tile: 62*4 + 4 (ragged tail) <= 255
 
-template <typename PT, typename TT, bool SIGMOID>
-__global__ void __launch_bounds__(1024, 1) binned_private_kernel(const BinnedParams P) {
-  using CT = typename CmpType<PT>::type;
+enum : int { kModeAsIs = 0, kModeAsIsCheck = 1, kModeSigmoid = 2 };
+
+// Evenly spaced thresholds (what torch.linspace / an int `thresholds` argument produce) need no table walk:
+// with j = clamp(round((p - lo) / step)) the stored values satisfy thr[j-1] <= p < thr[j+1], so
+// bin = j + (p >= thr[j]) — ONE compare against the caller's own value, still exact.  The spacing is verified
+// here, per CTA, against the actual tensor (every thr[i] within step/8 of lo + i*step, computed in double);
+// x = (p-lo)*inv_step+0.5 is off by at most T*2^-22 <= 1/64 for T <= 65536, which leaves the needed margin.
+struct UniformMap {
+  float lo, inv_step;
+  unsigned jmax;
+  bool ok;
+};
+
+__device__ __forceinline__ UniformMap detect_uniform(const float* s_thr, int T) {
+  UniformMap u;
+  const double lo = s_thr[0], hi = s_thr[T - 1];
+  const double step = T >= 2 ? (hi - lo) / (double)(T - 1) : 0.0;
+  int bad = !(T >= 2 && T <= 65536 && step > 0.0 && step < 1e30 && fabs(lo) < 1e30);
+  if (!bad)
+    for (int i = threadIdx.x; i < T; i += blockDim.x) {
+      double d = fabs((double)s_thr[i] - (lo + (double)i * step));
+      if (!(d <= 0.125 * step)) bad = 1;
+    }
+  bad = __syncthreads_or(bad);
+  u.ok = !bad;
+  u.lo = (float)lo;
+  u.inv_step = bad ? 0.f : (float)(1.0 / step);
+  u.jmax = (unsigned)(T - 1);
+  return u;
+}
+
+template <typename TT, int MODE, bool HAS_IGNORE, int MAXNT>
+__global__ void __launch_bounds__(MAXNT, 1) binned_private_kernel(const BinnedParams P) {
+  constexpr bool CHECK = MODE == kModeAsIsCheck;
+  constexpr bool SIGMOID = MODE == kModeSigmoid;
+  constexpr int PF = MAXNT > 768 ? 1 : MAXNT > 512 ? 2 : 3;  // tiles prefetched ahead (64 / 85 / 128 registers)
+  constexpr int NSLOT = PF + 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BinnedWs* ws = P.ws;
   if (P.only_if_flag && ws->flag_oor == 0) return;
@@ -173,30 +210,40 @@ __global__ void __launch_bounds__(1024, 1) binned_private_kernel(const BinnedPar
     if (blockIdx.x == 0 && tid == 0) atomicOr(P.status, TMB_STATUS_THRESHOLD_ORDER);
     return;  // uniform over the grid; workspace untouched
   }
+  const UniformMap um = detect_uniform(s_thr, T);
 
-  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const float* __restrict__ preds = static_cast<const float*>(P.preds);
   const TT* __restrict__ target = static_cast<const TT*>(P.target);
   const long long n = P.n_rows;
   const long long tile_elems = (long long)NT * 4;
-  const long long ntiles = (n + tile_elems - 1) / tile_elems;
-  u32* my = s_hist + tid;
+  const long long nfull = n / tile_elems;
+  const long long ignore = P.ignore;
+  u32* const my = s_hist + tid;
   int oor = 0;
 
-  // bin index of one sample (or -1 when it is ignored); reads only the threshold tables, so the four lookups
-  // of a vector are independent of the counter updates that follow and can overlap
-  auto index_of = [&](PT pv, TT tv) -> int {
-    long long tl = as_i64(tv);
-    const bool ign = P.has_ignore && tl == P.ignore;
-    CT p = to_cmp(pv);
-    if (P.check_range && (!ign || P.oor_counts_ignored)) oor |= out_of_unit(p);
-    if (ign) return -1;
-    if constexpr (SIGMOID) p = round_to_storage<PT>(sigmoid_ref(p));
-    return bin_of(p, m, s_thr, s_lut) + (tl == 1 ? NB : 0);
+  // (score, target) -> counter index, or increments nothing when ignored.  The four lookups of a vector read
+  // only the threshold tables, so they overlap; the four counter updates that follow are serial RMWs.
+  auto index_of = [&](float p, TT tv, u32& inc, auto uniform_tag) -> int {
+    const long long tl = as_i64(tv);
+    bool valid = true;
+    if constexpr (HAS_IGNORE) valid = tl != ignore;
+    if constexpr (CHECK) oor |= (int)(valid & !(p >= 0.f && p <= 1.f));
+    if constexpr (SIGMOID) p = sigmoid_ref(p);
+    int cnt;
+    if constexpr (decltype(uniform_tag)::value) {
+      const float x = fmaf(p - um.lo, um.inv_step, 0.5f);
+      const unsigned j = min(__float2uint_rz(x), um.jmax);  // saturating: negative / NaN -> 0
+      cnt = (int)j + (int)(p >= s_thr[j]);
+    } else {
+      cnt = bin_of(p, m, s_thr, s_lut);
+    }
+    const int idx = cnt + (tl == 1 ? NB : 0);
+    inc = (u32)valid << ((idx & 3) << 3);
+    return idx;
   };
-  auto bump = [&](int idx) {
-    if (idx < 0) return;
+  auto bump = [&](int idx, u32 inc) {
     u32* w = my + (idx >> 2) * NT;
-    *w += 1u << ((idx & 3) << 3);
+    *w += inc;
   };
 
   // fold every thread's byte counters into the CTA's 64-bit totals and clear them
@@ -225,46 +272,62 @@ __global__ void __launch_bounds__(1024, 1) binned_private_kernel(const BinnedPar
     __syncthreads();
   };
 
-  int since_fold = 0;
-  bool stop = false;
-  long long tile = blockIdx.x;
-  // software prefetch: the next tile's vectors are in flight while this one is binned
-  Vec4<PT> pn;
-  Vec4<TT> tn;
-  auto fetch = [&](long long tl_) {
-    long long base = tl_ * tile_elems + (long long)tid * 4;
-    if (tl_ < ntiles && base + 4 <= n) {
-      pn = load4(preds + base);
-      tn = load4(target + base);
+  auto run = [&](auto uniform_tag) {
+    const long long first = blockIdx.x;
+    const int my_tiles = first < nfull ? (int)((nfull - 1 - first) / gridDim.x) + 1 : 0;
+    const long long adv = (long long)gridDim.x * tile_elems;
+    const float* pp = preds + first * tile_elems + (long long)tid * 4;
+    const TT* tp = target + first * tile_elems + (long long)tid * 4;
+    Vec4<float> pb[NSLOT];
+    Vec4<TT> tb[NSLOT];
+#pragma unroll
+    for (int s = 0; s < PF; ++s)
+      if (s < my_tiles) {
+        pb[s] = load4(pp + s * adv);
+        tb[s] = load4(tp + s * adv);
+      }
+    int since_fold = 0;
+    bool stop = false;
+    for (int k = 0; k < my_tiles && !stop; k += NSLOT) {
+#pragma unroll
+      for (int s = 0; s < NSLOT; ++s) {
+        if (k + s < my_tiles && !stop) {
+          if (k + s + PF < my_tiles) {
+            pb[(s + PF) % NSLOT] = load4(pp + (long long)(k + s + PF) * adv);
+            tb[(s + PF) % NSLOT] = load4(tp + (long long)(k + s + PF) * adv);
+          }
+          int idx[4];
+          u32 inc[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) idx[j] = index_of(pb[s].v[j], tb[s].v[j], inc[j], uniform_tag);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bump(idx[j], inc[j]);
+          if (++since_fold == kTilesPerFold) {
+            since_fold = 0;
+            if constexpr (CHECK) {
+              if (oor) atomicOr(&ws->flag_oor, 1);
+              // a raised flag makes the rest of this pass useless: every CTA bails out at its next fold
+              stop = __syncthreads_or(oor | *(volatile int*)&ws->flag_oor) != 0;
+            }
+            fold();
+          }
+        }
+      }
+    }
+    // ragged tail (< one tile): owned by the CTA that would have taken tile `nfull`
+    if ((long long)blockIdx.x == nfull % gridDim.x && !stop) {
+      const long long base = nfull * tile_elems + (long long)tid * 4;
+      if (since_fold == kTilesPerFold - 1) fold();
+      for (long long i = base; i < n && i < base + 4; ++i) {
+        u32 inc;
+        int idx = index_of(preds[i], target[i], inc, uniform_tag);
+        bump(idx, inc);
+      }
     }
   };
-  fetch(tile);
-  while (tile < ntiles && !stop) {
-    Vec4<PT> pc = pn;
-    Vec4<TT> tc = tn;
-    const long long base = tile * tile_elems + (long long)tid * 4;
-    fetch(tile + gridDim.x);
-    if (base + 4 <= n) {
-      int idx[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) idx[j] = index_of(pc.v[j], tc.v[j]);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) bump(idx[j]);
-    } else {
-      for (long long i = base; i < n && i < base + 4; ++i) bump(index_of(preds[i], target[i]));
-    }
-    tile += gridDim.x;
-    if (++since_fold == kFlushEvery) {
-      since_fold = 0;
-      if (P.check_range) {
-        if (oor) atomicOr(&ws->flag_oor, 1);
-        // a raised flag makes the rest of this pass useless: every CTA bails out at its next fold
-        stop = __syncthreads_or(oor | *(volatile int*)&ws->flag_oor) != 0;
-      }
-      fold();
-    }
-  }
-  if (P.check_range && oor) atomicOr(&ws->flag_oor, 1);
+  if (um.ok) run(std::true_type{}); else run(std::false_type{});
+
+  if (CHECK && oor) atomicOr(&ws->flag_oor, 1);
   fold();
 
   u64* hist = reinterpret_cast<u64*>(ws + 1);
@@ -279,11 +342,11 @@ __global__ void __launch_bounds__(1024, 1) binned_private_kernel(const BinnedPar
   if (!s_last) return;
   __threadfence();
   const int flag = *(volatile int*)&ws->flag_oor;
-  const bool discard = P.check_range && flag != 0;
+  const bool discard = CHECK && flag != 0;
   finalize_columns(P, hist, s_acc, discard);
   if (tid == 0) {
     ws->ticket = 0;
-    if (P.check_range) {
+    if (CHECK) {
       if (discard && P.status_bit_on_oor) {
         atomicOr(P.status, P.status_bit_on_oor);
         ws->flag_oor = 0;
@@ -412,12 +475,35 @@ static size_t private_smem_bytes(int T, int NT) {
   return (size_t)W * NT * 4 + (size_t)NB2 * 8 + (size_t)NB * 4 + kLutCells * 2 + 16;
 }
 
-// largest CTA (multiple of 32 threads) whose private histograms fit; 0 if fewer than 128 threads would
+// largest CTA (multiple of 32 threads) whose private histograms fit; 0 if fewer than 448 threads would
 static int private_threads(int T) {
   const size_t budget = (size_t)max_optin_smem() - 64;  // static __shared__ s_last rides along
-  for (int nt = 1024; nt >= 128; nt -= 32)
-    if (private_smem_bytes(T, nt) <= budget) return nt;
+  int cap = 1024;
+  if (const char* e = getenv("TMB_BINNED_NT")) cap = atoi(e);  // tuning knob (development only)
+  // below ~14 warps per SM the private kernel cannot hide its load latency and the atomic kernel wins (measured)
+  for (int nt = cap; nt >= 448; nt -= 32)
+    if (private_smem_bytes(T, nt) <= budget) {
+      // just above a register-budget step the extra warp or two is worth less than the deeper prefetch below it
+      if (nt > 512 && nt <= 576 && !getenv("TMB_BINNED_NT")) nt = 512;
+      return nt;
+    }
   return 0;
+}
+
+template <typename TT>
+static void (*pick_private(int mode, bool has_ignore, int nt))(const BinnedParams) {
+#define TMB_PICK(MODE)                                                                     \
+  if (has_ignore)                                                                          \
+    return nt > 768 ? binned_private_kernel<TT, MODE, true, 1024>                          \
+                    : nt > 512 ? binned_private_kernel<TT, MODE, true, 768>                \
+                               : binned_private_kernel<TT, MODE, true, 512>;               \
+  return nt > 768 ? binned_private_kernel<TT, MODE, false, 1024>                           \
+                  : nt > 512 ? binned_private_kernel<TT, MODE, false, 768>                 \
+                             : binned_private_kernel<TT, MODE, false, 512>;
+  if (mode == kModeAsIs) { TMB_PICK(kModeAsIs) }
+  if (mode == kModeAsIsCheck) { TMB_PICK(kModeAsIsCheck) }
+  TMB_PICK(kModeSigmoid)
+#undef TMB_PICK
 }
 
 template <typename PT, typename TT>
@@ -425,7 +511,9 @@ static int launch_binned(BinnedParams P, int prob_mode, cudaStream_t st) {
   const long long total = P.n_rows * P.num_columns;
   const int NB = P.T + 1;
   const long long nbins = P.num_columns * 2 * NB;
-  const int nt_private = (P.num_columns == 1 && !P.target_is_class_index) ? private_threads(P.T) : 0;
+  // the private-histogram kernel reads float32 scores; other score dtypes take the atomic kernel
+  const int nt_private = (std::is_same<PT, float>::value && P.num_columns == 1 && !P.target_is_class_index)
+                             ? private_threads(P.T) : 0;
 
   auto run = [&](bool sigmoid) -> int {
     if (nt_private) {
@@ -433,7 +521,8 @@ static int launch_binned(BinnedParams P, int prob_mode, cudaStream_t st) {
       const long long tile = (long long)nt_private * 4;
       long long ntiles = (total + tile - 1) / tile;
       int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
-      auto k = sigmoid ? binned_private_kernel<PT, TT, true> : binned_private_kernel<PT, TT, false>;
+      const int mode = sigmoid ? kModeSigmoid : (P.check_range ? kModeAsIsCheck : kModeAsIs);
+      auto k = pick_private<TT>(mode, P.has_ignore != 0, nt_private);
       TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       k<<<grid, nt_private, smem, st>>>(P);
     } else {
