@@ -1,0 +1,369 @@
+"""`MetricCollection`: fan-out of update / forward / compute with compute groups.
+
+Behaviour follows the reference (src/torchmetrics/collections.py:34-661): metrics whose states turn out equal after
+the first `update` form a compute group (:228-287); members of a group share the state tensors of the first member
+by reference (:289-308) so later `update`s touch one metric per group (:200-226); `forward` never uses groups;
+accessing a member hands out a copy of the shared state (:515-550).
+
+What differs is `compute()` under a distributed run: the reference lets every member run its own sync (16 gathers =
+48 collectives for a 4-metric stat-scores group).  Here the states of ALL group leaders go through
+one `fused_state_sync` (one packed all_reduce + one padded all_gather per cat state for the whole collection),
+members compute from the synced tensors, then every leader is un-synced.  Metrics with a custom `dist_sync_fn`,
+`sync_on_compute=False` or their own process group keep their individual path.
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from copy import deepcopy
+from typing import Any, Dict, Hashable, Iterable, Iterator, List, Optional, Sequence, Tuple, Union
+
+import torch
+from torch import Tensor
+from torch.nn import ModuleDict
+
+from torchmetrics_b200.metric import Metric, fused_state_sync
+from torchmetrics_b200.utilities.data import apply_to_collection  # noqa: F401
+from torchmetrics_b200.utilities.prints import rank_zero_warn
+
+
+def _flatten_dict(x: Dict) -> Tuple[Dict, bool]:
+    flat: Dict = {}
+    dup = False
+    for key, value in x.items():
+        if isinstance(value, dict):
+            for k, v in value.items():
+                dup = dup or k in flat
+                flat[k] = v
+        else:
+            dup = dup or key in flat
+            flat[key] = value
+    return flat, dup
+
+
+def _allclose_recursive(a: Any, b: Any) -> bool:
+    if isinstance(a, Tensor) and isinstance(b, Tensor):
+        return a.shape == b.shape and torch.allclose(a, b)
+    if isinstance(a, (list, tuple)) and isinstance(b, (list, tuple)):
+        return len(a) == len(b) and all(_allclose_recursive(x, y) for x, y in zip(a, b))
+    return a == b
+
+
+class MetricCollection(ModuleDict):
+    """Dictionary of metrics that are updated / computed together."""
+
+    _modules: Dict[str, Metric]  # type: ignore[assignment]
+    _groups: Dict[int, List[str]]
+
+    def __init__(self, metrics: Union[Metric, Sequence[Metric], Dict[str, Metric]], *additional_metrics: Metric,
+                 prefix: Optional[str] = None, postfix: Optional[str] = None,
+                 compute_groups: Union[bool, List[List[str]]] = True) -> None:
+        super().__init__()
+        self.prefix = self._check_arg(prefix, "prefix")
+        self.postfix = self._check_arg(postfix, "postfix")
+        self._enable_compute_groups = compute_groups
+        self._groups_checked = False
+        self._state_is_copy = False
+        self.add_metrics(metrics, *additional_metrics)
+
+    # ------------------------------------------------------------------ update / forward / compute
+    @torch.jit.unused
+    def forward(self, *args: Any, **kwargs: Any) -> Dict[str, Any]:
+        return self._compute_and_reduce("forward", *args, **kwargs)
+
+    def update(self, *args: Any, **kwargs: Any) -> None:
+        if self._groups_checked:
+            for members in self._groups.values():
+                leader = getattr(self, members[0])
+                leader.update(*args, **leader._filter_kwargs(**kwargs))
+            if self._state_is_copy:
+                self._compute_groups_create_state_ref()
+                self._state_is_copy = False
+        else:
+            for m in self.values(copy_state=False):
+                m.update(*args, **m._filter_kwargs(**kwargs))
+            if self._enable_compute_groups:
+                self._merge_compute_groups()
+                self._compute_groups_create_state_ref()
+                self._groups_checked = True
+
+    def _merge_compute_groups(self) -> None:
+        """Repeatedly merge two groups whose leaders hold equal states until nothing changes."""
+        while True:
+            merged = False
+            keys = list(self._groups.keys())
+            for i, k1 in enumerate(keys):
+                for k2 in keys[i + 1:]:
+                    a = getattr(self, self._groups[k1][0])
+                    b = getattr(self, self._groups[k2][0])
+                    if self._equal_metric_states(a, b):
+                        self._groups[k1].extend(self._groups.pop(k2))
+                        merged = True
+                        break
+                if merged:
+                    break
+            if not merged:
+                break
+        self._groups = {i: v for i, v in enumerate(deepcopy(list(self._groups.values())))}
+
+    @staticmethod
+    def _equal_metric_states(a: Metric, b: Metric) -> bool:
+        if len(a._defaults) == 0 or len(b._defaults) == 0:
+            return False
+        if a._defaults.keys() != b._defaults.keys():
+            return False
+        for key in a._defaults:
+            s1, s2 = getattr(a, key), getattr(b, key)
+            if type(s1) != type(s2):  # noqa: E721
+                return False
+            if isinstance(s1, Tensor) and isinstance(s2, Tensor):
+                if s1.shape != s2.shape or not torch.allclose(s1, s2):
+                    return False
+            elif isinstance(s1, list) and isinstance(s2, list):
+                if not _allclose_recursive(s1, s2):
+                    return False
+        return True
+
+    def _compute_groups_create_state_ref(self, copy: bool = False) -> None:
+        """Members of a group get the leader's state objects (or deep copies of them when `copy`)."""
+        if not self._state_is_copy:
+            for members in self._groups.values():
+                leader = getattr(self, members[0])
+                for name in members[1:]:
+                    m = getattr(self, name)
+                    for state in leader._defaults:
+                        val = getattr(leader, state)
+                        setattr(m, state, deepcopy(val) if copy else val)
+                    m._update_count = leader._update_count
+                    m._computed = deepcopy(leader._computed) if copy else leader._computed
+        self._state_is_copy = copy
+
+    def compute(self) -> Dict[str, Any]:
+        return self._compute_and_reduce("compute")
+
+    def _fusable_leaders(self) -> List[Tuple[Metric, List[Metric]]]:
+        """(leader, followers) pairs whose sync can be merged into one fused exchange."""
+        out = []
+        if not self._groups_checked or self._state_is_copy:
+            groups: Iterable[List[str]] = [[k] for k in self.keys(keep_base=True)]
+        else:
+            groups = self._groups.values()
+        for members in groups:
+            leader = getattr(self, members[0])
+            if not isinstance(leader, Metric) or isinstance(leader, _NO_FUSE):
+                continue
+            if (leader.dist_sync_fn is not None or not leader._to_sync or leader._is_synced
+                    or leader.process_group is not None or leader._computed is not None
+                    or not leader._defaults or not leader.distributed_available_fn()):
+                continue
+            out.append((leader, [getattr(self, n) for n in members[1:]]))
+        return out
+
+    def _compute_and_reduce(self, method_name: str, *args: Any, **kwargs: Any) -> Dict[str, Any]:
+        if method_name not in ("compute", "forward"):
+            raise ValueError(f"method_name should be either 'compute' or 'forward', but got {method_name}")
+        result: Dict[str, Any] = {}
+        fused: List[Tuple[Metric, List[Metric]]] = []
+        if method_name == "compute":
+            fused = self._fusable_leaders()
+        if fused:
+            leaders = [ld for ld, _ in fused]
+            for ld in leaders:
+                ld._cache = {name: getattr(ld, name) for name in ld._defaults}
+            fused_state_sync(leaders)
+            saved_flags = []
+            for ld, followers in fused:
+                ld._is_synced = True
+                for m in [ld, *followers]:
+                    saved_flags.append((m, m._to_sync, m._should_unsync))
+                    m._to_sync = False       # states are already merged
+                    m._should_unsync = False
+                for m in followers:          # followers read the leader's synced tensors
+                    for state in ld._defaults:
+                        setattr(m, state, getattr(ld, state))
+        try:
+            for k, m in self.items(keep_base=True, copy_state=False):
+                result[k] = m.compute() if method_name == "compute" else m(*args, **m._filter_kwargs(**kwargs))
+        finally:
+            if fused:
+                for m, to_sync, should_unsync in saved_flags:
+                    m._to_sync, m._should_unsync = to_sync, should_unsync
+                for ld, followers in fused:
+                    ld.unsync()
+                    for m in followers:
+                        for state in ld._defaults:
+                            setattr(m, state, getattr(ld, state))
+
+        _, duplicates = _flatten_dict(result)
+        flat: Dict[str, Any] = {}
+        for k, m in self.items(keep_base=True, copy_state=False):
+            res = result[k]
+            if not isinstance(res, dict):
+                flat[k] = res
+                continue
+            for key, v in res.items():
+                if duplicates:
+                    stripped = k.replace(getattr(m, "prefix", "") or "", "").replace(getattr(m, "postfix", "") or "", "")
+                    key = f"{stripped}_{key}"
+                if getattr(m, "_from_collection", None) and m.prefix is not None:
+                    key = f"{m.prefix}{key}"
+                if getattr(m, "_from_collection", None) and m.postfix is not None:
+                    key = f"{key}{m.postfix}"
+                flat[key] = v
+        return {self._set_name(k): v for k, v in flat.items()}
+
+    def reset(self) -> None:
+        for m in self.values(copy_state=False):
+            m.reset()
+        if self._enable_compute_groups and self._groups_checked:
+            self._compute_groups_create_state_ref()
+
+    def clone(self, prefix: Optional[str] = None, postfix: Optional[str] = None) -> "MetricCollection":
+        mc = deepcopy(self)
+        if prefix:
+            mc.prefix = self._check_arg(prefix, "prefix")
+        if postfix:
+            mc.postfix = self._check_arg(postfix, "postfix")
+        return mc
+
+    def persistent(self, mode: bool = True) -> None:
+        for m in self.values(copy_state=False):
+            m.persistent(mode)
+
+    # ------------------------------------------------------------------ construction
+    def add_metrics(self, metrics: Union[Metric, Sequence[Metric], Dict[str, Metric]],
+                    *additional_metrics: Metric) -> None:
+        if isinstance(metrics, Metric):
+            metrics = [metrics]
+        if isinstance(metrics, Sequence):
+            metrics = list(metrics)
+            extra = []
+            for m in additional_metrics:
+                (metrics if isinstance(m, Metric) else extra).append(m)
+            if extra:
+                rank_zero_warn(f"You have passes extra arguments {extra} which are not `Metric` so they will be ignored.")
+        elif additional_metrics:
+            raise ValueError(
+                f"You have passes extra arguments {additional_metrics} which are not compatible"
+                f" with first passed dictionary {metrics} so they will be ignored."
+            )
+
+        if isinstance(metrics, dict):
+            for name in sorted(metrics.keys()):
+                metric = metrics[name]
+                if not isinstance(metric, (Metric, MetricCollection)):
+                    raise ValueError(
+                        f"Value {metric} belonging to key {name} is not an instance of"
+                        " `torchmetrics.Metric` or `torchmetrics.MetricCollection`"
+                    )
+                if isinstance(metric, Metric):
+                    self[name] = metric
+                else:
+                    for k, v in metric.items(keep_base=False):
+                        v.postfix = metric.postfix
+                        v.prefix = metric.prefix
+                        v._from_collection = True
+                        self[f"{name}_{k}"] = v
+        elif isinstance(metrics, Sequence):
+            for metric in metrics:
+                if not isinstance(metric, (Metric, MetricCollection)):
+                    raise ValueError(
+                        f"Input {metric} to `MetricCollection` is not a instance of"
+                        " `torchmetrics.Metric` or `torchmetrics.MetricCollection`"
+                    )
+                if isinstance(metric, Metric):
+                    name = metric.__class__.__name__
+                    if name in self:
+                        raise ValueError(f"Encountered two metrics both named {name}")
+                    self[name] = metric
+                else:
+                    for k, v in metric.items(keep_base=False):
+                        v.postfix = metric.postfix
+                        v.prefix = metric.prefix
+                        v._from_collection = True
+                        self[k] = v
+        else:
+            raise ValueError(
+                "Unknown input to MetricCollection. Expected, `Metric`, `MetricCollection` or `dict`/`sequence` of the"
+                f" previous, but got {metrics}"
+            )
+        self._groups_checked = False
+        if self._enable_compute_groups:
+            self._init_compute_groups()
+        else:
+            self._groups = {}
+
+    def _init_compute_groups(self) -> None:
+        if isinstance(self._enable_compute_groups, list):
+            self._groups = dict(enumerate(self._enable_compute_groups))
+            for members in self._groups.values():
+                for name in members:
+                    if name not in self:
+                        raise ValueError(
+                            f"Input {name} in `compute_groups` argument does not match a metric in the collection."
+                            f" Please make sure that {self._enable_compute_groups} matches {self.keys(keep_base=True)}"
+                        )
+            self._groups_checked = True
+        else:
+            self._groups = {i: [str(k)] for i, k in enumerate(self.keys(keep_base=True))}
+
+    @property
+    def compute_groups(self) -> Dict[int, List[str]]:
+        return self._groups
+
+    # ------------------------------------------------------------------ naming / access
+    def _set_name(self, base: str) -> str:
+        name = base if self.prefix is None else self.prefix + base
+        return name if self.postfix is None else name + self.postfix
+
+    def _to_renamed_ordered_dict(self) -> OrderedDict:
+        return OrderedDict((self._set_name(k), v) for k, v in self._modules.items())
+
+    def __iter__(self) -> Iterator[Hashable]:
+        return iter(self.keys())
+
+    def keys(self, keep_base: bool = False) -> Iterable[Hashable]:  # type: ignore[override]
+        if keep_base:
+            return self._modules.keys()
+        return self._to_renamed_ordered_dict().keys()
+
+    def items(self, keep_base: bool = False, copy_state: bool = True) -> Iterable[Tuple[str, Metric]]:  # type: ignore[override]
+        self._compute_groups_create_state_ref(copy_state)
+        if keep_base:
+            return self._modules.items()
+        return self._to_renamed_ordered_dict().items()
+
+    def values(self, copy_state: bool = True) -> Iterable[Metric]:  # type: ignore[override]
+        self._compute_groups_create_state_ref(copy_state)
+        return self._modules.values()
+
+    def __getitem__(self, key: str, copy_state: bool = True) -> Metric:  # type: ignore[override]
+        self._compute_groups_create_state_ref(copy_state)
+        if self.prefix:
+            key = key.removeprefix(self.prefix)
+        if self.postfix:
+            key = key.removesuffix(self.postfix)
+        return self._modules[key]
+
+    @staticmethod
+    def _check_arg(arg: Optional[str], name: str) -> Optional[str]:
+        if arg is None or isinstance(arg, str):
+            return arg
+        raise ValueError(f"Expected input `{name}` to be a string, but got {type(arg)}")
+
+    def __repr__(self) -> str:
+        text = super().__repr__()[:-2]
+        if self.prefix:
+            text += f",\n  prefix={self.prefix}{',' if self.postfix else ''}"
+        if self.postfix:
+            text += f"{',' if not self.prefix else ''}\n  postfix={self.postfix}"
+        return text + "\n)"
+
+    def set_dtype(self, dst_type: Union[str, torch.dtype]) -> "MetricCollection":
+        for m in self.values(copy_state=False):
+            m.set_dtype(dst_type)
+        return self
+
+
+from torchmetrics_b200.metric import CompositionalMetric  # noqa: E402
+
+_NO_FUSE = (CompositionalMetric,)

@@ -1,0 +1,172 @@
+"""Cross-rank state exchange (reference: utilities/distributed.py:91-147, metric.py:427-457).
+
+Two paths:
+  * `gather_all_tensors` keeps the reference's per-tensor protocol (list of world_size tensors, uneven shapes
+    padded and trimmed) for `dist_sync_fn` users and for states with custom / `None` reductions; it drops the
+    reference's barrier.
+  * `fused_state_sync` is the default path of `Metric.sync`: every sum / max / min / mean tensor state of the
+    metrics handed in is packed into ONE flat buffer per (op, dtype) and reduced with ONE all_reduce (NCCL over
+    NVLink on the GPU box, gloo in CPU tests); every cat state takes one shared size exchange plus one padded
+    all_gather. Integer addition is exact and order-free, so the sum states are bit-identical to the reference's
+    gather + stack + sum.
+"""
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+from torch import Tensor
+
+
+def distributed_available() -> bool:
+    return dist.is_available() and dist.is_initialized()
+
+
+def _simple_gather_all_tensors(result: Tensor, group: Any, world_size: int) -> List[Tensor]:
+    gathered = [torch.zeros_like(result) for _ in range(world_size)]
+    dist.all_gather(gathered, result, group)
+    return gathered
+
+
+def gather_all_tensors(result: Tensor, group: Optional[Any] = None) -> List[Tensor]:
+    """Every rank receives the list of all ranks' tensors; shapes may differ per rank in any dimension."""
+    if group is None:
+        group = dist.group.WORLD
+    result = result.contiguous()
+    world_size = dist.get_world_size(group)
+    if result.ndim == 0:
+        return _simple_gather_all_tensors(result, group, world_size)
+    local_size = torch.tensor(result.shape, device=result.device)
+    sizes = [torch.zeros_like(local_size) for _ in range(world_size)]
+    dist.all_gather(sizes, local_size, group=group)
+    sizes_cpu = torch.stack(sizes).cpu()
+    max_size = sizes_cpu.max(dim=0).values
+    if bool((sizes_cpu == max_size).all()):
+        return _simple_gather_all_tensors(result, group, world_size)
+    pad = []
+    for need in reversed((max_size - sizes_cpu.new_tensor(result.shape)).tolist()):
+        pad += [0, int(need)]
+    padded = F.pad(result, pad)
+    gathered = [torch.zeros_like(padded) for _ in range(world_size)]
+    dist.all_gather(gathered, padded, group)
+    out = []
+    for r, t in enumerate(gathered):
+        out.append(t[tuple(slice(int(d)) for d in sizes_cpu[r].tolist())])
+    return out
+
+
+# -------------------------------------------------------------------------------------------------
+# fused default sync
+# -------------------------------------------------------------------------------------------------
+_REDUCE_OPS = {"sum": dist.ReduceOp.SUM, "mean": dist.ReduceOp.SUM, "max": dist.ReduceOp.MAX, "min": dist.ReduceOp.MIN}
+
+_DTYPE_CODES = [torch.float32, torch.float64, torch.float16, torch.bfloat16, torch.int64, torch.int32, torch.int16,
+                torch.int8, torch.uint8, torch.bool]
+
+
+def fused_reduce(tensors: Sequence[Tuple[str, Tensor]], group: Optional[Any] = None) -> List[Tensor]:
+    """All-reduce several tensors with as few collectives as possible.
+
+    `tensors` is a list of (op, tensor) with op in sum/mean/max/min. Tensors sharing (op class, dtype, device) are
+    packed into one flat arena, reduced in one all_reduce and returned as views of that arena (fresh memory: the
+    inputs are left untouched so `unsync` can restore them).
+    """
+    if group is None:
+        group = dist.group.WORLD
+    world = dist.get_world_size(group)
+    out: List[Optional[Tensor]] = [None] * len(tensors)
+    buckets: Dict[Tuple[Any, torch.dtype, torch.device], List[int]] = {}
+    for i, (op, t) in enumerate(tensors):
+        buckets.setdefault((_REDUCE_OPS[op], t.dtype, t.device), []).append(i)
+    for (rop, dtype, device), idxs in buckets.items():
+        flat = [tensors[i][1].detach().reshape(-1) for i in idxs]
+        arena = torch.cat(flat) if len(flat) > 1 else flat[0].clone()
+        as_bool = dtype == torch.bool
+        if as_bool:
+            arena = arena.to(torch.uint8)
+        dist.all_reduce(arena, op=rop, group=group)
+        off = 0
+        for i in idxs:
+            op, t = tensors[i]
+            piece = arena[off:off + t.numel()].view(t.shape)
+            off += t.numel()
+            if op == "mean":
+                piece = piece / world
+            if as_bool:
+                piece = piece.to(torch.bool)
+            out[i] = piece
+    return out  # type: ignore[return-value]
+
+
+def fused_cat_gather(tensors: Sequence[Optional[Tensor]], group: Optional[Any] = None) -> List[Optional[Tensor]]:
+    """Concatenate every rank's dim-0 slices of several cat states.
+
+    One all_gather of a small int64 descriptor covers ALL states (length along dim 0, trailing shape, dtype), so a
+    rank whose list state is still empty (`None` here) can take part with a matching empty tensor; then one padded
+    `all_gather_into_tensor` per state, trimmed to the true lengths. Returns None for a state empty on every rank.
+    """
+    if group is None:
+        group = dist.group.WORLD
+    world = dist.get_world_size(group)
+    rank_device = None
+    for t in tensors:
+        if t is not None:
+            rank_device = t.device
+            break
+    if rank_device is None:
+        rank_device = _group_device(group)
+    MAXD = 6
+    desc = torch.zeros(len(tensors), MAXD + 3, dtype=torch.int64)
+    for i, t in enumerate(tensors):
+        if t is None:
+            continue
+        if t.ndim - 1 > MAXD:
+            raise ValueError("cat states with more than 7 dimensions are not supported by the fused gather")
+        desc[i, 0] = 1
+        desc[i, 1] = t.shape[0]
+        desc[i, 2] = _DTYPE_CODES.index(t.dtype)
+        desc[i, 3] = t.ndim - 1
+        for d, s in enumerate(t.shape[1:]):
+            desc[i, 4 + d] = s
+    desc = desc.to(rank_device)
+    # output is the dim-0 concatenation of every rank's block (the layout gloo and NCCL both accept)
+    all_desc = torch.empty(world * desc.shape[0], desc.shape[1], dtype=torch.int64, device=rank_device)
+    dist.all_gather_into_tensor(all_desc, desc, group=group)
+    all_desc = all_desc.cpu().view(world, desc.shape[0], desc.shape[1])
+    out: List[Optional[Tensor]] = []
+    for i, t in enumerate(tensors):
+        have = all_desc[:, i, 0].bool()
+        if not bool(have.any()):
+            out.append(None)
+            continue
+        src = int(torch.nonzero(have)[0])
+        dtype = _DTYPE_CODES[int(all_desc[src, i, 2])]
+        trailing = tuple(int(v) for v in all_desc[src, i, 4:4 + int(all_desc[src, i, 3])])
+        lens = [int(all_desc[r, i, 1]) if bool(have[r]) else 0 for r in range(world)]
+        if t is None:
+            t = torch.empty((0, *trailing), dtype=dtype, device=rank_device)
+        t = t.contiguous()
+        max_len = max(lens)
+        if t.shape[0] == max_len:
+            send = t
+        else:
+            send = torch.zeros((max_len, *trailing), dtype=dtype, device=t.device)
+            send[: t.shape[0]] = t
+        recv = torch.empty((world * max_len, *trailing), dtype=dtype, device=t.device)
+        if max_len > 0:
+            dist.all_gather_into_tensor(recv, send, group=group)
+        if all(n == max_len for n in lens):
+            out.append(recv)
+        else:
+            out.append(torch.cat([recv[r * max_len: r * max_len + lens[r]] for r in range(world)], dim=0))
+    return out
+
+
+def _group_device(group: Any) -> torch.device:
+    try:
+        backend = dist.get_backend(group)
+    except Exception:
+        backend = "gloo"
+    if "nccl" in str(backend):
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
