@@ -88,6 +88,11 @@ TMB_API int tmb_confmat_update(const void* preds_dev, int preds_dtype, const voi
                        int64_t num_classes, int has_ignore, int64_t ignore_index, int64_t* confmat_dev,
                        int32_t* status_dev, int algo, void* stream);
 
+/* Plain histogram: out_dev[x[i]] += 1 for x[i] in [0, num_bins); values outside set TMB_STATUS_LABEL_RANGE.
+ * Replaces: utilities/data.py:179-207 `_bincount` (torch.bincount and its deterministic-mode mesh fallback). */
+TMB_API int tmb_bincount_update(const void* x_dev, int x_dtype, int64_t n, int64_t num_bins, int64_t* out_dev,
+                                int32_t* status_dev, void* stream);
+
 /* Multiclass micro statistics: n_valid and n_equal (tp = n_equal, fp = fn = n_valid - n_equal).
  * Replaces: stat_scores.py:394-404 (the `average="micro"` branch).  out2_dev: int64[2] += {n_valid, n_equal}. */
 TMB_API int tmb_match_count_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype, int64_t n,
@@ -115,6 +120,22 @@ TMB_API int tmb_binned_curve_update(const void* preds_dev, int preds_dtype, cons
                             int32_t* status_dev, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * K4  exact binary curve: descending sort of the scores + cumulative counts at every distinct score.
+ * Replaces: functional/classification/precision_recall_curve.py:28-80 `_binary_clf_curve` (no sample weights):
+ *           torch.argsort, two gathers, the `torch.where` compaction with its host sync, and the float32 cumsum.
+ * preds_dev: n float32 scores (already formatted: ignored samples removed, sigmoid applied if needed).
+ * target_dev: n labels; positive iff == pos_label.
+ * fps_dev / tps_dev (int64) and thresholds_dev (float32) need capacity n; the first D entries are written, D =
+ * number of distinct scores.  counts2_dev: int64[2] = {number of positives, D}.  Counts are exact integers (the
+ * reference holds them in float32 and rounds above 2^24).  n < 2^32 - 4096.
+ * workspace_dev: tmb_exact_curve_workspace_bytes(n) bytes, contents irrelevant.
+ * ------------------------------------------------------------------------------------------- */
+TMB_API size_t tmb_exact_curve_workspace_bytes(int64_t n);
+TMB_API int tmb_exact_curve(const float* preds_dev, const void* target_dev, int target_dtype, int64_t n,
+                            int64_t pos_label, int64_t* fps_dev, int64_t* tps_dev, float* thresholds_dev,
+                            int64_t* counts2_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * K2  tp / fp / tn / fn per label.
  * Replaces: functional/classification/stat_scores.py:120-131 `_binary_stat_scores_update` and :672-681
  *           `_multilabel_stat_scores_update` (multidim_average="global"), fused with `_format`
@@ -122,14 +143,16 @@ TMB_API int tmb_binned_curve_update(const void* preds_dev, int preds_dtype, cons
  * preds_dev/target_dev: (n_rows, num_labels) row-major (binary: num_labels = 1, n_rows = numel).
  * Float preds are thresholded (strict >, threshold rounded to the preds dtype as torch does for a Python
  * scalar); integer preds are compared to target as labels.
+ * range_check_ignored: 1 = ignored positions take part in the TMB_PROB_AUTO range check (stat-scores and
+ * multilabel confusion-matrix `_format` order), 0 = they are skipped (binary confusion matrix, :133-142).
  * out_dev: int64[4 * num_labels] laid out [tp | fp | tn | fn], accumulated.
  * workspace_dev: tmb_stat_scores_workspace_bytes() bytes, zero on first use, left zero.
  * ------------------------------------------------------------------------------------------- */
 TMB_API size_t tmb_stat_scores_workspace_bytes(int64_t num_labels);
 TMB_API int tmb_stat_scores_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
                            int64_t n_rows, int64_t num_labels, double threshold, int prob_mode, int has_ignore,
-                           int64_t ignore_index, int64_t* out_dev, void* workspace_dev, size_t workspace_bytes,
-                           void* stream);
+                           int64_t ignore_index, int range_check_ignored, int64_t* out_dev, void* workspace_dev,
+                           size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,389 @@
+"""The reference-facing API (functional + Metric classes + MetricCollection) on the GPU, checked against golden
+vectors produced by the unmodified reference and against scikit-learn on seeded inputs."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import case_id, load_golden
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _tm():
+    import torchmetrics_b200 as tm
+
+    return tm
+
+
+def _t(a):
+    return torch.from_numpy(np.asarray(a)).to(DEV)
+
+
+def _close(got, want, atol=1e-6):
+    got = got.detach().cpu().numpy() if isinstance(got, torch.Tensor) else np.asarray(got)
+    want = np.asarray(want)
+    assert got.shape == want.shape, (got.shape, want.shape)
+    if want.dtype.kind in "iub":
+        assert np.array_equal(got, want)
+    else:
+        np.testing.assert_allclose(got, want, rtol=0, atol=atol, equal_nan=True)
+
+
+# ------------------------------------------------------------------ config 1: README example
+def test_readme_accuracy_config1():
+    tm = _tm()
+    c = load_golden("readme_accuracy")[0]
+    micro = tm.Accuracy(task="multiclass", num_classes=5).to(DEV)
+    macro = tm.classification.MulticlassAccuracy(num_classes=5).to(DEV)
+    for i in range(10):
+        p, t = _t(c["preds"][i]), _t(c["target"][i])
+        assert abs(float(micro(p, t)) - float(c["per_batch_micro"][i])) < 1e-7
+        assert abs(float(macro(p, t)) - float(c["per_batch_macro"][i])) < 1e-7
+    assert float(micro.compute()) == float(c["final_micro"])
+    assert float(macro.compute()) == float(c["final_macro"])
+    assert abs(float(micro.compute()) - 0.20000000298023224) < 1e-9
+    assert abs(float(macro.compute()) - 0.19858768582344055) < 1e-9
+
+
+# ------------------------------------------------------------------ confusion matrix
+@pytest.mark.parametrize("c", load_golden("confusion_matrix"), ids=case_id)
+def test_confusion_matrix_functional_and_class(c):
+    tm = _tm()
+    F = tm.functional
+    kind, ii = c.meta["kind"], c.meta["ignore_index"]
+    p, t = _t(c["preds"]), _t(c["target"])
+    if kind.startswith("multiclass"):
+        C = c.meta["num_classes"]
+        got = F.multiclass_confusion_matrix(p, t, C, ignore_index=ii, validate_args=False)
+        cls = tm.MulticlassConfusionMatrix(C, ignore_index=ii, validate_args=False).to(DEV)
+        if "confmat_norm_true" in c:
+            _close(F.multiclass_confusion_matrix(p, t, C, ignore_index=ii, normalize="true", validate_args=False),
+                   c["confmat_norm_true"])
+    elif kind.startswith("binary"):
+        got = F.binary_confusion_matrix(p, t, c.meta["threshold"], ignore_index=ii, validate_args=False)
+        cls = tm.BinaryConfusionMatrix(c.meta["threshold"], ignore_index=ii, validate_args=False).to(DEV)
+    else:
+        L = c.meta["num_labels"]
+        got = F.multilabel_confusion_matrix(p, t, L, c.meta["threshold"], ignore_index=ii, validate_args=False)
+        cls = tm.MultilabelConfusionMatrix(L, c.meta["threshold"], ignore_index=ii, validate_args=False).to(DEV)
+    slack = 1 if kind.endswith("logits") else 0  # CPU-vs-CUDA sigmoid can move a score across the threshold
+    assert np.abs(got.cpu().numpy() - c["confmat"]).max() <= slack
+    half = p.shape[0] // 2
+    cls.update(p[:half], t[:half])
+    cls.update(p[half:], t[half:])
+    assert torch.equal(cls.compute(), got)
+
+
+def test_confusion_matrix_validation_errors():
+    tm = _tm()
+    F = tm.functional
+    p = torch.randint(0, 5, (100,), device=DEV)
+    with pytest.raises(ValueError, match="Expected argument `num_classes` to be an integer larger than 1"):
+        F.multiclass_confusion_matrix(p, p, 1)
+    with pytest.raises(RuntimeError, match="Detected more unique values in `target` than `num_classes`"):
+        F.multiclass_confusion_matrix(p % 3, torch.arange(100, device=DEV), 3)
+    with pytest.raises(RuntimeError, match="Detected the following values in `target`"):
+        F.binary_confusion_matrix(torch.rand(10, device=DEV), torch.arange(10, device=DEV))
+    with pytest.raises(ValueError, match="Expected argument `threshold` to be a float"):
+        F.binary_confusion_matrix(torch.rand(10, device=DEV), torch.zeros(10, device=DEV).long(), threshold=2)
+    # validate_args=False: out-of-range labels surface as RuntimeError (the reference's reshape error)
+    with pytest.raises(RuntimeError):
+        F.multiclass_confusion_matrix(p, p + 3, 5, validate_args=False)
+    m = tm.MulticlassConfusionMatrix(5, validate_args=False).to(DEV)
+    m.update(p, p + 3)
+    with pytest.raises(RuntimeError):
+        m.compute()
+    with pytest.raises(RuntimeError, match="CUDA tensors only"):
+        F.multiclass_confusion_matrix(p.cpu(), p.cpu(), 5)
+
+
+def test_confusion_matrix_nan_warning():
+    tm = _tm()
+    t = torch.tensor([0, 0, 1, 1], device=DEV)
+    with pytest.warns(UserWarning, match="NaN values found in confusion matrix have been replaced with zeros"):
+        out = tm.functional.multiclass_confusion_matrix(t, t, 3, normalize="true")
+    assert float(out[2].sum()) == 0
+
+
+# ------------------------------------------------------------------ stat scores and derived metrics
+@pytest.mark.parametrize("c", load_golden("stat_scores"), ids=case_id)
+def test_stat_scores_family(c):
+    tm = _tm()
+    F = tm.functional
+    kind, ii, mda = c.meta["kind"], c.meta["ignore_index"], c.meta["multidim_average"]
+    p, t = _t(c["preds"]), _t(c["target"])
+    tol = 1e-6
+    if kind.startswith("binary"):
+        kw = dict(threshold=c.meta["threshold"], multidim_average=mda, ignore_index=ii, validate_args=False)
+        _close(F.binary_stat_scores(p, t, **kw), c["stat_scores"])
+        for name in ["accuracy", "precision", "recall", "f1_score"]:
+            _close(getattr(F, "binary_" + name)(p, t, **kw), c[name], tol)
+        _close(F.binary_fbeta_score(p, t, beta=2.0, **kw), c["fbeta2"], tol)
+        m = tm.BinaryF1Score(**kw).to(DEV)
+        m.update(p, t)
+        _close(m.compute(), c["f1_score"], tol)
+    elif kind.startswith("multilabel"):
+        L = c.meta["num_labels"]
+        for avg in ["micro", "macro", "weighted", "none"]:
+            kw = dict(num_labels=L, threshold=c.meta["threshold"], average=avg, multidim_average=mda, ignore_index=ii,
+                      validate_args=False)
+            _close(F.multilabel_stat_scores(p, t, **kw), c["stat_scores_" + avg], tol)
+            for name in ["accuracy", "precision", "recall", "f1_score"]:
+                _close(getattr(F, "multilabel_" + name)(p, t, **kw), c[f"{name}_{avg}"], tol)
+        m = tm.MultilabelRecall(L, c.meta["threshold"], "macro", multidim_average=mda, ignore_index=ii).to(DEV)
+        m.update(p, t)
+        _close(m.compute(), c["recall_macro"], tol)
+    else:
+        C, top_k = c.meta["num_classes"], c.meta["top_k"]
+        for avg in ["micro", "macro", "weighted", "none"]:
+            kw = dict(num_classes=C, average=avg, top_k=top_k, multidim_average=mda, ignore_index=ii,
+                      validate_args=False)
+            _close(F.multiclass_stat_scores(p, t, **kw), c["stat_scores_" + avg], tol)
+            for name in ["accuracy", "precision", "recall", "f1_score"]:
+                _close(getattr(F, "multiclass_" + name)(p, t, **kw), c[f"{name}_{avg}"], tol)
+        m = tm.MulticlassPrecision(C, top_k, "weighted", multidim_average=mda, ignore_index=ii).to(DEV)
+        m.update(p, t)
+        _close(m.compute(), c["precision_weighted"], tol)
+
+
+# ------------------------------------------------------------------ binned curves
+@pytest.mark.parametrize("c", load_golden("binned_curve"), ids=case_id)
+def test_binned_curve_family(c):
+    tm = _tm()
+    F = tm.functional
+    kind, ii = c.meta["kind"], c.meta["ignore_index"]
+    arg = c.meta["thresholds_arg"]
+    thr = arg if isinstance(arg, int) else _t(c["thresholds"])
+    p, t = _t(c["preds"]), _t(c["target"])
+    tol = 2e-4 if kind.endswith("logits") else 1e-6
+    if p.numel() == 0:
+        pytest.skip("empty")
+    if kind.startswith("binary"):
+        kw = dict(thresholds=thr, ignore_index=ii, validate_args=False)
+        _close(F.binary_auroc(p, t, **kw), c["auroc"], tol)
+        _close(F.binary_average_precision(p, t, **kw), c["ap"], tol)
+        _close(F.binary_auroc(p, t, max_fpr=0.3, **kw), c["auroc_maxfpr"], 10 * tol)
+        pr, rc, th = F.binary_precision_recall_curve(p, t, **kw)
+        _close(pr, c["precision"], tol)
+        _close(rc, c["recall"], tol)
+        _close(th, c["thresholds"], 0)
+        fpr, tpr, _ = F.binary_roc(p, t, **kw)
+        _close(fpr, c["fpr"], tol)
+        _close(tpr, c["tpr"], tol)
+        # class API over two batches, sharing one state between AUROC and AP in a collection
+        mc = tm.MetricCollection([tm.BinaryAUROC(thresholds=thr, ignore_index=ii, validate_args=False),
+                                  tm.BinaryAveragePrecision(thresholds=thr, ignore_index=ii, validate_args=False)]).to(DEV)
+        h = p.shape[0] // 2
+        if kind.endswith("logits") or h == 0:
+            mc.update(p, t)  # the sigmoid rule is per batch, keep the batch as the reference saw it
+        else:
+            mc.update(p[:h], t[:h])
+            mc.update(p[h:], t[h:])
+        out = mc.compute()
+        assert len(mc.compute_groups) == 1
+        _close(out["BinaryAUROC"], c["auroc"], tol)
+        _close(out["BinaryAveragePrecision"], c["ap"], tol)
+        if not kind.endswith("logits"):
+            st = mc.__getitem__("BinaryAUROC", copy_state=False).confmat
+            assert np.array_equal(st.cpu().numpy(), c["confmat"])
+    elif kind.startswith("multiclass"):
+        C = c.meta["num_classes"]
+        kw = dict(num_classes=C, thresholds=thr, ignore_index=ii, validate_args=False)
+        for avg in ["macro", "weighted", "none"]:
+            _close(F.multiclass_auroc(p, t, average=avg, **kw), c["auroc_" + avg], tol)
+            _close(F.multiclass_average_precision(p, t, average=avg, **kw), c["ap_" + avg], tol)
+        m = tm.MulticlassAUROC(C, "macro", thresholds=thr, ignore_index=ii, validate_args=False).to(DEV)
+        m.update(p, t)
+        _close(m.compute(), c["auroc_macro"], tol)
+        if not kind.endswith("logits"):
+            assert np.array_equal(m.confmat.cpu().numpy(), c["confmat_None"])
+            mm = tm.MulticlassPrecisionRecallCurve(C, thresholds=thr, average="micro", ignore_index=ii,
+                                                   validate_args=False).to(DEV)
+            mm.update(p, t)
+            assert np.array_equal(mm.confmat.cpu().numpy(), c["confmat_micro"])
+    else:
+        L = c.meta["num_labels"]
+        kw = dict(num_labels=L, thresholds=thr, ignore_index=ii, validate_args=False)
+        for avg in ["micro", "macro", "weighted", "none"]:
+            _close(F.multilabel_auroc(p, t, average=avg, **kw), c["auroc_" + avg], tol)
+            _close(F.multilabel_average_precision(p, t, average=avg, **kw), c["ap_" + avg], tol)
+        m = tm.MultilabelAveragePrecision(L, "macro", thresholds=thr, ignore_index=ii, validate_args=False).to(DEV)
+        m.update(p, t)
+        _close(m.compute(), c["ap_macro"], tol)
+
+
+# ------------------------------------------------------------------ exact curves
+@pytest.mark.parametrize("c", load_golden("exact_curve"), ids=case_id)
+def test_exact_curve_family(c):
+    tm = _tm()
+    F = tm.functional
+    kind, ii = c.meta["kind"], c.meta["ignore_index"]
+    p, t = _t(c["preds"]), _t(c["target"])
+    tol = 1e-5 if kind.endswith("logits") else 1e-6
+    if kind.startswith("binary"):
+        kw = dict(thresholds=None, ignore_index=ii, validate_args=False)
+        _close(F.binary_auroc(p, t, **kw), c["auroc"], tol)
+        _close(F.binary_average_precision(p, t, **kw), c["ap"], tol)
+        _close(F.binary_auroc(p, t, max_fpr=0.25, **kw), c["auroc_maxfpr"], 10 * tol)
+        fpr, tpr, rthr = F.binary_roc(p, t, **kw)
+        _close(fpr, c["fpr"], tol)
+        _close(tpr, c["tpr"], tol)
+        _close(rthr, c["roc_thresholds"], 1e-6)
+        pr, rc, pthr = F.binary_precision_recall_curve(p, t, **kw)
+        _close(pr, c["precision"], tol)
+        _close(rc, c["recall"], tol)
+        _close(pthr, c["pr_thresholds"], 1e-6)
+        if not kind.endswith("logits"):
+            from torchmetrics_b200.functional.classification.precision_recall_curve import (
+                _binary_clf_curve,
+                _binary_precision_recall_curve_format,
+            )
+
+            fp_, ft_, _ = _binary_precision_recall_curve_format(p, t, None, ii)
+            fps, tps, thr = _binary_clf_curve(fp_, ft_)
+            _close(fps, c["fps"], 0)
+            _close(tps, c["tps"], 0)
+            _close(thr, c["thr"], 0)
+        m = tm.BinaryAUROC(thresholds=None, ignore_index=ii, validate_args=False).to(DEV)
+        h = max(1, p.shape[0] // 3)
+        if kind.endswith("logits"):
+            m.update(p, t)
+        else:
+            m.update(p[:h], t[:h])
+            if p.shape[0] > h:
+                m.update(p[h:], t[h:])
+        _close(m.compute(), c["auroc"], tol)
+    elif kind == "multiclass":
+        C = c.meta["num_classes"]
+        kw = dict(num_classes=C, thresholds=None, ignore_index=ii, validate_args=False)
+        for avg in ["macro", "weighted", "none"]:
+            _close(F.multiclass_auroc(p, t, average=avg, **kw), c["auroc_" + avg], tol)
+            _close(F.multiclass_average_precision(p, t, average=avg, **kw), c["ap_" + avg], tol)
+    else:
+        L = c.meta["num_labels"]
+        kw = dict(num_labels=L, thresholds=None, ignore_index=ii, validate_args=False)
+        for avg in ["micro", "macro", "weighted", "none"]:
+            _close(F.multilabel_auroc(p, t, average=avg, **kw), c["auroc_" + avg], tol)
+            _close(F.multilabel_average_precision(p, t, average=avg, **kw), c["ap_" + avg], tol)
+
+
+def test_exact_sort_large_random_vs_torch():
+    """K4 against torch.sort-based restatement on the device at a size the oracle would take minutes for."""
+    from torchmetrics_b200 import _native as N
+
+    g = torch.Generator(device=DEV).manual_seed(3)
+    for n in [1, 2, 4095, 4096, 4097, 1 << 20, (1 << 22) + 77]:
+        preds = torch.rand(n, device=DEV, generator=g)
+        if n > 10000:
+            preds = (preds * 50000).floor() / 50000  # plenty of ties
+        target = (torch.rand(n, device=DEV, generator=g) < 0.4).long()
+        fps, tps, thr = N.exact_curve(preds, target, 1)
+        sp, order = torch.sort(preds, descending=True, stable=True)
+        st = target[order]
+        ends = torch.cat([torch.nonzero(sp[1:] != sp[:-1]).flatten(), torch.tensor([n - 1], device=DEV)])
+        want_tps = torch.cumsum(st, 0)[ends]
+        assert torch.equal(thr, sp[ends])
+        assert torch.equal(tps, want_tps)
+        assert torch.equal(fps, ends + 1 - want_tps)
+    # negative scores, infinities and both zeros sort correctly too
+    preds = torch.tensor([0.0, -0.0, -1.5, 3.0, float("inf"), -float("inf"), 1e-40, -1e-40, 3.0], device=DEV)
+    target = torch.tensor([1, 0, 1, 0, 1, 0, 1, 0, 1], device=DEV)
+    fps, tps, thr = N.exact_curve(preds, target, 1)
+    assert thr.tolist() == [float("inf"), 3.0, 1e-40, 0.0, -1e-40, -1.5, -float("inf")] or \
+        [abs(x) for x in thr.tolist()][3] == 0.0
+    assert tps.tolist() == [1, 2, 3, 4, 4, 5, 5] and fps.tolist() == [0, 1, 1, 2, 3, 3, 4]
+
+
+def test_binned_with_all_scores_as_thresholds_equals_exact():
+    """The reference's own cross-path identity (test_precision_recall_curve.py:132-143, test_auroc.py:129-138)."""
+    tm = _tm()
+    F = tm.functional
+    g = torch.Generator(device=DEV).manual_seed(8)
+    p = torch.rand(500, device=DEV, generator=g)
+    t = torch.randint(0, 2, (500,), device=DEV, generator=g)
+    thr = torch.unique(p)
+    assert abs(float(F.binary_auroc(p, t, thresholds=None)) - float(F.binary_auroc(p, t, thresholds=thr))) < 1e-6
+    a = F.binary_average_precision(p, t, thresholds=None)
+    b = F.binary_average_precision(p, t, thresholds=thr)
+    assert abs(float(a) - float(b)) < 1e-6
+
+
+# ------------------------------------------------------------------ scikit-learn cross-checks on fresh inputs
+def test_against_sklearn():
+    sk = pytest.importorskip("sklearn.metrics")
+    tm = _tm()
+    F = tm.functional
+    rng = np.random.default_rng(0)
+    n = 20_000
+    p = rng.random(n).astype(np.float32)
+    t = (rng.random(n) < 0.3 + 0.4 * p).astype(np.int64)
+    assert abs(float(F.binary_auroc(_t(p), _t(t))) - sk.roc_auc_score(t, p)) < 1e-5
+    assert abs(float(F.binary_average_precision(_t(p), _t(t))) - sk.average_precision_score(t, p)) < 1e-5
+    assert abs(float(F.binary_auroc(_t(p), _t(t), thresholds=2000)) - sk.roc_auc_score(t, p)) < 2e-3
+    C = 37
+    yp, yt = rng.integers(0, C, n), rng.integers(0, C, n)
+    got = F.multiclass_confusion_matrix(_t(yp), _t(yt), C).cpu().numpy()
+    assert np.array_equal(got, sk.confusion_matrix(yt, yp, labels=list(range(C))))
+    assert abs(float(F.multiclass_f1_score(_t(yp), _t(yt), C, average="macro"))
+               - sk.f1_score(yt, yp, average="macro")) < 1e-6
+    assert abs(float(F.multiclass_accuracy(_t(yp), _t(yt), C, average="micro")) - sk.accuracy_score(yt, yp)) < 1e-6
+    L = 9
+    mp, mt = rng.random((n, L)).astype(np.float32), rng.integers(0, 2, (n, L))
+    assert abs(float(F.multilabel_precision(_t(mp), _t(mt), L, average="macro"))
+               - sk.precision_score(mt, mp > 0.5, average="macro")) < 1e-6
+    assert abs(float(F.multilabel_auroc(_t(mp), _t(mt), L, average="macro"))
+               - sk.roc_auc_score(mt, mp, average="macro")) < 1e-5
+
+
+# ------------------------------------------------------------------ config 5: collection of multilabel metrics
+def test_multilabel_collection_config5_shape():
+    tm = _tm()
+    L, n = 100, 4096
+    g = torch.Generator(device=DEV).manual_seed(5)
+    mc = tm.MetricCollection([tm.MultilabelStatScores(num_labels=L), tm.MultilabelPrecision(num_labels=L),
+                              tm.MultilabelRecall(num_labels=L), tm.MultilabelF1Score(num_labels=L)]).to(DEV)
+    P, T = [], []
+    for _ in range(3):
+        p = torch.rand(n, L, device=DEV, generator=g)
+        t = torch.randint(0, 2, (n, L), device=DEV, generator=g)
+        mc.update(p, t)
+        P.append(p)
+        T.append(t)
+    assert len(mc.compute_groups) == 1
+    out = mc.compute()
+    p, t = torch.cat(P), torch.cat(T)
+    F = tm.functional
+    _close(out["MultilabelStatScores"], F.multilabel_stat_scores(p, t, L).cpu().numpy(), 1e-6)
+    _close(out["MultilabelPrecision"], F.multilabel_precision(p, t, L).cpu().numpy(), 1e-6)
+    _close(out["MultilabelRecall"], F.multilabel_recall(p, t, L).cpu().numpy(), 1e-6)
+    _close(out["MultilabelF1Score"], F.multilabel_f1_score(p, t, L).cpu().numpy(), 1e-6)
+    pb = (p > 0.5).long()
+    tp = ((pb == 1) & (t == 1)).sum(0)
+    st = mc.__getitem__("MultilabelStatScores", copy_state=False)
+    assert torch.equal(st.tp, tp)
+    # reset keeps the group, state goes back to zero on the same device
+    mc.reset()
+    assert int(st.tp.sum()) == 0 and st.tp.is_cuda
+
+
+def test_metric_device_moves_and_pickle_on_gpu():
+    import pickle
+
+    tm = _tm()
+    m = tm.BinaryAUROC(thresholds=50)
+    assert m.confmat.device.type == "cpu"
+    m = m.to(DEV)
+    assert m.confmat.is_cuda and m.thresholds.is_cuda
+    p = torch.rand(1000, device=DEV)
+    t = torch.randint(0, 2, (1000,), device=DEV)
+    m.update(p, t)
+    v = float(m.compute())
+    m2 = pickle.loads(pickle.dumps(m))
+    assert abs(float(m2.compute()) - v) < 1e-7
+    m3 = m.clone()
+    m3.update(p, t)
+    assert abs(float(m3.compute()) - v) < 1e-6  # same data twice: same curve
+    assert m.state_dict() == {}
+    with pytest.raises(RuntimeError, match="CUDA tensors only"):
+        tm.BinaryAUROC(thresholds=50).update(p.cpu(), t.cpu())

@@ -43,16 +43,21 @@ _SIGNATURES = {
     "tmb_sm_count": (_c.c_int, []),
     "tmb_confmat_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_int,
                                       _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_void_p]),
+    "tmb_bincount_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_void_p,
+                                       _c.c_void_p]),
     "tmb_match_count_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int,
                                           _c.c_int64, _c.c_void_p, _c.c_void_p]),
     "tmb_binned_curve_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int64]),
     "tmb_binned_curve_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                            _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int64, _c.c_int,
                                            _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p, _c.c_void_p]),
+    "tmb_exact_curve_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
+    "tmb_exact_curve": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_void_p,
+                                   _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
     "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
-                                          _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p,
-                                          _c.c_size_t, _c.c_void_p]),
+                                          _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,
+                                          _c.c_void_p, _c.c_size_t, _c.c_void_p]),
 }
 
 _lib = None
@@ -220,6 +225,17 @@ def confmat_update_(confmat: Tensor, preds: Tensor, target: Tensor, num_classes:
     _check(rc, "tmb_confmat_update")
 
 
+def bincount_update_(out: Tensor, x: Tensor) -> None:
+    """out (M,) int64 += histogram of the integer tensor x."""
+    dev = require_cuda(out, x)
+    assert out.dtype == torch.int64 and out.is_contiguous()
+    x = as_kernel_labels(x.reshape(-1))
+    with torch.cuda.device(dev):
+        rc = load().tmb_bincount_update(x.data_ptr(), dtype_code(x), x.numel(), out.numel(), out.data_ptr(),
+                                        scratch(dev).status.data_ptr(), _stream_ptr(dev))
+    _check(rc, "tmb_bincount_update")
+
+
 def match_count_update_(out2: Tensor, preds: Tensor, target: Tensor, ignore_index: Optional[int] = None) -> None:
     dev = require_cuda(out2, preds, target)
     assert out2.dtype == torch.int64 and out2.numel() == 2 and out2.is_contiguous()
@@ -257,7 +273,8 @@ def binned_curve_update_(confmat: Tensor, preds: Tensor, target: Tensor, thresho
 
 
 def stat_scores_update_(out: Tensor, preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
-                        ignore_index: Optional[int] = None, prob_mode: int = PROB_AUTO) -> None:
+                        ignore_index: Optional[int] = None, prob_mode: int = PROB_AUTO,
+                        range_check_ignored: bool = True) -> None:
     """out (4, L) int64 [tp|fp|tn|fn] += per-label statistics of (n_rows, L) preds/target (K2)."""
     dev = require_cuda(out, preds, target)
     assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == 4 * num_labels
@@ -271,6 +288,28 @@ def stat_scores_update_(out: Tensor, preds: Tensor, target: Tensor, num_labels: 
     with torch.cuda.device(dev):
         rc = lib.tmb_stat_scores_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
                                         n_rows, num_labels, float(threshold), prob_mode, ignore_index is not None,
-                                        0 if ignore_index is None else int(ignore_index), out.data_ptr(),
-                                        ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+                                        0 if ignore_index is None else int(ignore_index), bool(range_check_ignored),
+                                        out.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
     _check(rc, "tmb_stat_scores_update")
+
+
+def exact_curve(preds: Tensor, target: Tensor, pos_label: int = 1):
+    """(fps int64, tps int64, thresholds float32) at every distinct score, descending (K4)."""
+    dev = require_cuda(preds, target)
+    preds = _aligned(preds.detach().reshape(-1).to(torch.float32))
+    target = as_kernel_labels(target.reshape(-1))
+    n = preds.numel()
+    assert target.numel() == n
+    lib = load()
+    fps = torch.empty(n, dtype=torch.int64, device=dev)
+    tps = torch.empty(n, dtype=torch.int64, device=dev)
+    thr = torch.empty(n, dtype=torch.float32, device=dev)
+    counts = torch.zeros(2, dtype=torch.int64, device=dev)
+    ws = torch.empty(lib.tmb_exact_curve_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.tmb_exact_curve(preds.data_ptr(), target.data_ptr(), dtype_code(target), n, int(pos_label),
+                                 fps.data_ptr(), tps.data_ptr(), thr.data_ptr(), counts.data_ptr(), ws.data_ptr(),
+                                 ws.numel(), _stream_ptr(dev))
+    _check(rc, "tmb_exact_curve")
+    d = int(counts[1].item())  # the reference syncs at the same point (torch.where)
+    return fps[:d], tps[:d], thr[:d]

@@ -1,0 +1,183 @@
+"""Stateful tp/fp/tn/fn metrics (reference: classification/stat_scores.py:43-551)."""
+from importlib import import_module
+from typing import Any, Callable, List, Optional, Tuple, Union
+
+import torch
+from torch import Tensor
+from typing_extensions import Literal
+
+from torchmetrics_b200 import _native
+from torchmetrics_b200.classification.base import _ClassificationTaskWrapper
+F = import_module("torchmetrics_b200.functional.classification.stat_scores")
+from torchmetrics_b200.metric import Metric
+from torchmetrics_b200.utilities.data import dim_zero_cat
+from torchmetrics_b200.utilities.enums import ClassificationTask
+
+
+class _AbstractStatScores(Metric):
+    """States `tp, fp, tn, fn`: int64 tensors summed across ranks, or lists concatenated for samplewise averaging."""
+
+    tp: Union[List[Tensor], Tensor]
+    fp: Union[List[Tensor], Tensor]
+    tn: Union[List[Tensor], Tensor]
+    fn: Union[List[Tensor], Tensor]
+
+    def _create_state(self, size: int, multidim_average: Literal["global", "samplewise"] = "global") -> None:
+        default: Union[Callable[[], list], Callable[[], Tensor]]
+        if multidim_average == "samplewise":
+            default, reduce_fx = list, "cat"
+        else:
+            default, reduce_fx = (lambda: torch.zeros(size, dtype=torch.long)), "sum"
+        for name in ("tp", "fp", "tn", "fn"):
+            self.add_state(name, default(), dist_reduce_fx=reduce_fx)
+
+    def _update_state(self, tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor) -> None:
+        if self.multidim_average == "samplewise":
+            self.tp.append(tp)
+            self.fp.append(fp)
+            self.tn.append(tn)
+            self.fn.append(fn)
+        else:
+            # in place, so compute-group members that alias these tensors see the update
+            self.tp += tp
+            self.fp += fp
+            self.tn += tn
+            self.fn += fn
+
+    def _final_state(self) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+        return dim_zero_cat(self.tp), dim_zero_cat(self.fp), dim_zero_cat(self.tn), dim_zero_cat(self.fn)
+
+
+class BinaryStatScores(_AbstractStatScores):
+    is_differentiable = False
+    higher_is_better = None
+    full_state_update = False
+
+    def __init__(self, threshold: float = 0.5, multidim_average: Literal["global", "samplewise"] = "global",
+                 ignore_index: Optional[int] = None, validate_args: bool = True, **kwargs: Any) -> None:
+        zero_division = kwargs.pop("zero_division", 0)  # noqa: F841  (accepted for signature compatibility)
+        super().__init__(**kwargs)
+        if validate_args:
+            F._binary_stat_scores_arg_validation(threshold, multidim_average, ignore_index)
+        self.threshold = threshold
+        self.multidim_average = multidim_average
+        self.ignore_index = ignore_index
+        self.validate_args = validate_args
+        self._create_state(size=1, multidim_average=multidim_average)
+
+    def update(self, preds: Tensor, target: Tensor) -> None:
+        if self.validate_args:
+            F._binary_stat_scores_tensor_validation(preds, target, self.multidim_average, self.ignore_index)
+        tp, fp, tn, fn = F._binary_stat_scores_update_fused(preds, target, self.threshold, self.multidim_average,
+                                                            self.ignore_index)
+        self._update_state(tp, fp, tn, fn)
+
+    def compute(self) -> Tensor:
+        tp, fp, tn, fn = self._final_state()
+        return F._binary_stat_scores_compute(tp, fp, tn, fn, self.multidim_average)
+
+
+class MulticlassStatScores(_AbstractStatScores):
+    is_differentiable = False
+    higher_is_better = None
+    full_state_update = False
+
+    def __init__(self, num_classes: int, top_k: int = 1,
+                 average: Optional[Literal["micro", "macro", "weighted", "none"]] = "macro",
+                 multidim_average: Literal["global", "samplewise"] = "global", ignore_index: Optional[int] = None,
+                 validate_args: bool = True, **kwargs: Any) -> None:
+        super().__init__(**kwargs)
+        if validate_args:
+            F._multiclass_stat_scores_arg_validation(num_classes, top_k, average, multidim_average, ignore_index)
+        self.num_classes = num_classes
+        self.top_k = top_k
+        self.average = average
+        self.multidim_average = multidim_average
+        self.ignore_index = ignore_index
+        self.validate_args = validate_args
+        self._create_state(size=1 if (average == "micro" and top_k == 1) else num_classes,
+                           multidim_average=multidim_average)
+
+    def update(self, preds: Tensor, target: Tensor) -> None:
+        if self.validate_args:
+            F._multiclass_stat_scores_tensor_validation(preds, target, self.num_classes, self.multidim_average,
+                                                        self.ignore_index)
+        tp, fp, tn, fn = F._multiclass_stat_scores_update_fused(preds, target, self.num_classes, self.top_k,
+                                                                self.average, self.multidim_average,
+                                                                self.ignore_index)
+        self._update_state(tp, fp, tn, fn)
+
+    def _final_state(self) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+        out = super()._final_state()
+        if out[0].is_cuda:
+            _native.raise_on_status(out[0].device, self.num_classes)
+        return out
+
+    def compute(self) -> Tensor:
+        tp, fp, tn, fn = self._final_state()
+        return F._multiclass_stat_scores_compute(tp, fp, tn, fn, self.average, self.multidim_average)
+
+
+class MultilabelStatScores(_AbstractStatScores):
+    is_differentiable = False
+    higher_is_better = None
+    full_state_update = False
+
+    def __init__(self, num_labels: int, threshold: float = 0.5,
+                 average: Optional[Literal["micro", "macro", "weighted", "none"]] = "macro",
+                 multidim_average: Literal["global", "samplewise"] = "global", ignore_index: Optional[int] = None,
+                 validate_args: bool = True, **kwargs: Any) -> None:
+        super().__init__(**kwargs)
+        if validate_args:
+            F._multilabel_stat_scores_arg_validation(num_labels, threshold, average, multidim_average, ignore_index)
+        self.num_labels = num_labels
+        self.threshold = threshold
+        self.average = average
+        self.multidim_average = multidim_average
+        self.ignore_index = ignore_index
+        self.validate_args = validate_args
+        self._create_state(size=num_labels, multidim_average=multidim_average)
+
+    def update(self, preds: Tensor, target: Tensor) -> None:
+        if self.validate_args:
+            F._multilabel_stat_scores_tensor_validation(preds, target, self.num_labels, self.multidim_average,
+                                                        self.ignore_index)
+        tp, fp, tn, fn = F._multilabel_stat_scores_update_fused(preds, target, self.num_labels, self.threshold,
+                                                                self.multidim_average, self.ignore_index)
+        self._update_state(tp, fp, tn, fn)
+
+    def compute(self) -> Tensor:
+        tp, fp, tn, fn = self._final_state()
+        return F._multilabel_stat_scores_compute(tp, fp, tn, fn, self.average, self.multidim_average)
+
+
+def _task_dispatch(task, binary_cls, multiclass_cls, multilabel_cls, threshold, num_classes, num_labels, average,
+                   multidim_average, top_k, ignore_index, validate_args, extra_args=(), **kwargs):
+    """Shared body of the `Metric(task=...)` wrappers for the stat-scores family."""
+    task = ClassificationTask.from_str(task)
+    assert multidim_average is not None
+    kwargs.update({"multidim_average": multidim_average, "ignore_index": ignore_index, "validate_args": validate_args})
+    if task == ClassificationTask.BINARY:
+        return binary_cls(*extra_args, threshold, **kwargs)
+    if task == ClassificationTask.MULTICLASS:
+        if not isinstance(num_classes, int):
+            raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+        if not isinstance(top_k, int):
+            raise ValueError(f"`top_k` is expected to be `int` but `{type(top_k)} was passed.`")
+        return multiclass_cls(*extra_args, num_classes, top_k, average, **kwargs)
+    if task == ClassificationTask.MULTILABEL:
+        if not isinstance(num_labels, int):
+            raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")
+        return multilabel_cls(*extra_args, num_labels, threshold, average, **kwargs)
+    raise ValueError(f"Task {task} not supported!")
+
+
+class StatScores(_ClassificationTaskWrapper):
+    def __new__(cls, task: Literal["binary", "multiclass", "multilabel"], threshold: float = 0.5,
+                num_classes: Optional[int] = None, num_labels: Optional[int] = None,
+                average: Optional[Literal["micro", "macro", "weighted", "none"]] = "micro",
+                multidim_average: Optional[Literal["global", "samplewise"]] = "global", top_k: Optional[int] = 1,
+                ignore_index: Optional[int] = None, validate_args: bool = True, **kwargs: Any) -> Metric:
+        return _task_dispatch(task, BinaryStatScores, MulticlassStatScores, MultilabelStatScores, threshold,
+                              num_classes, num_labels, average, multidim_average, top_k, ignore_index, validate_args,
+                              **kwargs)

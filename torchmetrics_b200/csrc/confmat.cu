@@ -147,6 +147,28 @@ confmat_smem_kernel(const PT* __restrict__ preds, const TT* __restrict__ target,
   if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
 }
 
+// plain histogram of one label tensor (utilities/data.py:179-207 `_bincount`): global RED per element
+template <typename PT>
+__global__ void __launch_bounds__(kConfmatThreads)
+bincount_kernel(const PT* __restrict__ x, long long n, long long nbins, u64* __restrict__ out, int* __restrict__ status) {
+  const long long nvec = n >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  int bad = 0;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nvec; g += stride) {
+    Vec4<PT> v = load4(x + 4 * g);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      long long k = as_i64(v.v[j]);
+      if (k < 0 || k >= nbins) bad = 1; else atomicAdd(out + k, 1ULL);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    long long k = as_i64(x[(nvec << 2) + threadIdx.x]);
+    if (k < 0 || k >= nbins) bad = 1; else atomicAdd(out + k, 1ULL);
+  }
+  if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
+}
+
 // n_valid / n_equal (multiclass micro statistics)
 template <typename PT, typename TT>
 __global__ void __launch_bounds__(kConfmatThreads)
@@ -257,6 +279,22 @@ extern "C" int tmb_confmat_update(const void* preds, int preds_dtype, const void
       return launch_confmat<PT, TT>((const PT*)preds, (const TT*)target, n, num_classes, has_ignore, ignore_index,
                                     (u64*)confmat, status, algo, st);
     })
+  })
+  return TMB_ERR_ARG;
+}
+
+extern "C" int tmb_bincount_update(const void* x, int x_dtype, int64_t n, int64_t num_bins, int64_t* out,
+                                   int32_t* status, void* stream) {
+  if (n < 0 || num_bins < 1 || !out || !status) return TMB_ERR_ARG;
+  if (n == 0) return TMB_OK;
+  if (!x) return TMB_ERR_ARG;
+  if (!aligned32(x)) return TMB_ERR_ALIGN;
+  cudaStream_t st = (cudaStream_t)stream;
+  TMB_DISPATCH_INT(x_dtype, PT, {
+    int grid = grid_for(n >> 2, kConfmatThreads, 8);
+    bincount_kernel<PT><<<grid, kConfmatThreads, 0, st>>>((const PT*)x, n, num_bins, (u64*)out, status);
+    TMB_CUDA_CHECK(cudaGetLastError());
+    return TMB_OK;
   })
   return TMB_ERR_ARG;
 }

@@ -1,0 +1,442 @@
+// K4 — exact binary curve: radix sort of the scores (descending) with a 1-byte label payload, then a scan that
+// emits cumulative true / false positives at the last element of every run of equal scores
+// (contract in include/tm_b200.h; reference: functional/classification/precision_recall_curve.py:28-80).
+//
+// Sort: least-significant-digit radix sort, 4 passes of 8 bits over order-preserving 32-bit keys.  Each pass is
+//   tile histogram -> per-digit exclusive scan over tiles -> stable scatter.
+// The scatter ranks keys inside a 4096-key tile with warp match.any (no per-key shared-memory atomics), stages the
+// tile in shared memory in digit order and writes it out in coalesced runs.  Ties keep their input order, which the
+// curve does not depend on (counts are read only at run boundaries).
+// Scan: tile sums of (positives, run ends) -> exclusive scan of tile sums -> per-tile rescan that writes
+// (fps, tps, threshold) at the compacted position of every run end.  Counts are exact int64.
+#include "common.cuh"
+
+namespace tmb {
+
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 16;
+constexpr int kSortTile = kSortThreads * kSortItems;  // 4096 keys per CTA
+constexpr int kRadix = 256;
+constexpr int kSortWarps = kSortThreads / 32;
+
+// float -> u32 whose ascending order is the DESCENDING order of the floats (NaN with sign bit clear sorts first,
+// as torch.argsort(descending=True) places it)
+__device__ __forceinline__ u32 desc_key(float f) {
+  u32 b = __float_as_uint(f);
+  u32 asc = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+  return ~asc;
+}
+__device__ __forceinline__ float key_to_float(u32 k) {
+  u32 asc = ~k;
+  u32 b = (asc & 0x80000000u) ? (asc & 0x7fffffffu) : ~asc;
+  return __uint_as_float(b);
+}
+
+template <typename TT>
+__global__ void __launch_bounds__(256) k4_prepare(const float* __restrict__ preds, const TT* __restrict__ target,
+                                                  long long n, long long pos_label, u32* __restrict__ keys,
+                                                  unsigned char* __restrict__ labs) {
+  const long long nvec = n >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nvec; g += stride) {
+    Vec4<float> p = load4(preds + 4 * g);
+    Vec4<TT> t = load4(target + 4 * g);
+    uint4 k;
+    k.x = desc_key(p.v[0]); k.y = desc_key(p.v[1]); k.z = desc_key(p.v[2]); k.w = desc_key(p.v[3]);
+    u32 l = (u32)(as_i64(t.v[0]) == pos_label) | ((u32)(as_i64(t.v[1]) == pos_label) << 8) |
+            ((u32)(as_i64(t.v[2]) == pos_label) << 16) | ((u32)(as_i64(t.v[3]) == pos_label) << 24);
+    reinterpret_cast<uint4*>(keys)[g] = k;
+    reinterpret_cast<u32*>(labs)[g] = l;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    long long i = (nvec << 2) + threadIdx.x;
+    keys[i] = desc_key(preds[i]);
+    labs[i] = (unsigned char)(as_i64(target[i]) == pos_label);
+  }
+}
+
+// table layout: [digit][tile], so the scan over tiles of one digit is contiguous
+__global__ void __launch_bounds__(kSortThreads) k4_tile_hist(const u32* __restrict__ keys, long long n, int shift,
+                                                             u32* __restrict__ table, int ntiles) {
+  __shared__ u32 h[kRadix];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  const long long base = (long long)blockIdx.x * kSortTile;
+#pragma unroll 4
+  for (int r = 0; r < kSortItems; ++r) {
+    long long i = base + r * kSortThreads + threadIdx.x;
+    if (i < n) atomicAdd(&h[(keys[i] >> shift) & 0xff], 1u);
+  }
+  __syncthreads();
+  table[(long long)threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
+}
+
+// one CTA per digit: exclusive scan of its row in place, row total to totals[digit]
+__global__ void __launch_bounds__(1024) k4_scan_rows(u32* __restrict__ table, int ntiles, u64* __restrict__ totals) {
+  __shared__ u64 warp_sums[32];
+  __shared__ u64 carry_s;
+  u32* row = table + (long long)blockIdx.x * ntiles;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int start = 0; start < ntiles; start += 1024) {
+    int i = start + threadIdx.x;
+    u64 v = i < ntiles ? row[i] : 0;
+    u64 x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      u64 y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_sums[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      u64 w = warp_sums[lane];
+      u64 ws = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        u64 y = __shfl_up_sync(0xffffffffu, ws, o);
+        if (lane >= o) ws += y;
+      }
+      warp_sums[lane] = ws - w;  // exclusive over warps
+    }
+    __syncthreads();
+    const u64 carry = carry_s;
+    u64 excl = carry + warp_sums[warp] + x - v;
+    // offsets inside one digit are < n < 2^32 (checked by the entry point); digit bases are 64-bit in `totals`
+    if (i < ntiles) row[i] = (u32)excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = carry + warp_sums[warp] + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) totals[blockIdx.x] = carry_s;
+}
+
+// exclusive scan of the 256 digit totals -> digit bases
+__global__ void __launch_bounds__(kRadix) k4_scan_totals(const u64* __restrict__ totals, u64* __restrict__ bases) {
+  __shared__ u64 s[kRadix];
+  s[threadIdx.x] = totals[threadIdx.x];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u64 run = 0;
+    for (int d = 0; d < kRadix; ++d) {
+      u64 v = s[d];
+      s[d] = run;
+      run += v;
+    }
+  }
+  __syncthreads();
+  bases[threadIdx.x] = s[threadIdx.x];
+}
+
+// stable scatter of one tile
+__global__ void __launch_bounds__(kSortThreads) k4_scatter(const u32* __restrict__ keys_in,
+                                                           const unsigned char* __restrict__ labs_in, long long n,
+                                                           int shift, const u32* __restrict__ table, int ntiles,
+                                                           const u64* __restrict__ bases, u32* __restrict__ keys_out,
+                                                           unsigned char* __restrict__ labs_out) {
+  __shared__ u32 s_keys[kSortTile];
+  __shared__ unsigned char s_labs[kSortTile];
+  __shared__ u32 warp_cnt[kSortWarps][kRadix];  // per-warp digit counts, then exclusive offsets in the tile
+  __shared__ u32 digit_start[kRadix];           // first position of each digit in the digit-ordered tile
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long base = (long long)blockIdx.x * kSortTile;
+  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&warp_cnt[0][0])[i] = 0;
+  __syncthreads();
+
+  // warp w owns the contiguous slice [w*512, (w+1)*512) of the tile, taken 32 keys per round: input order is
+  // (warp, round, lane), and ranks are handed out in exactly that order => stable
+  u32 key[kSortItems];
+  unsigned char lab[kSortItems];
+  unsigned short rank[kSortItems];
+  const long long wbase = base + (long long)warp * (32 * kSortItems);
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) {
+    long long i = wbase + r * 32 + lane;
+    const bool in = i < n;
+    key[r] = in ? keys_in[i] : 0u;
+    lab[r] = in ? labs_in[i] : 0;
+    const u32 d = (key[r] >> shift) & 0xff;
+    // slots past the end of the input (last tile only) match nobody and take no rank
+    const unsigned peers = __match_any_sync(0xffffffffu, in ? d : (0x100u + lane));
+    u32 before = 0;
+    if (in) {
+      before = warp_cnt[warp][d];
+      rank[r] = (unsigned short)(before + __popc(peers & ((1u << lane) - 1)));
+    }
+    __syncwarp();
+    if (in && lane == __ffs(peers) - 1) warp_cnt[warp][d] = before + __popc(peers);
+    __syncwarp();
+  }
+  __syncthreads();
+  // per digit: exclusive prefix over warps, and the digit's total in this tile
+  {
+    const int d = tid;  // 256 threads <-> 256 digits
+    u32 run = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) {
+      u32 c = warp_cnt[w][d];
+      warp_cnt[w][d] = run;
+      run += c;
+    }
+    // exclusive scan of the digit totals across the CTA
+    u32 x = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      u32 y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    __shared__ u32 wsum[kSortWarps];
+    if (lane == 31) wsum[warp] = x;
+    __syncthreads();
+    u32 add = 0;
+    for (int w = 0; w < warp; ++w) add += wsum[w];
+    digit_start[d] = add + x - run;
+  }
+  __syncthreads();
+  // stage the tile in digit order
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) {
+    long long i = wbase + r * 32 + lane;
+    if (i < n) {
+      const u32 d = (key[r] >> shift) & 0xff;
+      const u32 pos = digit_start[d] + warp_cnt[warp][d] + rank[r];
+      s_keys[pos] = key[r];
+      s_labs[pos] = lab[r];
+    }
+  }
+  __syncthreads();
+  // coalesced write-out: consecutive threads hold consecutive positions of the same digit run
+  const long long remaining = n - base;
+  const int valid = remaining < kSortTile ? (int)remaining : kSortTile;
+  for (int pos = tid; pos < valid; pos += kSortThreads) {
+    const u32 k = s_keys[pos];
+    const u32 d = (k >> shift) & 0xff;
+    const long long dst = (long long)bases[d] + table[(long long)d * ntiles + blockIdx.x] + (pos - digit_start[d]);
+    keys_out[dst] = k;
+    labs_out[dst] = s_labs[pos];
+  }
+}
+
+// ---- scan over the sorted sequence ------------------------------------------------------------------
+// run end at i  <=>  i == n-1 or score[i] != score[i+1] (float compare: -0.0 and 0.0 are one run, as in the
+// reference's `preds[1:] - preds[:-1]`)
+__device__ __forceinline__ bool run_end(const u32* __restrict__ keys, long long i, long long n) {
+  if (i == n - 1) return true;
+  float a = key_to_float(keys[i]), b = key_to_float(keys[i + 1]);
+  return (a - b) != 0.0f;  // NaN - x is NaN != 0 -> true, exactly what torch.where(diff) sees
+}
+
+__global__ void __launch_bounds__(kSortThreads) k4_tile_sums(const u32* __restrict__ keys,
+                                                             const unsigned char* __restrict__ labs, long long n,
+                                                             u64* __restrict__ tile_pos, u64* __restrict__ tile_ends) {
+  const long long base = (long long)blockIdx.x * kSortTile;
+  u32 pos = 0, ends = 0;
+  for (int r = 0; r < kSortItems; ++r) {
+    long long i = base + r * kSortThreads + threadIdx.x;
+    if (i < n) {
+      pos += labs[i];
+      ends += run_end(keys, i, n);
+    }
+  }
+  pos = __reduce_add_sync(0xffffffffu, pos);
+  ends = __reduce_add_sync(0xffffffffu, ends);
+  __shared__ u32 sp[kSortWarps], se[kSortWarps];
+  if ((threadIdx.x & 31) == 0) {
+    sp[threadIdx.x >> 5] = pos;
+    se[threadIdx.x >> 5] = ends;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u64 a = 0, b = 0;
+    for (int w = 0; w < kSortWarps; ++w) {
+      a += sp[w];
+      b += se[w];
+    }
+    tile_pos[blockIdx.x] = a;
+    tile_ends[blockIdx.x] = b;
+  }
+}
+
+// single CTA: exclusive scan of both tile arrays in place; totals to out2 = {num_positive, num_distinct}
+__global__ void __launch_bounds__(1024) k4_scan_tiles(u64* __restrict__ tile_pos, u64* __restrict__ tile_ends,
+                                                      int ntiles, long long* __restrict__ out2) {
+  __shared__ u64 wa[32], wb[32];
+  __shared__ u64 ca, cb;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) { ca = 0; cb = 0; }
+  __syncthreads();
+  for (int start = 0; start < ntiles; start += 1024) {
+    int i = start + threadIdx.x;
+    u64 va = i < ntiles ? tile_pos[i] : 0, vb = i < ntiles ? tile_ends[i] : 0;
+    u64 xa = va, xb = vb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      u64 ya = __shfl_up_sync(0xffffffffu, xa, o), yb = __shfl_up_sync(0xffffffffu, xb, o);
+      if (lane >= o) { xa += ya; xb += yb; }
+    }
+    if (lane == 31) { wa[warp] = xa; wb[warp] = xb; }
+    __syncthreads();
+    if (warp == 0) {
+      u64 a = wa[lane], b = wb[lane], sa = a, sb = b;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        u64 ya = __shfl_up_sync(0xffffffffu, sa, o), yb = __shfl_up_sync(0xffffffffu, sb, o);
+        if (lane >= o) { sa += ya; sb += yb; }
+      }
+      wa[lane] = sa - a;
+      wb[lane] = sb - b;
+    }
+    __syncthreads();
+    const u64 baseA = ca + wa[warp], baseB = cb + wb[warp];
+    if (i < ntiles) {
+      tile_pos[i] = baseA + xa - va;
+      tile_ends[i] = baseB + xb - vb;
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) { ca = baseA + xa; cb = baseB + xb; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    out2[0] = (long long)ca;
+    out2[1] = (long long)cb;
+  }
+}
+
+// per tile: inclusive scans with the tile's base, emit at run ends
+__global__ void __launch_bounds__(kSortThreads) k4_emit(const u32* __restrict__ keys,
+                                                        const unsigned char* __restrict__ labs, long long n,
+                                                        const u64* __restrict__ tile_pos, const u64* __restrict__ tile_ends,
+                                                        long long* __restrict__ fps, long long* __restrict__ tps,
+                                                        float* __restrict__ thr) {
+  // blocked arrangement: thread t owns items [t*16, t*16+16) of the tile so its running sums are sequential
+  __shared__ u32 wp[kSortWarps], we[kSortWarps];
+  const long long base = (long long)blockIdx.x * kSortTile + (long long)threadIdx.x * kSortItems;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  u32 lp[kSortItems];
+  bool le[kSortItems];
+  u32 tp = 0, te = 0;
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) {
+    long long i = base + r;
+    bool in = i < n;
+    lp[r] = in ? labs[i] : 0;
+    le[r] = in ? run_end(keys, i, n) : false;
+    tp += lp[r];
+    te += le[r];
+  }
+  u32 xp = tp, xe = te;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    u32 yp = __shfl_up_sync(0xffffffffu, xp, o), ye = __shfl_up_sync(0xffffffffu, xe, o);
+    if (lane >= o) { xp += yp; xe += ye; }
+  }
+  if (lane == 31) { wp[warp] = xp; we[warp] = xe; }
+  __syncthreads();
+  u32 addp = 0, adde = 0;
+  for (int w = 0; w < warp; ++w) { addp += wp[w]; adde += we[w]; }
+  u64 run_pos = tile_pos[blockIdx.x] + addp + xp - tp;   // positives strictly before this thread's first item
+  u64 run_end_cnt = tile_ends[blockIdx.x] + adde + xe - te;
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) {
+    long long i = base + r;
+    run_pos += lp[r];
+    if (le[r]) {
+      tps[run_end_cnt] = (long long)run_pos;
+      fps[run_end_cnt] = (long long)(i + 1) - (long long)run_pos;
+      thr[run_end_cnt] = key_to_float(keys[i]);
+      ++run_end_cnt;
+    }
+  }
+}
+
+struct K4Ws {
+  u32* keys[2];
+  unsigned char* labs[2];
+  u32* table;
+  u64* totals;
+  u64* bases;
+  u64* tile_pos;
+  u64* tile_ends;
+};
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static size_t k4_layout(long long n, unsigned char* base, K4Ws* ws) {
+  const long long ntiles = (n + kSortTile - 1) / kSortTile;
+  const size_t npad = (size_t)ntiles * kSortTile;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    unsigned char* p = base ? base + off : nullptr;
+    off += align256(bytes);
+    return p;
+  };
+  u32* k0 = (u32*)take(npad * 4);
+  u32* k1 = (u32*)take(npad * 4);
+  unsigned char* l0 = take(npad);
+  unsigned char* l1 = take(npad);
+  u32* table = (u32*)take((size_t)kRadix * ntiles * 4);
+  u64* totals = (u64*)take(kRadix * 8);
+  u64* bases = (u64*)take(kRadix * 8);
+  u64* tp = (u64*)take((size_t)ntiles * 8);
+  u64* te = (u64*)take((size_t)ntiles * 8);
+  if (ws) {
+    ws->keys[0] = k0; ws->keys[1] = k1; ws->labs[0] = l0; ws->labs[1] = l1;
+    ws->table = table; ws->totals = totals; ws->bases = bases; ws->tile_pos = tp; ws->tile_ends = te;
+  }
+  return off;
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" size_t tmb_exact_curve_workspace_bytes(int64_t n) {
+  if (n < 1) return 256;
+  return k4_layout(n, nullptr, nullptr);
+}
+
+extern "C" int tmb_exact_curve(const float* preds, const void* target, int target_dtype, int64_t n, int64_t pos_label,
+                               int64_t* fps, int64_t* tps, float* thresholds, int64_t* counts2, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  if (n < 0 || !counts2 || !workspace) return TMB_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    TMB_CUDA_CHECK(cudaMemsetAsync(counts2, 0, 16, st));
+    return TMB_OK;
+  }
+  if (!preds || !target || !fps || !tps || !thresholds) return TMB_ERR_ARG;
+  if (n >= (1LL << 32) - kSortTile) return TMB_ERR_TOO_LARGE;  // per-digit tile offsets are 32-bit
+  if (workspace_bytes < tmb_exact_curve_workspace_bytes(n)) return TMB_ERR_ARG;
+  if (!aligned32(preds) || !aligned32(target) || !aligned32(workspace)) return TMB_ERR_ALIGN;
+  K4Ws ws;
+  k4_layout(n, (unsigned char*)workspace, &ws);
+  const long long ntiles_ll = (n + kSortTile - 1) / kSortTile;
+  if (ntiles_ll > 0x7fffffff) return TMB_ERR_TOO_LARGE;
+  const int ntiles = (int)ntiles_ll;
+  {
+    long long nvec = n >> 2;
+    long long want = (nvec + 255) / 256;
+    long long cap = (long long)sm_count() * 8;
+    int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
+    TMB_DISPATCH_INT(target_dtype, TT, {
+      k4_prepare<TT><<<grid, 256, 0, st>>>(preds, (const TT*)target, n, pos_label, ws.keys[0], ws.labs[0]);
+    })
+  }
+  int cur = 0;
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 8 * pass;
+    k4_tile_hist<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], n, shift, ws.table, ntiles);
+    k4_scan_rows<<<kRadix, 1024, 0, st>>>(ws.table, ntiles, ws.totals);
+    k4_scan_totals<<<1, kRadix, 0, st>>>(ws.totals, ws.bases);
+    k4_scatter<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], ws.labs[cur], n, shift, ws.table, ntiles, ws.bases,
+                                                ws.keys[cur ^ 1], ws.labs[cur ^ 1]);
+    cur ^= 1;
+  }
+  k4_tile_sums<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], ws.labs[cur], n, ws.tile_pos, ws.tile_ends);
+  k4_scan_tiles<<<1, 1024, 0, st>>>(ws.tile_pos, ws.tile_ends, ntiles, (long long*)counts2);
+  k4_emit<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], ws.labs[cur], n, ws.tile_pos, ws.tile_ends,
+                                           (long long*)fps, (long long*)tps, thresholds);
+  TMB_CUDA_CHECK(cudaGetLastError());
+  return TMB_OK;
+}

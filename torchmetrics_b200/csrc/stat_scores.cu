@@ -33,6 +33,7 @@ struct StatParams {
   long long ignore;
   int check_range;
   int only_if_flag;
+  int range_check_ignored;  // 1: ignored positions take part in the [0,1] check (stat-scores _format order)
   u64* out;  // [4][L]
   StatWs* ws;
 };
@@ -66,9 +67,11 @@ __device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typenam
   if constexpr (IsFloatScore<PT>::value) {
     using CT = typename CmpType<PT>::type;
     CT p = to_cmp(pv);
-    // the reference range-checks the whole preds tensor, ignored positions included (stat_scores.py:104, :657)
-    if (P.check_range) oor |= !(p >= (CT)0 && p <= (CT)1);
-    if (P.has_ignore && t == P.ignore) return;
+    // stat-scores _format range-checks the whole preds tensor, ignored positions included (stat_scores.py:104,
+    // :657); the binary confusion-matrix _format drops ignored samples first (confusion_matrix.py:133-142)
+    const bool ign = P.has_ignore && t == P.ignore;
+    if (P.check_range && (P.range_check_ignored || !ign)) oor |= !(p >= (CT)0 && p <= (CT)1);
+    if (ign) return;
     if constexpr (SIGMOID) p = round_to_storage<PT>(sigmoid_ref(p));
     const bool pb = p > thr;
     c.tp += (t == 1) & pb;
@@ -265,8 +268,8 @@ extern "C" size_t tmb_stat_scores_workspace_bytes(int64_t num_labels) {
 
 extern "C" int tmb_stat_scores_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
                                       int64_t n_rows, int64_t num_labels, double threshold, int prob_mode,
-                                      int has_ignore, int64_t ignore_index, int64_t* out, void* workspace,
-                                      size_t workspace_bytes, void* stream) {
+                                      int has_ignore, int64_t ignore_index, int range_check_ignored, int64_t* out,
+                                      void* workspace, size_t workspace_bytes, void* stream) {
   if (n_rows < 0 || num_labels < 1 || !out || !workspace) return TMB_ERR_ARG;
   if (workspace_bytes < tmb_stat_scores_workspace_bytes(num_labels)) return TMB_ERR_ARG;
   if (n_rows == 0) return TMB_OK;
@@ -280,6 +283,7 @@ extern "C" int tmb_stat_scores_update(const void* preds, int preds_dtype, const 
   P.threshold = threshold;
   P.has_ignore = has_ignore ? 1 : 0;
   P.ignore = ignore_index;
+  P.range_check_ignored = range_check_ignored ? 1 : 0;
   P.out = (u64*)out;
   P.ws = (StatWs*)workspace;
   cudaStream_t st = (cudaStream_t)stream;

@@ -1,0 +1,158 @@
+"""Argument and tensor validation shared by the classification functionals.
+
+Conditions and exception types follow the reference's `_*_arg_validation` / `_*_tensor_validation` functions
+(functional/classification/confusion_matrix.py:62-116, :228-303; stat_scores.py:30-87, :216-322, :560-644;
+precision_recall_curve.py:94-159, :360-420, :684-736).  Value checks avoid the reference's `torch.unique` sort on
+the passing path: labels inside the legal set cannot have too many distinct values, so one min/max (or one masked
+`any`) pass decides; only an input that is about to fail pays for the exact unique count used in the message.
+"""
+from typing import List, Optional, Sequence, Union
+
+import torch
+from torch import Tensor
+
+from torchmetrics_b200.utilities.checks import _check_same_shape
+
+
+def check_ignore_index(ignore_index: Optional[int]) -> None:
+    if ignore_index is not None and not isinstance(ignore_index, int):
+        raise ValueError(f"Expected argument `ignore_index` to either be `None` or an integer, but got {ignore_index}")
+
+
+def check_threshold(threshold: float) -> None:
+    if not (isinstance(threshold, float) and (0 <= threshold <= 1)):
+        raise ValueError(f"Expected argument `threshold` to be a float in the [0,1] range, but got {threshold}.")
+
+
+def check_choice(name: str, value, allowed: Sequence) -> None:
+    if value not in allowed:
+        raise ValueError(f"Expected argument `{name}` to be one of {tuple(allowed)}, but got {value}")
+
+
+def check_num(name: str, value, minimum: int = 2) -> None:
+    if not isinstance(value, int) or value < minimum:
+        raise ValueError(f"Expected argument `{name}` to be an integer larger than {minimum - 1}, but got {value}")
+
+
+def check_thresholds_arg(thresholds: Optional[Union[int, List[float], Tensor]]) -> None:
+    """precision_recall_curve.py:94-122."""
+    if thresholds is not None and not isinstance(thresholds, (list, int, Tensor)):
+        raise ValueError(
+            "Expected argument `thresholds` to either be an integer, list of floats or"
+            f" tensor of floats, but got {thresholds}"
+        )
+    if isinstance(thresholds, int) and thresholds < 2:
+        raise ValueError(
+            f"If argument `thresholds` is an integer, expected it to be larger than 1, but got {thresholds}"
+        )
+    if isinstance(thresholds, list) and not all(isinstance(t, float) and 0 <= t <= 1 for t in thresholds):
+        raise ValueError(
+            "If argument `thresholds` is a list, expected all elements to be floats in the [0,1] range,"
+            f" but got {thresholds}"
+        )
+    if isinstance(thresholds, Tensor) and not thresholds.ndim == 1:
+        raise ValueError("If argument `thresholds` is an tensor, expected the tensor to be 1d")
+
+
+def check_binary_values(t: Tensor, name: str, ignore_index: Optional[int] = None, what: str = "") -> None:
+    """Every value must be 0, 1 (or ignore_index); one fused elementwise pass + any()."""
+    bad = (t != 0) & (t != 1)
+    if ignore_index is not None:
+        bad &= t != ignore_index
+    if bool(bad.any()):
+        uniq = torch.unique(t)
+        if name == "target":
+            raise RuntimeError(
+                f"Detected the following values in `target`: {uniq} but expected only"
+                f" the following values {[0, 1] if ignore_index is None else [ignore_index]}."
+            )
+        raise RuntimeError(
+            f"Detected the following values in `preds`: {uniq} but expected only"
+            f" the following values [0,1] since {what or 'preds'} is a label tensor."
+        )
+
+
+def check_label_count(t: Tensor, name: str, num_classes: int, ignore_index: Optional[int] = None) -> None:
+    """The reference rejects tensors with more distinct values than classes (+1 for ignore_index)."""
+    if t.numel() == 0:
+        return
+    allowed = num_classes + (1 if (ignore_index is not None and name == "target") else 0)
+    lo, hi = torch.aminmax(t)
+    lo, hi = int(lo), int(hi)
+    span_ok = lo >= 0 and hi < num_classes
+    if not span_ok and ignore_index is not None and name == "target":
+        kept = t[t != ignore_index]
+        if kept.numel() == 0:
+            return
+        lo, hi = (int(v) for v in torch.aminmax(kept))
+        span_ok = lo >= 0 and hi < num_classes
+    if span_ok:
+        return
+    n_unique = len(torch.unique(t))
+    if n_unique > allowed:
+        raise RuntimeError(
+            f"Detected more unique values in `{name}` than `num_classes`. Expected only"
+            f" {allowed} but found {n_unique} in `{name}`."
+        )
+
+
+def check_multiclass_shapes(preds: Tensor, target: Tensor, num_classes: int, multidim_average: str = "global") -> None:
+    if preds.ndim == target.ndim + 1:
+        if not preds.is_floating_point():
+            raise ValueError("If `preds` have one dimension more than `target`, `preds` should be a float tensor.")
+        if preds.shape[1] != num_classes:
+            raise ValueError(
+                "If `preds` have one dimension more than `target`, `preds.shape[1]` should be"
+                " equal to number of classes."
+            )
+        if preds.shape[2:] != target.shape[1:]:
+            raise ValueError(
+                "If `preds` have one dimension more than `target`, the shape of `preds` should be"
+                " (N, C, ...), and the shape of `target` should be (N, ...)."
+            )
+        if multidim_average != "global" and preds.ndim < 3:
+            raise ValueError(
+                "If `preds` have one dimension more than `target`, the shape of `preds` should "
+                " at least 3D when multidim_average is set to `samplewise`"
+            )
+    elif preds.ndim == target.ndim:
+        if preds.shape != target.shape:
+            raise ValueError(
+                "The `preds` and `target` should have the same shape,",
+                f" got `preds` with shape={preds.shape} and `target` with shape={target.shape}.",
+            )
+        if multidim_average != "global" and preds.ndim < 2:
+            raise ValueError(
+                "When `preds` and `target` have the same shape, the shape of `preds` should "
+                " at least 2D when multidim_average is set to `samplewise`"
+            )
+    else:
+        raise ValueError(
+            "Either `preds` and `target` both should have the (same) shape (N, ...), or `target` should be (N, ...)"
+            " and `preds` should be (N, C, ...)."
+        )
+
+
+def check_multilabel_shapes(preds: Tensor, target: Tensor, num_labels: int) -> None:
+    _check_same_shape(preds, target)
+    if preds.shape[1] != num_labels:
+        raise ValueError(
+            "Expected both `target.shape[1]` and `preds.shape[1]` to be equal to the number of labels"
+            f" but got {preds.shape[1]} and expected {num_labels}"
+        )
+
+
+def check_curve_target_dtype(target: Tensor) -> None:
+    if target.is_floating_point():
+        raise ValueError(
+            "Expected argument `target` to be an int or long tensor with ground truth labels"
+            f" but got tensor with dtype {target.dtype}"
+        )
+
+
+def check_float_preds(preds: Tensor) -> None:
+    if not preds.is_floating_point():
+        raise ValueError(
+            "Expected argument `preds` to be an floating tensor with probability/logit scores,"
+            f" but got tensor with dtype {preds.dtype}"
+        )

@@ -1,0 +1,339 @@
+"""tp / fp / tn / fn statistics (reference: functional/classification/stat_scores.py).
+
+`_binary_stat_scores_update`, `_multilabel_stat_scores_update` (global) run the K2 kernel; the multiclass update
+runs K1 (confusion matrix, then diag / row / column sums exactly as stat_scores.py:405-418) or the match-count kernel
+for `average="micro"` (:394-404).  `_*_update_fused` folds `_format` into the kernel pass.
+
+`multidim_average="samplewise"` and `top_k > 1` follow the reference's one-hot formulation with device-side torch
+ops (:363-393): they return per-sample rows rather than O(C) counts and are outside the streaming-histogram path.
+"""
+from importlib import import_module
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+from typing_extensions import Literal
+
+from torchmetrics_b200 import _native
+C = import_module("torchmetrics_b200.functional.classification._checks")
+from torchmetrics_b200.functional.classification.confusion_matrix import _label_major
+from torchmetrics_b200.utilities.checks import _check_same_shape
+from torchmetrics_b200.utilities.data import select_topk
+from torchmetrics_b200.utilities.enums import ClassificationTask
+
+_AVG = ("micro", "macro", "weighted", "none", None)
+_MDA = ("global", "samplewise")
+
+
+def _four_masked_sums(preds: Tensor, target: Tensor, dims) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    eq = target == preds
+    tp = (eq & (target == 1)).sum(dims)
+    fn = (~eq & (target == 1)).sum(dims)
+    fp = (~eq & (target == 0)).sum(dims)
+    tn = (eq & (target == 0)).sum(dims)
+    return tp, fp, tn, fn
+
+
+# ======================================================================================= binary
+def _binary_stat_scores_arg_validation(threshold: float = 0.5, multidim_average: str = "global",
+                                       ignore_index: Optional[int] = None) -> None:
+    C.check_threshold(threshold)
+    C.check_choice("multidim_average", multidim_average, _MDA)
+    C.check_ignore_index(ignore_index)
+
+
+def _binary_stat_scores_tensor_validation(preds: Tensor, target: Tensor, multidim_average: str = "global",
+                                          ignore_index: Optional[int] = None) -> None:
+    _check_same_shape(preds, target)
+    C.check_binary_values(target, "target", ignore_index)
+    if not preds.is_floating_point():
+        C.check_binary_values(preds, "preds", what="`preds`")
+    if multidim_average != "global" and preds.ndim < 2:
+        raise ValueError("Expected input to be at least 2D when multidim_average is set to `samplewise`")
+
+
+def _binary_stat_scores_format(preds: Tensor, target: Tensor, threshold: float = 0.5,
+                               ignore_index: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+    """Reference-contract formatting (stat_scores.py:90-117): ignored targets become -1."""
+    if preds.is_floating_point():
+        if not torch.all((preds >= 0) * (preds <= 1)):
+            preds = preds.sigmoid()
+        preds = preds > threshold
+    preds = preds.reshape(preds.shape[0], -1)
+    target = target.reshape(target.shape[0], -1)
+    if ignore_index is not None:
+        target = torch.where(target == ignore_index, torch.full_like(target, -1), target)
+    return preds, target
+
+
+def _binary_stat_scores_update(preds: Tensor, target: Tensor, multidim_average: str = "global"
+                               ) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Counts over formatted label tensors (stat_scores.py:120-131); global -> K2 with one label."""
+    if multidim_average == "global":
+        stats = torch.zeros(4, 1, dtype=torch.int64, device=preds.device)
+        _native.stat_scores_update_(stats, preds, target, 1, 0.5, None, _native.PROB_AS_IS)
+        return stats[0, 0], stats[1, 0], stats[2, 0], stats[3, 0]
+    tp, fp, tn, fn = _four_masked_sums(preds, target, [1])
+    return tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze()
+
+
+def _binary_stat_scores_update_fused(preds: Tensor, target: Tensor, threshold: float = 0.5,
+                                     multidim_average: str = "global", ignore_index: Optional[int] = None,
+                                     out: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """_format + _update in one K2 pass (global); `out` is an optional (4,1) int64 accumulator."""
+    if multidim_average != "global":
+        return _binary_stat_scores_update(*_binary_stat_scores_format(preds, target, threshold, ignore_index),
+                                          multidim_average)
+    stats = out if out is not None else torch.zeros(4, 1, dtype=torch.int64, device=preds.device)
+    _native.stat_scores_update_(stats, preds, target, 1, threshold, ignore_index, _native.PROB_AUTO)
+    return stats[0, 0], stats[1, 0], stats[2, 0], stats[3, 0]
+
+
+def _binary_stat_scores_compute(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor,
+                                multidim_average: str = "global") -> Tensor:
+    return torch.stack([tp, fp, tn, fn, tp + fn], dim=0 if multidim_average == "global" else 1).squeeze()
+
+
+def binary_stat_scores(preds: Tensor, target: Tensor, threshold: float = 0.5,
+                       multidim_average: Literal["global", "samplewise"] = "global",
+                       ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    if validate_args:
+        _binary_stat_scores_arg_validation(threshold, multidim_average, ignore_index)
+        _binary_stat_scores_tensor_validation(preds, target, multidim_average, ignore_index)
+    tp, fp, tn, fn = _binary_stat_scores_update_fused(preds, target, threshold, multidim_average, ignore_index)
+    return _binary_stat_scores_compute(tp, fp, tn, fn, multidim_average)
+
+
+# ======================================================================================= multiclass
+def _multiclass_stat_scores_arg_validation(num_classes: int, top_k: int = 1, average: Optional[str] = "macro",
+                                           multidim_average: str = "global", ignore_index: Optional[int] = None) -> None:
+    C.check_num("num_classes", num_classes)
+    if not isinstance(top_k, int) and top_k < 1:
+        raise ValueError(f"Expected argument `top_k` to be an integer larger than or equal to 1, but got {top_k}")
+    if top_k > num_classes:
+        raise ValueError(
+            f"Expected argument `top_k` to be smaller or equal to `num_classes` but got {top_k} and {num_classes}"
+        )
+    C.check_choice("average", average, _AVG)
+    C.check_choice("multidim_average", multidim_average, _MDA)
+    C.check_ignore_index(ignore_index)
+
+
+def _multiclass_stat_scores_tensor_validation(preds: Tensor, target: Tensor, num_classes: int,
+                                              multidim_average: str = "global",
+                                              ignore_index: Optional[int] = None) -> None:
+    C.check_multiclass_shapes(preds, target, num_classes, multidim_average)
+    C.check_label_count(target, "target", num_classes, ignore_index)
+    if not preds.is_floating_point():
+        C.check_label_count(preds, "preds", num_classes)
+
+
+def _multiclass_stat_scores_format(preds: Tensor, target: Tensor, top_k: int = 1) -> Tuple[Tensor, Tensor]:
+    """argmax when preds carry a class dimension and top_k == 1; flatten extra dims (stat_scores.py:325-341)."""
+    if preds.ndim == target.ndim + 1 and top_k == 1:
+        preds = preds.argmax(dim=1)
+    preds = preds.reshape(*preds.shape[:2], -1) if top_k != 1 else preds.reshape(preds.shape[0], -1)
+    target = target.reshape(target.shape[0], -1)
+    return preds, target
+
+
+def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: int, top_k: int = 1,
+                                   average: Optional[str] = "macro", multidim_average: str = "global",
+                                   ignore_index: Optional[int] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """stat_scores.py:344-419."""
+    if multidim_average == "samplewise" or top_k != 1:
+        return _multiclass_stat_scores_onehot(preds, target, num_classes, top_k, multidim_average, ignore_index)
+    dev = preds.device
+    if average == "micro":
+        cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+        _native.match_count_update_(cnt, preds, target, ignore_index)
+        n_valid, tp = cnt[0], cnt[1]
+        fp = n_valid - tp
+        fn = fp.clone()
+        tn = num_classes * n_valid - (fp + fn + tp)
+        return tp, fp, tn, fn
+    cm = torch.zeros(num_classes, num_classes, dtype=torch.int64, device=dev)
+    _native.confmat_update_(cm, preds, target, num_classes, ignore_index)
+    tp = cm.diag()
+    fp = cm.sum(0) - tp
+    fn = cm.sum(1) - tp
+    tn = cm.sum() - (fp + fn + tp)
+    return tp, fp, tn, fn
+
+
+def _multiclass_stat_scores_onehot(preds: Tensor, target: Tensor, num_classes: int, top_k: int,
+                                   multidim_average: str, ignore_index: Optional[int]):
+    """One-hot branch of the reference (stat_scores.py:363-393), device-side torch ops."""
+    ignore_in = 0 <= ignore_index <= num_classes - 1 if ignore_index is not None else None
+    if ignore_index is not None and not ignore_in:
+        preds, target = preds.clone(), target.clone()
+        idx = target == ignore_index
+        target[idx] = num_classes
+        idx = idx.unsqueeze(1).repeat(1, num_classes, 1) if preds.ndim > target.ndim else idx
+        preds[idx] = num_classes
+    depth = num_classes + 1 if ignore_index is not None and not ignore_in else num_classes
+    if top_k > 1:
+        preds_oh = torch.movedim(select_topk(preds, topk=top_k, dim=1), 1, -1)
+    else:
+        preds_oh = torch.nn.functional.one_hot(preds.long(), depth)
+    target_oh = torch.nn.functional.one_hot(target.long(), depth)
+    if ignore_index is not None:
+        if ignore_in:
+            target_oh[target == ignore_index, :] = -1
+        else:
+            preds_oh = preds_oh[..., :-1] if top_k == 1 else preds_oh
+            target_oh = target_oh[..., :-1]
+            target_oh[target == num_classes, :] = -1
+    return _four_masked_sums(preds_oh, target_oh, [0, 1] if multidim_average == "global" else [1])
+
+
+def _multiclass_stat_scores_update_fused(preds: Tensor, target: Tensor, num_classes: int, top_k: int = 1,
+                                         average: Optional[str] = "macro", multidim_average: str = "global",
+                                         ignore_index: Optional[int] = None):
+    preds, target = _multiclass_stat_scores_format(preds, target, top_k)
+    return _multiclass_stat_scores_update(preds, target, num_classes, top_k, average, multidim_average, ignore_index)
+
+
+def _multiclass_stat_scores_compute(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str] = "macro",
+                                    multidim_average: str = "global") -> Tensor:
+    """Stack [tp, fp, tn, fn, support] and average over classes (stat_scores.py:422-448)."""
+    res = torch.stack([tp, fp, tn, fn, tp + fn], dim=-1)
+    sum_dim = 0 if multidim_average == "global" else 1
+    if average == "micro":
+        return res.sum(sum_dim) if res.ndim > 1 else res
+    if average == "macro":
+        return res.float().mean(sum_dim)
+    if average == "weighted":
+        weight = tp + fn
+        if multidim_average == "global":
+            return (res * (weight / weight.sum()).reshape(*weight.shape, 1)).sum(sum_dim)
+        return (res * (weight / weight.sum(-1, keepdim=True)).reshape(*weight.shape, 1)).sum(sum_dim)
+    if average is None or average == "none":
+        return res
+    return None
+
+
+def multiclass_stat_scores(preds: Tensor, target: Tensor, num_classes: int,
+                           average: Optional[Literal["micro", "macro", "weighted", "none"]] = "macro", top_k: int = 1,
+                           multidim_average: Literal["global", "samplewise"] = "global",
+                           ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    if validate_args:
+        _multiclass_stat_scores_arg_validation(num_classes, top_k, average, multidim_average, ignore_index)
+        _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
+    tp, fp, tn, fn = _multiclass_stat_scores_update_fused(preds, target, num_classes, top_k, average,
+                                                          multidim_average, ignore_index)
+    _native.raise_on_status(preds.device, num_classes)
+    return _multiclass_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
+
+
+# ======================================================================================= multilabel
+def _multilabel_stat_scores_arg_validation(num_labels: int, threshold: float = 0.5, average: Optional[str] = "macro",
+                                           multidim_average: str = "global", ignore_index: Optional[int] = None) -> None:
+    C.check_num("num_labels", num_labels)
+    C.check_threshold(threshold)
+    C.check_choice("average", average, _AVG)
+    C.check_choice("multidim_average", multidim_average, _MDA)
+    C.check_ignore_index(ignore_index)
+
+
+def _multilabel_stat_scores_tensor_validation(preds: Tensor, target: Tensor, num_labels: int,
+                                              multidim_average: str, ignore_index: Optional[int] = None) -> None:
+    C.check_multilabel_shapes(preds, target, num_labels)
+    C.check_binary_values(target, "target", ignore_index)
+    if not preds.is_floating_point():
+        C.check_binary_values(preds, "preds")
+    if multidim_average != "global" and preds.ndim < 3:
+        raise ValueError("Expected input to be at least 3D when multidim_average is set to `samplewise`")
+
+
+def _multilabel_stat_scores_format(preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
+                                   ignore_index: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+    """Reference-contract formatting (stat_scores.py:647-669): (N, L, X) label tensors, ignored targets -1."""
+    if preds.is_floating_point():
+        if not torch.all((preds >= 0) * (preds <= 1)):
+            preds = preds.sigmoid()
+        preds = preds > threshold
+    preds = preds.reshape(*preds.shape[:2], -1)
+    target = target.reshape(*target.shape[:2], -1)
+    if ignore_index is not None:
+        target = torch.where(target == ignore_index, torch.full_like(target, -1), target)
+    return preds, target
+
+
+def _multilabel_stat_scores_update(preds: Tensor, target: Tensor, multidim_average: str = "global"
+                                   ) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Per-label counts of formatted (N, L, X) tensors (stat_scores.py:672-681); global -> K2."""
+    if multidim_average == "global":
+        L = preds.shape[1]
+        stats = torch.zeros(4, L, dtype=torch.int64, device=preds.device)
+        _native.stat_scores_update_(stats, _label_major(preds, L), _label_major(target, L), L, 0.5, None,
+                                    _native.PROB_AS_IS)
+        return stats[0], stats[1], stats[2], stats[3]
+    tp, fp, tn, fn = _four_masked_sums(preds, target, [-1])
+    return tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze()
+
+
+def _multilabel_stat_scores_update_fused(preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
+                                         multidim_average: str = "global", ignore_index: Optional[int] = None,
+                                         out: Optional[Tensor] = None):
+    """_format + _update in one K2 pass over the raw scores; `out` is an optional (4, L) int64 accumulator."""
+    if multidim_average != "global":
+        return _multilabel_stat_scores_update(
+            *_multilabel_stat_scores_format(preds, target, num_labels, threshold, ignore_index), multidim_average)
+    stats = out if out is not None else torch.zeros(4, num_labels, dtype=torch.int64, device=preds.device)
+    _native.stat_scores_update_(stats, _label_major(preds, num_labels), _label_major(target, num_labels), num_labels,
+                                threshold, ignore_index, _native.PROB_AUTO)
+    return stats[0], stats[1], stats[2], stats[3]
+
+
+def _multilabel_stat_scores_compute(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str] = "macro",
+                                    multidim_average: str = "global") -> Tensor:
+    res = torch.stack([tp, fp, tn, fn, tp + fn], dim=-1)
+    sum_dim = 0 if multidim_average == "global" else 1
+    if average == "micro":
+        return res.sum(sum_dim)
+    if average == "macro":
+        return res.float().mean(sum_dim)
+    if average == "weighted":
+        w = tp + fn
+        return (res * (w / w.sum()).reshape(*w.shape, 1)).sum(sum_dim)
+    if average is None or average == "none":
+        return res
+    return None
+
+
+def multilabel_stat_scores(preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
+                           average: Optional[Literal["micro", "macro", "weighted", "none"]] = "macro",
+                           multidim_average: Literal["global", "samplewise"] = "global",
+                           ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    if validate_args:
+        _multilabel_stat_scores_arg_validation(num_labels, threshold, average, multidim_average, ignore_index)
+        _multilabel_stat_scores_tensor_validation(preds, target, num_labels, multidim_average, ignore_index)
+    tp, fp, tn, fn = _multilabel_stat_scores_update_fused(preds, target, num_labels, threshold, multidim_average,
+                                                          ignore_index)
+    return _multilabel_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
+
+
+# ======================================================================================= task wrapper
+def stat_scores(preds: Tensor, target: Tensor, task: Literal["binary", "multiclass", "multilabel"],
+                threshold: float = 0.5, num_classes: Optional[int] = None, num_labels: Optional[int] = None,
+                average: Optional[Literal["micro", "macro", "weighted", "none"]] = "micro",
+                multidim_average: Optional[Literal["global", "samplewise"]] = "global", top_k: Optional[int] = 1,
+                ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    task = ClassificationTask.from_str(task)
+    assert multidim_average is not None
+    if task == ClassificationTask.BINARY:
+        return binary_stat_scores(preds, target, threshold, multidim_average, ignore_index, validate_args)
+    if task == ClassificationTask.MULTICLASS:
+        if not isinstance(num_classes, int):
+            raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+        if not isinstance(top_k, int):
+            raise ValueError(f"`top_k` is expected to be `int` but `{type(top_k)} was passed.`")
+        return multiclass_stat_scores(preds, target, num_classes, average, top_k, multidim_average, ignore_index,
+                                      validate_args)
+    if task == ClassificationTask.MULTILABEL:
+        if not isinstance(num_labels, int):
+            raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")
+        return multilabel_stat_scores(preds, target, num_labels, threshold, average, multidim_average, ignore_index,
+                                      validate_args)
+    raise ValueError(f"Task {task} not supported.")
