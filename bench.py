@@ -1,0 +1,348 @@
+"""Benchmark of the metric-state hot path (contract: see the task statement; one JSON line on stdout from rank 0).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1], the configuration the headline metric is quoted on): `MulticlassConfusionMatrix(
+num_classes=1000).update` on 2**24-sample int64 batches, one batch per step per GPU (weak scaling: every rank has its
+own batches).  `value` = samples consumed by update() per second over all ranks with the inputs already in HBM;
+`e2e` = the same through the public Metric API with inputs in pinned HOST memory, the host->device copies and a
+device->host read of the state inside the timed region.  `extra` carries the second half of the headline metric
+(binned AUROC+AP, T=200) and, for N>1, the sync latencies.
+
+`--impl reference` times the CPU restatement of the reference's algorithm (oracle/oracle.c, OpenMP, all host
+threads) on the same workload.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NUM_CLASSES = 1000
+BATCH = 1 << 24
+BYTES_PER_SAMPLE = 16  # int64 pred + int64 target
+METRIC = "update samples/s (MulticlassConfusionMatrix C=1000, 2^24-sample int64 batches)"
+
+
+def _measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms during the timed region (profiling recipe's clocks line)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu_index = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 9:
+                self.rows.append(parts)
+
+    def stop(self):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = max(mx, float(r[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference(args, rank, world):
+    """CPU arm: oracle/oracle.c (C + OpenMP restatement of confusion_matrix.py:333-337) on the box's host cores."""
+    if rank != 0:
+        return
+    import numpy as np
+
+    from oracle import oracle_c as OC
+
+    rng = np.random.default_rng(1234)
+    batches = [(rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)) for _ in range(2)]
+    state = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)
+    for i in range(args.warmup):
+        OC.confmat_update(*batches[i % 2], NUM_CLASSES, out=state)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        OC.confmat_update(*batches[i % 2], NUM_CLASSES, out=state)
+    dt = time.perf_counter() - t0
+    assert int(state.sum()) == (args.warmup + args.steps) * BATCH
+    value = args.steps * BATCH / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": {"workload": "configs[1]: MulticlassConfusionMatrix num_classes=1000, 2^24-sample int64 batches",
+                   "samples_per_step": BATCH, "note": "CPU arm runs on rank 0 only, one batch per step"},
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": OC.num_threads(), "kind": "port",
+                         "sample": f"{args.steps} full 2^24-sample batches (oracle/oracle.c, OpenMP)"},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--skip-extra", action="store_true", help="only the headline workload")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import torchmetrics_b200 as tm
+    from torchmetrics_b200 import _native as N
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    N.load()
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local_rank])
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ------------------------------------------------------------------ headline: confusion matrix updates
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    batches = [(torch.randint(0, NUM_CLASSES, (BATCH,), device=dev, generator=g),
+                torch.randint(0, NUM_CLASSES, (BATCH,), device=dev, generator=g)) for _ in range(2)]
+    metric = tm.MulticlassConfusionMatrix(NUM_CLASSES, validate_args=False).to(dev)
+    for i in range(args.warmup):
+        metric.update(*batches[i % 2])
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        metric.update(*batches[i % 2])
+    e1.record()
+    barrier()
+    step_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    assert int(metric.compute().sum()) == (args.warmup + args.steps) * BATCH * world  # synced count, exact
+    value = BATCH * world / (step_ms * 1e-3)
+
+    # dominant kernel alone (roofline.achieved): same launches through the C ABI, CUDA events on the launch stream
+    cm = torch.zeros(NUM_CLASSES, NUM_CLASSES, dtype=torch.int64, device=dev)
+    for i in range(3):
+        N.confmat_update_(cm, *batches[i % 2], NUM_CLASSES)
+    torch.cuda.synchronize()
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record()
+    for i in range(args.steps):
+        N.confmat_update_(cm, *batches[i % 2], NUM_CLASSES)
+    k1.record()
+    torch.cuda.synchronize()
+    kernel_ms = k0.elapsed_time(k1) / args.steps
+    peak, peak_src = _measured_peak()
+    achieved = BATCH * BYTES_PER_SAMPLE / (kernel_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("confmat_global_kernel_bytes_per_launch")
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "confmat_global_kernel<int64,int64>", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": BATCH * BYTES_PER_SAMPLE, "kernel_ms": kernel_ms,
+                "frac_of_nominal_8TBps": achieved / 8000.0}
+
+    # ------------------------------------------------------------------ e2e: host buffers through the public API
+    e2e_steps = max(5, min(args.steps, 20))
+    host = [(p.cpu().pin_memory(), t.cpu().pin_memory()) for p, t in batches]
+    dbuf = [(torch.empty_like(batches[0][0]), torch.empty_like(batches[0][1])) for _ in range(2)]
+    out_host = torch.empty(NUM_CLASSES, NUM_CLASSES, dtype=torch.int64).pin_memory()
+    copy_stream = torch.cuda.Stream(device=dev)
+    m2 = tm.MulticlassConfusionMatrix(NUM_CLASSES, validate_args=False).to(dev)
+    main_stream = torch.cuda.current_stream(dev)
+
+    def e2e_run(nsteps):
+        ready = [torch.cuda.Event() for _ in range(2)]
+        freed = [torch.cuda.Event() for _ in range(2)]
+
+        def stage(i):
+            with torch.cuda.stream(copy_stream):
+                if i >= 2:
+                    copy_stream.wait_event(freed[i % 2])
+                dbuf[i % 2][0].copy_(host[i % 2][0], non_blocking=True)
+                dbuf[i % 2][1].copy_(host[i % 2][1], non_blocking=True)
+                ready[i % 2].record(copy_stream)
+
+        stage(0)
+        for i in range(nsteps):
+            if i + 1 < nsteps:
+                stage(i + 1)  # next step's copy overlaps this step's kernel
+            main_stream.wait_event(ready[i % 2])
+            m2.update(*dbuf[i % 2])
+            freed[i % 2].record(main_stream)
+            out_host.copy_(m2.confmat, non_blocking=True)  # the step's result (the state) back on the host
+        torch.cuda.synchronize()
+
+    e2e_run(3)
+    m2.reset()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_run(e2e_steps)
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    assert int(out_host.sum()) == e2e_steps * BATCH
+    e2e = {"value": e2e_steps * BATCH * world / e2e_s, "unit": "samples/s",
+           "h2d_bytes_per_step": BATCH * BYTES_PER_SAMPLE, "d2h_bytes_per_step": NUM_CLASSES * NUM_CLASSES * 8,
+           "steps": e2e_steps, "note": "pinned host tensors -> .copy_ on a side stream (double-buffered) -> "
+                                       "Metric.update -> state copied back; PCIe-bound"}
+    del host, dbuf, m2
+    # the sampler covers all three timed regions above (device-resident steps, kernel-only loop, e2e)
+    clocks = sampler.stop() if rank == 0 else None
+    gpu_launches = args.steps  # one confmat_global_kernel per update in the timed region
+
+    # ------------------------------------------------------------------ extra: binned AUROC+AP (config 3) and sync
+    extra = {}
+    if not args.skip_extra:
+        del batches, cm
+        torch.cuda.empty_cache()
+        n_total = 1 << 28
+        n_local = n_total // world
+        g2 = torch.Generator(device=dev).manual_seed(99 + rank)
+        preds = torch.rand(n_local, device=dev, generator=g2)
+        target = (torch.rand(n_local, device=dev, generator=g2) < 0.3 + 0.4 * preds).long()
+        coll = tm.MetricCollection([tm.BinaryAUROC(thresholds=200, validate_args=False),
+                                    tm.BinaryAveragePrecision(thresholds=200, validate_args=False)]).to(dev)
+        for _ in range(3):
+            coll.update(preds, target)
+        barrier()
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        b0.record()
+        for _ in range(reps):
+            coll.update(preds, target)
+        b1.record()
+        barrier()
+        bms = max_over_ranks(b0.elapsed_time(b1)) / reps
+        out = coll.compute()
+        extra["binned_auroc_ap_T200"] = {
+            "workload": "configs[2]: BinaryAUROC+BinaryAveragePrecision thresholds=200, 2^28 fp32 scores + int64 "
+                        "targets sharded over the ranks (strong scaling), one compute group => one update",
+            "value": n_total / (bms * 1e-3), "unit": "samples/s", "ms_per_update": bms,
+            "achieved_GBps_per_gpu": n_local * 12 / (bms * 1e-3) / 1e9,
+            "frac_of_measured_peak": n_local * 12 / (bms * 1e-3) / 1e9 / peak,
+            "auroc": float(out["BinaryAUROC"]), "ap": float(out["BinaryAveragePrecision"]),
+        }
+        if world > 1:
+            def sync_us(m, reps=30):
+                ts = []
+                for _ in range(reps):
+                    torch.cuda.synchronize()
+                    dist.barrier(device_ids=[local_rank])
+                    t0 = time.perf_counter()
+                    m.sync()
+                    torch.cuda.synchronize()
+                    ts.append((time.perf_counter() - t0) * 1e6)
+                    m.unsync()
+                return max_over_ranks(statistics.median(ts))
+
+            extra["sync_us"] = {
+                "confmat_8MB_one_allreduce": sync_us(metric),
+                "binned_6.4KB_one_allreduce": sync_us(coll.__getitem__("BinaryAUROC", copy_state=False)),
+                "note": "median host-timed Metric.sync() incl. stream sync, max over ranks",
+            }
+        del preds, target
+
+    # ------------------------------------------------------------------ CPU baseline (rank 0, N=1 only)
+    cpu_baseline = None
+    if rank == 0 and world == 1:
+        import numpy as np
+
+        from oracle import oracle_c as OC
+
+        rng = np.random.default_rng(1234)
+        p, t = rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)
+        st = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)
+        OC.confmat_update(p, t, NUM_CLASSES, out=st)
+        t0, reps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < 10.0 and reps < 200:
+            OC.confmat_update(p, t, NUM_CLASSES, out=st)
+            reps += 1
+        dt = time.perf_counter() - t0
+        cpu_baseline = {"value": reps * BATCH / dt, "unit": "samples/s", "cores": OC.num_threads(), "kind": "port",
+                        "sample": f"{reps} repetitions of one 2^24-sample batch (~10 s), oracle/oracle.c with OpenMP"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+            "config": {"workload": "configs[1]: MulticlassConfusionMatrix num_classes=1000, 2^24-sample int64 batches",
+                       "samples_per_step_per_gpu": BATCH, "validate_args": False,
+                       "l2_policy": "inputs larger than L2: 268 MB read per step, two alternating batches (L2 126 MB)",
+                       "api": "torchmetrics_b200.MulticlassConfusionMatrix.update"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
+            "cpu_baseline": cpu_baseline, "extra": extra,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -181,3 +181,24 @@ def test_sync_state_restatement():
     _eq(O.sync_state(a, "sum"), a[0] + a[1])
     b = [np.ones((2,)), np.ones((3,)) * 2]
     _eq(O.sync_state(b, "cat"), [1, 1, 2, 2, 2])
+
+
+# ---------------------------------------------------------------- C/OpenMP restatement (timed CPU baseline)
+def test_c_oracle_against_golden_and_numpy():
+    from oracle import oracle_c as OC
+
+    assert OC.num_threads() >= 1
+    for c in load_golden("confusion_matrix"):
+        if c.meta["kind"] == "multiclass_labels" and c.meta["ignore_index"] is None:
+            _eq(OC.confmat_update(c["preds"], c["target"], c.meta["num_classes"]), c["confmat"])
+    with pytest.raises(RuntimeError):
+        OC.confmat_update(np.array([0, 1]), np.array([1, 5]), 5)
+    for c in load_golden("binned_curve"):
+        if c.meta["kind"] in ("binary_probs", "binary_grid", "binary_special") and c.meta["ignore_index"] is None:
+            _eq(OC.binned_update_loop(c["preds"], c["target"], c["thresholds"]), c["confmat"])
+    rng = np.random.default_rng(0)
+    p = rng.random((5000, 12)).astype(np.float32)
+    t = rng.integers(-1, 2, (5000, 12))
+    fp_, ft_ = O.multilabel_stat_scores_format(p[:, :, None], t[:, :, None], 12, 0.37, -1)
+    tp, fp, tn, fn = O.multilabel_stat_scores_update(fp_, ft_)
+    _eq(OC.multilabel_stats(p, t, 0.37, -1), np.stack([tp, fp, tn, fn]))
