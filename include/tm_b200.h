@@ -120,6 +120,30 @@ TMB_API int tmb_binned_curve_update(const void* preds_dev, int preds_dtype, cons
                             int32_t* status_dev, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * K3 without any allocation.  This entry point has no counterpart in the reference.
+ * Same computation and arguments as tmb_binned_curve_update, minus the workspace: the scratch is a fixed
+ * TMB_BINNED_STATIC_SCRATCH_BYTES array built into the library (each GPU that loads the library keeps it until the
+ * process exits), and the call performs no cudaMalloc / cudaFree and uses no allocating routine.  It is for callers
+ * that cannot allocate device memory when they update a curve: loops that forbid allocation after warm-up because
+ * cudaMalloc / cudaFree stall the whole device, processes whose device memory already belongs to another pool, and
+ * bindings that only ever receive pointers and have no device allocator to call.
+ * Limit: num_columns * 2 * (num_thresholds + 1) * 8 + 32 bytes must fit the array (binary curve: up to 4093
+ * thresholds; T = 200: up to 20 columns); larger problems return TMB_ERR_TOO_LARGE with an explanatory
+ * tmb_last_cuda_error() text.
+ * The first call on a device looks up the array's device address (cudaGetSymbolAddress); make that first call
+ * before starting any stream capture on the device.  All calls on a device share the one array and the call clears
+ * the part it uses before launching, so two calls that may overlap on the GPU (different streams, different host
+ * threads) race with each other: serialise them, or give the overlapping ones tmb_binned_curve_update with their
+ * own workspaces.
+ * ------------------------------------------------------------------------------------------- */
+#define TMB_BINNED_STATIC_SCRATCH_BYTES 65536
+TMB_API int tmb_binned_curve_update_static(const void* preds_dev, int preds_dtype, const void* target_dev,
+                                           int target_dtype, int64_t n_rows, int64_t num_columns,
+                                           int target_is_class_index, const float* thresholds_dev, int num_thresholds,
+                                           int has_ignore, int64_t ignore_index, int prob_mode, int64_t* confmat_dev,
+                                           int32_t* status_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * K4  exact binary curve: descending sort of the scores + cumulative counts at every distinct score.
  * Replaces: functional/classification/precision_recall_curve.py:28-80 `_binary_clf_curve` (no sample weights):
  *           torch.argsort, two gathers, the `torch.where` compaction with its host sync, and the float32 cumsum.

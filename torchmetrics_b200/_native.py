@@ -51,6 +51,9 @@ _SIGNATURES = {
     "tmb_binned_curve_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                            _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int64, _c.c_int,
                                            _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p, _c.c_void_p]),
+    "tmb_binned_curve_update_static": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
+                                                  _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int64, _c.c_int,
+                                                  _c.c_void_p, _c.c_void_p, _c.c_void_p]),
     "tmb_exact_curve_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_exact_curve": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_void_p,
                                    _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
@@ -313,3 +316,33 @@ def exact_curve(preds: Tensor, target: Tensor, pos_label: int = 1):
     _check(rc, "tmb_exact_curve")
     d = int(counts[1].item())  # the reference syncs at the same point (torch.where)
     return fps[:d], tps[:d], thr[:d]
+
+
+def binned_curve_update_static_(confmat: Tensor, preds: Tensor, target: Tensor, thresholds: Tensor,
+                                num_columns: int = 1, target_is_class_index: bool = False,
+                                ignore_index: Optional[int] = None, prob_mode: int = PROB_AUTO) -> None:
+    """`binned_curve_update_` for callers that must not allocate device memory: the kernel scratch is the fixed
+    64 KiB array inside libtm_b200 instead of a torch-allocated workspace (tmb_binned_curve_update_static).
+
+    The inputs must already be contiguous, aligned tensors of a kernel dtype, because this wrapper does not copy or
+    cast (that would allocate); problems whose counters do not fit the array raise.  Calls on one device share the
+    array, so do not let two of them overlap on the GPU.
+    """
+    dev = require_cuda(confmat, preds, target, thresholds)
+    T = thresholds.numel()
+    assert confmat.dtype == torch.int64 and confmat.is_contiguous() and confmat.numel() == T * num_columns * 4
+    assert thresholds.dtype == torch.float32 and thresholds.is_contiguous()
+    for t in (preds, target):
+        if not t.is_contiguous() or t.data_ptr() % 32 != 0:
+            raise ValueError("the allocation-free entry point needs contiguous, 32-byte aligned inputs")
+    n_rows = preds.numel() // num_columns
+    with torch.cuda.device(dev):
+        rc = load().tmb_binned_curve_update_static(
+            preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target), n_rows, num_columns,
+            bool(target_is_class_index), thresholds.data_ptr(), T, ignore_index is not None,
+            0 if ignore_index is None else int(ignore_index), prob_mode, confmat.data_ptr(),
+            scratch(dev).status.data_ptr(), _stream_ptr(dev))
+    if rc == -4:
+        raise RuntimeError("tmb_binned_curve_update_static failed with TMB_ERR_TOO_LARGE: "
+                           + load().tmb_last_cuda_error().decode())
+    _check(rc, "tmb_binned_curve_update_static")

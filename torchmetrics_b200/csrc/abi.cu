@@ -13,6 +13,8 @@ void set_cuda_error(cudaError_t e, const char* where) {
   cudaGetLastError();  // clear the sticky-less error so the next call starts clean
 }
 
+void set_error_text(const char* text) { g_last_error = text; }
+
 struct DevProps {
   int sms = 0;
   int smem_optin = 0;

@@ -20,6 +20,8 @@
 // exits at once unless the flag is up, in which case it redoes the batch with sigmoid(p) and pass 1's
 // partial histogram is discarded.
 #include <cstdlib>
+#include <mutex>
+#include <string>
 #include <type_traits>
 
 #include "common.cuh"
@@ -612,4 +614,58 @@ extern "C" int tmb_binned_curve_update(const void* preds, int preds_dtype, const
     TMB_DISPATCH_INT(target_dtype, TT, { return launch_binned<PT, TT>(P, prob_mode, st); })
   })
   return TMB_ERR_ARG;
+}
+
+// =================================================================================================
+// Entry point that allocates nothing (no counterpart in the reference)
+// =================================================================================================
+// Some callers of this library may not allocate device memory at the moment they want a curve update: an
+// evaluation or serving loop that forbids allocation after warm-up (cudaMalloc / cudaFree synchronise the whole
+// device and would stall every other stream), a process whose device memory is entirely owned by another pool so a
+// raw cudaMalloc would fail or fragment it, or a thin foreign-language binding that is only ever handed pointers and
+// has no device allocator of its own.  For them the kernel's scratch (flag, ticket, histogram) lives in this
+// fixed array, which every GPU that loads the library holds until the process exits.
+static __device__ __align__(256) unsigned char g_binned_static_scratch[TMB_BINNED_STATIC_SCRATCH_BYTES];
+
+namespace {
+// In host code the array's name is only a stand-in: the device address has to be asked for, once per device,
+// with that device current.
+std::mutex g_static_mu;
+void* g_static_addr[64] = {};
+}  // namespace
+
+extern "C" int tmb_binned_curve_update_static(const void* preds, int preds_dtype, const void* target,
+                                              int target_dtype, int64_t n_rows, int64_t num_columns,
+                                              int target_is_class_index, const float* thresholds, int num_thresholds,
+                                              int has_ignore, int64_t ignore_index, int prob_mode, int64_t* confmat,
+                                              int32_t* status, void* stream) {
+  if (num_thresholds < 1 || num_columns < 1) return TMB_ERR_ARG;
+  const size_t need = tmb_binned_curve_workspace_bytes(num_thresholds, num_columns);
+  if (need > (size_t)TMB_BINNED_STATIC_SCRATCH_BYTES) {
+    std::string msg = "tmb_binned_curve_update_static: num_columns * 2 * (num_thresholds + 1) counters need " +
+                      std::to_string(need) + " bytes of scratch but the built-in array holds " +
+                      std::to_string((size_t)TMB_BINNED_STATIC_SCRATCH_BYTES) +
+                      "; use tmb_binned_curve_update with a caller-provided workspace";
+    set_error_text(msg.c_str());
+    return TMB_ERR_TOO_LARGE;
+  }
+  int dev = 0;
+  TMB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return TMB_ERR_ARG;
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_addr[dev]) {
+      // first call on this device: resolve the device address of the array (do this before any stream capture)
+      void* p = nullptr;
+      TMB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_binned_static_scratch));
+      g_static_addr[dev] = p;
+    }
+    scratch = g_static_addr[dev];
+  }
+  // the array keeps whatever the previous call left behind; flag, ticket and histogram must start at zero
+  TMB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, need, (cudaStream_t)stream));
+  return tmb_binned_curve_update(preds, preds_dtype, target, target_dtype, n_rows, num_columns, target_is_class_index,
+                                 thresholds, num_thresholds, has_ignore, ignore_index, prob_mode, confmat, scratch,
+                                 (size_t)TMB_BINNED_STATIC_SCRATCH_BYTES, status, stream);
 }

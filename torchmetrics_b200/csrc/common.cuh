@@ -16,6 +16,7 @@ using u32 = unsigned int;
 
 // ---- host side -------------------------------------------------------------------------------
 void set_cuda_error(cudaError_t e, const char* where);
+void set_error_text(const char* text);  // message returned by tmb_last_cuda_error() for non-CUDA failures
 int sm_count();            // cached per device
 int max_optin_smem();      // cached per device (bytes)
 
