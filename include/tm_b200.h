@@ -82,11 +82,23 @@ TMB_API int tmb_sm_count(void);
  *           `_binary_confusion_matrix_update` (:149-153, C = 2).
  * preds_dev/target_dev: n labels of the given integer dtype.  confmat_dev: C*C int64, row = target.
  * Keys outside [0, C*C) set TMB_STATUS_LABEL_RANGE and are not counted (the reference raises).
- * algo: 0 = choose by C; 1 = global 64-bit RED straight into confmat_dev; 2 = shared-memory privatised.
+ * algo: 0 = choose by C; 1 = global 64-bit RED straight into confmat_dev (lanes holding the same cell are merged
+ *       first when a warp looks concentrated); 2 = shared-memory privatised; 3/4/5 = RED variants for tuning.
  * ------------------------------------------------------------------------------------------- */
 TMB_API int tmb_confmat_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype, int64_t n,
                        int64_t num_classes, int has_ignore, int64_t ignore_index, int64_t* confmat_dev,
                        int32_t* status_dev, int algo, void* stream);
+
+/* K1 for large C through a bucket partition (phase A: queue 12-bit local bins per bucket, phase B: per-bucket
+ * shared-memory histograms) instead of one L2 RED per sample; same contract and result as tmb_confmat_update.
+ * Serves ceil(C*C / 4096) <= 1024 buckets (C <= 2048) and n < 2^32.  workspace_dev: at least
+ * tmb_confmat_workspace_bytes(n, C) bytes (more = roomier queues), contents irrelevant; samples that do not fit a
+ * bucket's queue are still counted, through the slower direct RED.  Not for launches that overlap on one workspace. */
+TMB_API size_t tmb_confmat_workspace_bytes(int64_t n, int64_t num_classes);
+TMB_API int tmb_confmat_update_ws(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
+                                  int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index,
+                                  int64_t* confmat_dev, int32_t* status_dev, void* workspace_dev,
+                                  size_t workspace_bytes, void* stream);
 
 /* Plain histogram: out_dev[x[i]] += 1 for x[i] in [0, num_bins); values outside set TMB_STATUS_LABEL_RANGE.
  * Replaces: utilities/data.py:179-207 `_bincount` (torch.bincount and its deterministic-mode mesh fallback). */

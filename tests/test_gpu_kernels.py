@@ -25,7 +25,7 @@ def _np(t):
 # =========================================================================== K1 confusion matrix
 @pytest.mark.parametrize("c", [c for c in load_golden("confusion_matrix") if c.meta["kind"] == "multiclass_labels"],
                          ids=case_id)
-@pytest.mark.parametrize("algo", [0, 1, 2])
+@pytest.mark.parametrize("algo", [0, 1, 2, 6])
 def test_confmat_golden(c, algo):
     N = _native()
     C = c.meta["num_classes"]
@@ -68,6 +68,34 @@ def test_confmat_diagonal_heavy_and_single_cell():
             cm = torch.zeros(CC, CC, dtype=torch.int64, device=DEV)
             N.confmat_update_(cm, pp2.to(DEV), tt2.to(DEV), CC, algo=algo)
             assert np.array_equal(_np(cm), O.multiclass_confusion_matrix_update(pp2.numpy(), tt2.numpy(), CC))
+
+
+@pytest.mark.parametrize("C", [2, 64, 65, 1000, 2048])
+@pytest.mark.parametrize("n", [1, 8191, 8192, 8193, (1 << 21) + 3])
+def test_confmat_partition_path(C, n):
+    """algo 6 (bucket partition + shared-memory histograms): uniform, diagonal-heavy, single-cell (queue overflow)
+    and ignore_index inputs must all give the oracle's matrix."""
+    N = _native()
+    g = torch.Generator().manual_seed(C * 13 + n)
+    t = torch.randint(0, C, (n,), generator=g)
+    uniform = torch.randint(0, C, (n,), generator=g)
+    diag = torch.where(torch.rand(n, generator=g) < 0.8, t, uniform)
+    hot_t = torch.where(torch.rand(n, generator=g) < 0.9, torch.full((n,), C - 1), t)
+    for p, tt, ii in [(uniform, t, None), (diag, t, None), (torch.full((n,), C - 1), hot_t, None), (uniform, t, 0)]:
+        cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+        N.confmat_update_(cm, p.to(DEV), tt.to(DEV), C, ii, algo=6)
+        N.confmat_update_(cm, p.to(DEV), tt.to(DEV), C, ii, algo=6)  # accumulates, workspace reused
+        pp, tf = O.multiclass_confusion_matrix_format(p.numpy(), tt.numpy(), ii)
+        assert np.array_equal(_np(cm), 2 * O.multiclass_confusion_matrix_update(pp, tf, C))
+    assert N.read_status(torch.device(DEV)) == 0
+    # out-of-range labels are flagged, in-range ones still counted
+    if n > 4:
+        bad_t = t.clone()
+        bad_t[3] = C
+        cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+        N.confmat_update_(cm, uniform.to(DEV), bad_t.to(DEV), C, algo=6)
+        assert int(cm.sum()) == n - 1
+        assert N.read_status(torch.device(DEV)) == N.STATUS_LABEL_RANGE
 
 
 def test_confmat_out_of_range_sets_status():

@@ -37,23 +37,29 @@ def report(name, nbytes, med, best, nsamples):
 
 
 def bench_confmat():
-    for C, n in [(1000, 1 << 24), (1000, 1 << 26), (100, 1 << 24), (10, 1 << 24), (5, 1 << 24)]:
+    for C, n in [(1000, 1 << 24), (1000, 1 << 26), (1000, 1 << 22), (1000, 1 << 20), (150, 1 << 24), (100, 1 << 24), (10, 1 << 24), (5, 1 << 24)]:
         g = torch.Generator(device=DEV).manual_seed(1)
         p = torch.randint(0, C, (n,), device=DEV, generator=g)
         t = torch.randint(0, C, (n,), device=DEV, generator=g)
         cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
-        algos = [1, 3, 4, 5] if C * C * 4 > 200 * 1024 else [1, 2]
+        algos = [1, 3, 6] if C * C * 4 > 200 * 1024 else [1, 2, 6]
         for algo in algos:
             med, best = timeit(lambda: N.confmat_update_(cm, p, t, C, algo=algo))
             report(f"confmat C={C} n=2^{n.bit_length()-1} i64 uniform algo={algo}", n * 16, med, best, n)
         if C == 1000 and n == 1 << 24:
             p2 = torch.where(torch.rand(n, device=DEV) < 0.8, t, p)
-            for algo in [1, 5]:
+            for algo in [1, 6]:
                 med, best = timeit(lambda: N.confmat_update_(cm, p2, t, C, algo=algo))
                 report(f"confmat C={C} n=2^24 i64 diag-heavy algo={algo}", n * 16, med, best, n)
             p3, t3 = p.int(), t.int()
-            med, best = timeit(lambda: N.confmat_update_(cm, p3, t3, C, algo=1))
-            report(f"confmat C={C} n=2^24 i32 uniform algo=1", n * 8, med, best, n)
+            for algo in [1, 6]:
+                med, best = timeit(lambda: N.confmat_update_(cm, p3, t3, C, algo=algo))
+                report(f"confmat C={C} n=2^24 i32 uniform algo={algo}", n * 8, med, best, n)
+            t4 = torch.where(torch.rand(n, device=DEV) < 0.5, torch.zeros_like(t), t)
+            p4 = torch.where(torch.rand(n, device=DEV) < 0.9, t4, p)
+            for algo in [1, 6]:
+                med, best = timeit(lambda: N.confmat_update_(cm, p4, t4, C, algo=algo), iters=5)
+                report(f"confmat C={C} n=2^24 i64 half-in-one-cell algo={algo}", n * 16, med, best, n)
             # reference-on-cuda comparator (ATen): key materialisation + bincount
             med, best = timeit(lambda: torch.bincount(t * C + p, minlength=C * C), iters=5)
             report("torch: bincount(t*C+p) [reference's ops on cuda]", n * 16, med, best, n)

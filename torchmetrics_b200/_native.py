@@ -43,6 +43,9 @@ _SIGNATURES = {
     "tmb_sm_count": (_c.c_int, []),
     "tmb_confmat_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_int,
                                       _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_void_p]),
+    "tmb_confmat_workspace_bytes": (_c.c_size_t, [_c.c_int64, _c.c_int64]),
+    "tmb_confmat_update_ws": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_int,
+                                         _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
     "tmb_bincount_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_void_p,
                                        _c.c_void_p]),
     "tmb_match_count_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int,
@@ -220,6 +223,20 @@ def confmat_update_(confmat: Tensor, preds: Tensor, target: Tensor, num_classes:
     assert confmat.dtype == torch.int64 and confmat.is_contiguous() and confmat.numel() == num_classes * num_classes
     preds, target = as_kernel_labels(preds.reshape(-1)), as_kernel_labels(target.reshape(-1))
     assert preds.numel() == target.numel()
+    n = preds.numel()
+    cc = num_classes * num_classes
+    # large matrices and large batches: bucket partition + shared-memory histograms (algo 6); else direct kernels
+    if algo == 6 or (algo == 0 and cc > 51200 and cc <= 4096 * 1024 and (1 << 23) <= n < (1 << 32)):
+        lib = load()
+        sc = scratch(dev)
+        ws = sc.workspace("confmat", lib.tmb_confmat_workspace_bytes(n, num_classes), dev)
+        with torch.cuda.device(dev):
+            rc = lib.tmb_confmat_update_ws(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                           n, num_classes, ignore_index is not None,
+                                           0 if ignore_index is None else int(ignore_index), confmat.data_ptr(),
+                                           sc.status.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+        _check(rc, "tmb_confmat_update_ws")
+        return
     with torch.cuda.device(dev):
         rc = load().tmb_confmat_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
                                        preds.numel(), num_classes, ignore_index is not None,

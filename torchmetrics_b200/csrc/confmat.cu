@@ -29,6 +29,24 @@ __device__ __forceinline__ bool make_key(PT p, TT t, long long C, long long CC, 
 // ---- large C: global RED ---------------------------------------------------------------------
 // one RED per sample; AGG: lanes of a warp holding the same key are merged first (match.any), which pays when
 // the data are concentrated on few cells (diagonal-heavy confusion matrices) and costs ~10% when they are not
+// Default policy: plain REDs, unless the warp looks concentrated.  The probe compares every lane's key with its
+// neighbour's (one shuffle): uniform data almost never has 4 equal neighbours among 32 lanes, while a cell holding a
+// third of the samples has ~3.5 on average and a dominant one far more; only then is the match.any merge paid.
+__device__ __forceinline__ void global_count_adaptive(u64* confmat, long long key, bool valid) {
+  const unsigned lane = threadIdx.x & 31;
+  const long long nb = __shfl_sync(0xffffffffu, key, (lane + 1) & 31);
+  const unsigned eq = __ballot_sync(0xffffffffu, valid && nb == key);
+  if (__popc(eq) >= 4) {
+    const unsigned active = __ballot_sync(0xffffffffu, valid);
+    if (valid) {
+      const unsigned peers = __match_any_sync(active, (unsigned long long)key);
+      if ((int)lane == __ffs(peers) - 1) atomicAdd(confmat + key, (u64)__popc(peers));
+    }
+  } else if (valid) {
+    atomicAdd(confmat + key, 1ULL);
+  }
+}
+
 template <bool AGG>
 __device__ __forceinline__ void global_count(u64* confmat, long long key, bool valid) {
   if constexpr (AGG) {
@@ -42,7 +60,7 @@ __device__ __forceinline__ void global_count(u64* confmat, long long key, bool v
   }
 }
 
-template <typename PT, typename TT, int UNROLL, int MINB, bool AGG>
+template <typename PT, typename TT, int UNROLL, int MINB, int AGG>  // AGG: 0 never, 1 always, 2 adaptive
 __global__ void __launch_bounds__(kConfmatThreads, MINB)
 confmat_global_kernel(const PT* __restrict__ preds, const TT* __restrict__ target, long long n, long long C,
                       int has_ignore, long long ignore, u64* __restrict__ confmat, int* __restrict__ status) {
@@ -71,7 +89,8 @@ confmat_global_kernel(const PT* __restrict__ preds, const TT* __restrict__ targe
       for (int j = 0; j < 4; ++j) {
         long long key = 0;
         const bool valid = in && make_key(p[u].v[j], t[u].v[j], C, CC, has_ignore, ignore, key, bad);
-        global_count<AGG>(confmat, key, valid);
+        if constexpr (AGG == 2) global_count_adaptive(confmat, key, valid);
+        else global_count<AGG == 1>(confmat, key, valid);
       }
     }
   }
@@ -221,25 +240,25 @@ static int launch_confmat(const PT* preds, const TT* target, long long n, long l
   const long long CC = C * C;
   const size_t smem = (size_t)CC * sizeof(u32);
   const bool fits = smem <= (size_t)max_optin_smem() - 1024;
-  if (algo == 0) algo = (fits && CC <= 16384) ? 2 : 1;
+  if (algo == 0) algo = (fits && CC <= 51200) ? 2 : 1;  // <= 200 KB of u32 bins: one privatised copy per CTA
   if (algo == 2 && !fits) return TMB_ERR_TOO_LARGE;
   const long long nvec = n >> 2;
   if (algo == 1) {
     // 4 resident CTAs of 256 threads per SM, 2 groups of 4 samples in flight per thread
     int grid = grid_for((nvec + 1) / 2, kConfmatThreads, 4);
-    confmat_global_kernel<PT, TT, 2, 4, false><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+    confmat_global_kernel<PT, TT, 2, 4, 2><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
                                                                                  ignore, confmat, status);
   } else if (algo == 3) {
-    int grid = grid_for((nvec + 3) / 4, kConfmatThreads, 3);
-    confmat_global_kernel<PT, TT, 4, 3, false><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+    int grid = grid_for((nvec + 1) / 2, kConfmatThreads, 4);
+    confmat_global_kernel<PT, TT, 2, 4, 0><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
                                                                                  ignore, confmat, status);
   } else if (algo == 4) {
     int grid = grid_for(nvec, kConfmatThreads, 8);
-    confmat_global_kernel<PT, TT, 1, 8, false><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+    confmat_global_kernel<PT, TT, 1, 8, 0><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
                                                                                  ignore, confmat, status);
   } else if (algo == 5) {
     int grid = grid_for((nvec + 1) / 2, kConfmatThreads, 4);
-    confmat_global_kernel<PT, TT, 2, 4, true><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
+    confmat_global_kernel<PT, TT, 2, 4, 1><<<grid, kConfmatThreads, 0, st>>>(preds, target, n, C, has_ignore,
                                                                                 ignore, confmat, status);
   } else if (algo != 2) {
     return TMB_ERR_ARG;
