@@ -110,3 +110,22 @@ if __name__ == "__main__":
         bench_binned()
     if what in ("stat", "all"):
         bench_stat()
+
+
+def bench_exact():
+    for n in [1 << 20, 1 << 24, 1 << 26]:
+        g = torch.Generator(device=DEV).manual_seed(1)
+        preds = torch.rand(n, device=DEV, generator=g)
+        target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
+        med, best = timeit(lambda: N.exact_curve(preds, target, 1), iters=5)
+        report(f"exact_curve n=2^{n.bit_length()-1} f32+i64 (sort+scan, incl. D sync)", n * 12, med, best, n)
+        med, best = timeit(lambda: torch.sort(preds, descending=True), iters=5)
+        report(f"torch.sort(preds) alone [CUB radix sort, keys+indices]", n * 12, med, best, n)
+        import torchmetrics_b200.functional as F
+        med, best = timeit(lambda: F.binary_auroc(preds, target, thresholds=None, validate_args=False), iters=3)
+        report(f"binary_auroc(thresholds=None) n=2^{n.bit_length()-1} end to end", n * 12, med, best, n)
+        del preds, target
+
+
+if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "exact"):
+    bench_exact()

@@ -157,8 +157,17 @@ __global__ void __launch_bounds__(kSortThreads) k4_scatter(const u32* __restrict
     key[r] = in ? keys_in[i] : 0u;
     lab[r] = in ? labs_in[i] : 0;
     const u32 d = (key[r] >> shift) & 0xff;
-    // slots past the end of the input (last tile only) match nobody and take no rank
-    const unsigned peers = __match_any_sync(0xffffffffu, in ? d : (0x100u + lane));
+    // lanes holding the same digit: eight ballots (one per digit bit) instead of match.any, whose cost grows with
+    // the number of distinct values in the warp (~30 of 256 here) and measured 10x slower than shared-memory atomics.
+    // Slots past the end of the input (last tile only) match nobody and take no rank.
+    unsigned peers = __ballot_sync(0xffffffffu, in);
+#pragma unroll
+    for (int bit = 0; bit < 8; ++bit) {
+      const bool one = (d >> bit) & 1u;
+      const unsigned vote = __ballot_sync(0xffffffffu, one);
+      peers &= one ? vote : ~vote;
+    }
+    if (!in) peers = 1u << lane;
     u32 before = 0;
     if (in) {
       before = warp_cnt[warp][d];
@@ -206,13 +215,18 @@ __global__ void __launch_bounds__(kSortThreads) k4_scatter(const u32* __restrict
     }
   }
   __syncthreads();
-  // coalesced write-out: consecutive threads hold consecutive positions of the same digit run
+  // coalesced write-out: consecutive threads hold consecutive positions of the same digit run.  The destination of
+  // digit d's run (global digit base + this tile's offset inside the digit - its start in the staged tile) is
+  // fetched once per digit, not once per key.
+  __shared__ long long s_dst[kRadix];
+  s_dst[tid] = (long long)bases[tid] + table[(long long)tid * ntiles + blockIdx.x] - (long long)digit_start[tid];
+  __syncthreads();
   const long long remaining = n - base;
   const int valid = remaining < kSortTile ? (int)remaining : kSortTile;
+#pragma unroll 4
   for (int pos = tid; pos < valid; pos += kSortThreads) {
     const u32 k = s_keys[pos];
-    const u32 d = (k >> shift) & 0xff;
-    const long long dst = (long long)bases[d] + table[(long long)d * ntiles + blockIdx.x] + (pos - digit_start[d]);
+    const long long dst = s_dst[(k >> shift) & 0xff] + pos;
     keys_out[dst] = k;
     labs_out[dst] = s_labs[pos];
   }
@@ -309,19 +323,35 @@ __global__ void __launch_bounds__(kSortThreads) k4_emit(const u32* __restrict__ 
                                                         const u64* __restrict__ tile_pos, const u64* __restrict__ tile_ends,
                                                         long long* __restrict__ fps, long long* __restrict__ tps,
                                                         float* __restrict__ thr) {
-  // blocked arrangement: thread t owns items [t*16, t*16+16) of the tile so its running sums are sequential
+  // The tile (+ the first key of the next tile) is staged in shared memory with coalesced loads; thread t then owns
+  // items [t*16, t*16+16) so its running sums are sequential.  Row stride 17 words keeps the blocked reads
+  // conflict-free (bank = (17*t + r) % 32).
+  __shared__ u32 s_key[kSortThreads * (kSortItems + 1) + 1];
+  __shared__ unsigned char s_lab[kSortTile];
   __shared__ u32 wp[kSortWarps], we[kSortWarps];
-  const long long base = (long long)blockIdx.x * kSortTile + (long long)threadIdx.x * kSortItems;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long tbase = (long long)blockIdx.x * kSortTile;
+  for (int j = tid; j <= kSortTile; j += kSortThreads) {
+    const long long i = tbase + j;
+    const u32 k = i < n ? keys[i] : 0u;
+    s_key[(j / kSortItems) * (kSortItems + 1) + (j % kSortItems)] = k;
+    if (j < kSortTile) s_lab[j] = i < n ? labs[i] : 0;
+  }
+  __syncthreads();
+  const u32* mk = s_key + tid * (kSortItems + 1);
+  const u32 next_first = s_key[((tid + 1) * kSortItems / kSortItems) * (kSortItems + 1)];  // item 0 of thread t+1
+  const long long base = tbase + (long long)tid * kSortItems;
   u32 lp[kSortItems];
   bool le[kSortItems];
   u32 tp = 0, te = 0;
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
-    long long i = base + r;
-    bool in = i < n;
-    lp[r] = in ? labs[i] : 0;
-    le[r] = in ? run_end(keys, i, n) : false;
+    const long long i = base + r;
+    const bool in = i < n;
+    lp[r] = in ? s_lab[tid * kSortItems + r] : 0;
+    const u32 nxt = r + 1 < kSortItems ? mk[r + 1] : next_first;
+    // run end  <=>  last element, or score differs from the next one (float compare: -0.0 == 0.0, NaN != x)
+    le[r] = in && (i == n - 1 || (key_to_float(mk[r]) - key_to_float(nxt)) != 0.0f);
     tp += lp[r];
     te += le[r];
   }
@@ -335,18 +365,32 @@ __global__ void __launch_bounds__(kSortThreads) k4_emit(const u32* __restrict__ 
   __syncthreads();
   u32 addp = 0, adde = 0;
   for (int w = 0; w < warp; ++w) { addp += wp[w]; adde += we[w]; }
-  u64 run_pos = tile_pos[blockIdx.x] + addp + xp - tp;   // positives strictly before this thread's first item
-  u64 run_end_cnt = tile_ends[blockIdx.x] + adde + xe - te;
+  // compact this tile's run ends in shared memory (position in tile + positives so far in tile), then write the
+  // three output arrays with consecutive threads on consecutive rows
+  __shared__ unsigned short s_idx[kSortTile];
+  __shared__ unsigned short s_cum[kSortTile];
+  u32 local_pos = addp + xp - tp;   // positives of this tile strictly before this thread's first item
+  u32 slot = adde + xe - te;        // run ends of this tile before this thread
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
-    long long i = base + r;
-    run_pos += lp[r];
+    local_pos += lp[r];
     if (le[r]) {
-      tps[run_end_cnt] = (long long)run_pos;
-      fps[run_end_cnt] = (long long)(i + 1) - (long long)run_pos;
-      thr[run_end_cnt] = key_to_float(keys[i]);
-      ++run_end_cnt;
+      s_idx[slot] = (unsigned short)(tid * kSortItems + r);
+      s_cum[slot] = (unsigned short)local_pos;  // <= 4096 fits
+      ++slot;
     }
+  }
+  __shared__ u32 s_nend;
+  if (tid == kSortThreads - 1) s_nend = slot;
+  __syncthreads();
+  const u32 nend = s_nend;
+  const u64 pos0 = tile_pos[blockIdx.x], out0 = tile_ends[blockIdx.x];
+  for (u32 e = tid; e < nend; e += kSortThreads) {
+    const u32 j = s_idx[e];
+    const long long tpv = (long long)(pos0 + s_cum[e]);
+    tps[out0 + e] = tpv;
+    fps[out0 + e] = tbase + j + 1 - tpv;
+    thr[out0 + e] = key_to_float(s_key[(j / kSortItems) * (kSortItems + 1) + (j % kSortItems)]);
   }
 }
 
