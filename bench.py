@@ -93,6 +93,8 @@ def run_reference(args, rank, world):
 
     from oracle import oracle_c as OC
 
+    # torchrun exports OMP_NUM_THREADS=1 to its children; the CPU arm is meant to use every host core
+    OC.set_num_threads(os.cpu_count() or 1)
     rng = np.random.default_rng(1234)
     batches = [(rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)) for _ in range(2)]
     state = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)
@@ -200,10 +202,10 @@ def main():
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("confmat_global_kernel_bytes_per_launch")
+            traffic = json.load(f).get("confmat_partition_plus_hist_bytes_per_update")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "confmat_global_kernel<int64,int64>", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "confmat_partition_kernel<int64,int64> + confmat_bucket_hist_kernel (2 launches per update)", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": BATCH * BYTES_PER_SAMPLE, "kernel_ms": kernel_ms,
                 "frac_of_nominal_8TBps": achieved / 8000.0}
@@ -254,7 +256,7 @@ def main():
     del host, dbuf, m2
     # the sampler covers all three timed regions above (device-resident steps, kernel-only loop, e2e)
     clocks = sampler.stop() if rank == 0 else None
-    gpu_launches = args.steps  # one confmat_global_kernel per update in the timed region
+    gpu_launches = 2 * args.steps  # partition + bucket-histogram kernel per update in the timed region
 
     # ------------------------------------------------------------------ extra: binned AUROC+AP (config 3) and sync
     extra = {}
@@ -306,7 +308,74 @@ def main():
                 "binned_6.4KB_one_allreduce": sync_us(coll.__getitem__("BinaryAUROC", copy_state=False)),
                 "note": "median host-timed Metric.sync() incl. stream sync, max over ranks",
             }
-        del preds, target
+        del preds, target, coll
+        torch.cuda.empty_cache()
+
+        # configs[4]: MetricCollection of multilabel StatScores / Precision / Recall / F1, L = 100, 2^23 rows per rank
+        L, rows = 100, 1 << 23
+        g3 = torch.Generator(device=dev).manual_seed(7 + rank)
+        mp = torch.rand(rows, L, device=dev, generator=g3)
+        mt = torch.randint(0, 2, (rows, L), device=dev, generator=g3)
+        mcoll = tm.MetricCollection([tm.MultilabelStatScores(num_labels=L, validate_args=False),
+                                     tm.MultilabelPrecision(num_labels=L, validate_args=False),
+                                     tm.MultilabelRecall(num_labels=L, validate_args=False),
+                                     tm.MultilabelF1Score(num_labels=L, validate_args=False)]).to(dev)
+        for _ in range(2):
+            mcoll.update(mp, mt)
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 5
+        c0.record()
+        for _ in range(reps):
+            mcoll.update(mp, mt)
+        c1.record()
+        barrier()
+        cms = max_over_ranks(c0.elapsed_time(c1)) / reps
+        mcoll.compute()  # warm-up (lazy kernel loading of the small torch reducers)
+        mcoll.update(mp, mt)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = mcoll.compute()
+        torch.cuda.synchronize()
+        compute_ms = (time.perf_counter() - t0) * 1e3
+        extra["multilabel_collection_L100"] = {
+            "workload": "configs[4]: MetricCollection[MultilabelStatScores, Precision, Recall, F1] num_labels=100, "
+                        "2^23-row batches per rank (weak), one compute group => one K2 pass per update",
+            "value": rows * world / (cms * 1e-3), "unit": "samples/s", "ms_per_update": cms,
+            "achieved_GBps_per_gpu": rows * L * 12 / (cms * 1e-3) / 1e9,
+            "frac_of_measured_peak": rows * L * 12 / (cms * 1e-3) / 1e9 / peak,
+            "compute_ms_incl_sync": compute_ms, "compute_groups": len(mcoll.compute_groups),
+            "f1_macro": float(res["MultilabelF1Score"]),
+        }
+        del mp, mt, mcoll
+        torch.cuda.empty_cache()
+
+        # configs[3]: BinaryAUROC(thresholds=None), 2^26 scores in total; cat states gathered, sort + scan on every rank
+        n_exact = (1 << 26) // world
+        g4 = torch.Generator(device=dev).manual_seed(11 + rank)
+        ep = torch.rand(n_exact, device=dev, generator=g4)
+        et = (torch.rand(n_exact, device=dev, generator=g4) < 0.3 + 0.4 * ep).long()
+        em = tm.BinaryAUROC(thresholds=None, validate_args=False).to(dev)
+        em.update(ep, et)  # full-size warm-up: the caching allocator has to grow by ~2 GB the first time
+        em.compute()
+        em.reset()
+        barrier()
+        t0 = time.perf_counter()
+        em.update(ep, et)
+        torch.cuda.synchronize()
+        upd_ms = (time.perf_counter() - t0) * 1e3
+        barrier()
+        t0 = time.perf_counter()
+        val = float(em.compute())
+        torch.cuda.synchronize()
+        cmp_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+        extra["exact_auroc_2p26"] = {
+            "workload": "configs[3]: BinaryAUROC(thresholds=None), 2^26 fp32 scores in total, cat-state all_gather "
+                        "then radix sort + scan (K4) on every rank",
+            "update_ms": upd_ms, "compute_ms_incl_gather": cmp_ms, "value": (1 << 26) / (cmp_ms * 1e-3),
+            "unit": "samples/s (compute)", "auroc": val,
+        }
+        del ep, et, em
 
     # ------------------------------------------------------------------ CPU baseline (rank 0, N=1 only)
     cpu_baseline = None
@@ -315,6 +384,7 @@ def main():
 
         from oracle import oracle_c as OC
 
+        OC.set_num_threads(os.cpu_count() or 1)
         rng = np.random.default_rng(1234)
         p, t = rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)
         st = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)

@@ -18,6 +18,7 @@
 #include <string.h>
 
 int orc_num_threads(void) { return omp_get_max_threads(); }
+void orc_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 /* returns 0, or -1 when a key falls outside [0, C*C) (the reference raises there) */
 int orc_confmat_update(const int64_t* preds, const int64_t* target, int64_t n, int64_t C, int64_t* confmat /* C*C, += */) {

@@ -28,6 +28,10 @@ def num_threads() -> int:
     return load().orc_num_threads()
 
 
+def set_num_threads(n: int) -> None:
+    load().orc_set_num_threads(ctypes.c_int(int(n)))
+
+
 def confmat_update(preds, target, num_classes, out=None):
     preds = np.ascontiguousarray(preds, dtype=np.int64)
     target = np.ascontiguousarray(target, dtype=np.int64)
