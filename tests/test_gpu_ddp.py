@@ -1,0 +1,109 @@
+"""Cross-GPU synchronisation over NCCL (one process per GPU). Needs >= 2 GPUs; skipped otherwise.
+Run on a 2-GPU box with: gpurun --gpus 2 -- python -m pytest tests/test_gpu_ddp.py -m gpu -q"""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+pytestmark = pytest.mark.gpu
+WORLD = 2
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, port, body):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=WORLD, device_id=torch.device("cuda", rank))
+    try:
+        globals()[body](rank)
+        torch.cuda.synchronize()
+    finally:
+        dist.destroy_process_group()
+
+
+def _data(rank_or_all, n_per_rank):
+    """Deterministic per-rank shards; rank None -> everything, in rank order."""
+    out = []
+    for r in range(WORLD):
+        g = torch.Generator().manual_seed(100 + r)
+        n = n_per_rank + 17 * r  # uneven shards
+        p = torch.rand(n, generator=g)
+        t = (torch.rand(n, generator=g) < 0.3 + 0.4 * p).long()
+        lp = torch.randint(0, 1000, (n,), generator=g)
+        lt = torch.randint(0, 1000, (n,), generator=g)
+        out.append((p, t, lp, lt))
+    if rank_or_all is None:
+        return tuple(torch.cat([o[i] for o in out]) for i in range(4))
+    return out[rank_or_all]
+
+
+def _body_sum_and_cat_states(rank):
+    import numpy as np
+
+    import torchmetrics_b200 as tm
+    from oracle import oracle_np as O
+
+    dev = torch.device("cuda", rank)
+    p, t, lp, lt = (x.to(dev) for x in _data(rank, 50_000))
+    ap, at, alp, alt = _data(None, 50_000)
+
+    cm = tm.MulticlassConfusionMatrix(1000, validate_args=False).to(dev)
+    cm.update(lp, lt)
+    got = cm.compute()  # one packed all_reduce over NVLink
+    assert np.array_equal(got.cpu().numpy(), O.multiclass_confusion_matrix_update(alp.numpy(), alt.numpy(), 1000))
+    # local state restored after compute
+    assert int(cm.confmat.sum()) == lp.numel()
+
+    coll = tm.MetricCollection([tm.BinaryAUROC(thresholds=200), tm.BinaryAveragePrecision(thresholds=200)]).to(dev)
+    coll.update(p, t)
+    out = coll.compute()
+    thr = torch.linspace(0, 1, 200)
+    want = O.binary_precision_recall_curve_update_hist(ap.numpy(), at.numpy(), thr.numpy())
+    assert abs(float(out["BinaryAUROC"]) - float(O.binary_auroc_binned(want, thr.numpy()))) < 1e-6
+    assert abs(float(out["BinaryAveragePrecision"]) - float(O.binary_average_precision_binned(want, thr.numpy()))) < 1e-6
+
+    exact = tm.BinaryAUROC(thresholds=None).to(dev)
+    exact.update(p, t)  # uneven cat states: padded all_gather
+    val = float(exact.compute())
+    assert abs(val - float(O.binary_auroc_exact(ap.numpy(), at.numpy(), np.float64))) < 1e-6
+    assert isinstance(exact.preds, list) and exact.preds[0].numel() == p.numel()  # un-synced again
+
+
+def _body_multilabel_collection(rank):
+    import torchmetrics_b200 as tm
+
+    dev = torch.device("cuda", rank)
+    L = 100
+    g = torch.Generator().manual_seed(5)
+    allp = torch.rand(2 * 4096, L, generator=g)
+    allt = torch.randint(0, 2, (2 * 4096, L), generator=g)
+    mine = slice(rank * 4096, (rank + 1) * 4096)
+    mc = tm.MetricCollection([tm.MultilabelStatScores(num_labels=L), tm.MultilabelPrecision(num_labels=L),
+                              tm.MultilabelRecall(num_labels=L), tm.MultilabelF1Score(num_labels=L)]).to(dev)
+    mc.update(allp[mine].to(dev), allt[mine].to(dev))
+    mc.update(allp[mine].to(dev), allt[mine].to(dev))
+    out = mc.compute()
+    F = tm.functional
+    both_p, both_t = torch.cat([allp, allp]).to(dev), torch.cat([allt, allt]).to(dev)
+    assert torch.equal(out["MultilabelStatScores"], F.multilabel_stat_scores(both_p, both_t, L))
+    assert torch.allclose(out["MultilabelF1Score"], F.multilabel_f1_score(both_p, both_t, L), atol=1e-6)
+
+
+@pytest.mark.parametrize("body", ["_body_sum_and_cat_states", "_body_multilabel_collection"])
+def test_nccl_sync(body):
+    if torch.cuda.device_count() < WORLD:
+        pytest.skip("needs 2 GPUs")
+    mp.spawn(_worker, args=(_free_port(), body), nprocs=WORLD, join=True)
