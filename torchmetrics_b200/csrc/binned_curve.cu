@@ -5,14 +5,11 @@
 // float32 threshold values), a histogram over (T+1) x {neg,pos} bins is accumulated on chip, and a suffix
 // sum over bins in the last CTA turns it into the (T,2,2) state, which is added in place.
 //
-// Two accumulation strategies:
-//   * private  (one column, small T — the BinaryAUROC/AP(thresholds=200) case): every THREAD owns a
-//     private histogram of 8-bit counters in shared memory, word-interleaved so that lane l always hits
-//     bank l (address = word*NT + tid).  An increment is LDS + IADD + STS without any atomic and without
-//     bank conflicts; counters are folded into per-CTA 64-bit totals every <=252 samples per thread.
-//     Shared-memory atomics top out near 0.5 samples/clk/SM, this path needs ~2.5 to keep up with HBM.
-//   * atomic   (any number of columns / large T): u32 bins in shared memory (or u64 in global scratch when
-//     they do not fit) updated with atomics.
+// Two accumulation strategies, both on shared-memory atomics (measured at >1500 G increments/s chip-wide on B200):
+//   * warp histograms (one column of float32 scores — the BinaryAUROC/AP(thresholds=200) case): one u32 copy of
+//     the bins per warp, bins found arithmetically for evenly spaced thresholds;
+//   * generic (any number of columns, any score dtype): one copy of all columns' bins per CTA in shared memory, or
+//     u64 bins in global scratch when they do not fit.
 //
 // The all-or-nothing sigmoid of the reference's `_format` step (":183-184: if not torch.all((preds >= 0) *
 // (preds <= 1)): preds = preds.sigmoid()") is resolved on the device without a host round trip: pass 1
@@ -55,6 +52,7 @@ struct BinnedParams {
   BinnedWs* ws;
   int* status;
   int status_bit_on_oor;  // TMB_PROB_CHECK semantics: report instead of redoing
+  int hist_copies;        // warp-histogram kernel: copies of the bins per CTA
 };
 
 // ---- exact binning ------------------------------------------------------------------------------
@@ -150,10 +148,8 @@ __device__ void finalize_columns(const BinnedParams& P, u64* hist, u64* s_scan, 
 }
 
 // =================================================================================================
-// private-histogram kernel (one column, float32 scores)
+// shared pieces of the one-column kernels
 // =================================================================================================
-constexpr int kTilesPerFold = 62;  // 4 samples per thread per tile: 62*4 + 4 (ragged tail) <= 255
-
 enum : int { kModeAsIs = 0, kModeAsIsCheck = 1, kModeSigmoid = 2 };
 
 // Evenly spaced thresholds (what torch.linspace / an int `thresholds` argument produce) need no table walk:
@@ -185,47 +181,66 @@ __device__ __forceinline__ UniformMap detect_uniform(const float* s_thr, int T) 
   return u;
 }
 
-template <typename TT, int MODE, bool HAS_IGNORE, int MAXNT>
-__global__ void __launch_bounds__(MAXNT, 1) binned_private_kernel(const BinnedParams P) {
+// =================================================================================================
+// warp-histogram kernel (one column, float32 scores): shared-memory atomics on per-warp copies of the bins
+// =================================================================================================
+// Measured on B200 (profiles/r1_red_bench.log): shared-memory atomics sustain >1500 G increments/s chip-wide, four
+// times what this path needs.  One u32 copy of the 2*(T+1) bins per WARP keeps contention to same-bin lanes of one
+// warp, costs ~1.6 KB per warp at T = 200 and leaves room for 64 resident warps per SM, which is what hides the HBM
+// latency (a first version with per-THREAD 8-bit counters in 202 KB of shared memory ran 16 warps per SM and stopped
+// at 75 % of the HBM peak; this one reads at 97-106 % of the measured copy bandwidth from 2^26 samples up).
+// For large T the warps share fewer copies (copy = warp % copies) so that two CTAs still fit an SM.
+constexpr int kWarpHistThreads = 1024;
+constexpr size_t kWarpHistSmemBudget = 100 * 1024;
+
+static size_t warphist_fixed_bytes(int T) {
+  const int NB2 = 2 * (T + 1);
+  return (size_t)NB2 * 8 + (size_t)(T + 1) * 4 + kLutCells * 2 + 16;
+}
+// number of histogram copies per CTA (<= one per warp); 0 if not even one fits
+static int warphist_copies(int T) {
+  const size_t per = (size_t)2 * (T + 1) * 4;
+  if (warphist_fixed_bytes(T) + per > kWarpHistSmemBudget) return 0;
+  size_t c = (kWarpHistSmemBudget - warphist_fixed_bytes(T)) / per;
+  return (int)(c > kWarpHistThreads / 32 ? kWarpHistThreads / 32 : c);
+}
+
+template <typename TT, int MODE, bool HAS_IGNORE>
+__global__ void __launch_bounds__(kWarpHistThreads, 2) binned_warphist_kernel(const BinnedParams P) {
   constexpr bool CHECK = MODE == kModeAsIsCheck;
   constexpr bool SIGMOID = MODE == kModeSigmoid;
-  constexpr int PF = MAXNT > 768 ? 1 : MAXNT > 512 ? 2 : 3;  // tiles prefetched ahead (64 / 85 / 128 registers)
-  constexpr int NSLOT = PF + 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BinnedWs* ws = P.ws;
   if (P.only_if_flag && ws->flag_oor == 0) return;
 
-  const int NT = blockDim.x, tid = threadIdx.x;
+  const int NT = kWarpHistThreads, tid = threadIdx.x, warp = tid >> 5;
   const int T = P.T, NB = T + 1, NB2 = 2 * NB;
-  const int W = (NB2 + 3) >> 2;  // 32-bit words of 4 byte-counters per thread
-  u32* s_hist = reinterpret_cast<u32*>(smem_raw);
-  u64* s_acc = reinterpret_cast<u64*>(smem_raw + (size_t)W * NT * 4);
+  const int copies = P.hist_copies;
+  u32* s_hist = reinterpret_cast<u32*>(smem_raw);                       // [copies][NB2]
+  u64* s_acc = reinterpret_cast<u64*>(smem_raw + (((size_t)copies * NB2 * 4 + 7) & ~(size_t)7));  // finalize scratch
   float* s_thr = reinterpret_cast<float*>(s_acc + NB2);
   unsigned short* s_lut = reinterpret_cast<unsigned short*>(s_thr + NB);
   __shared__ int s_last;
 
-  for (int i = tid; i < W * NT; i += NT) s_hist[i] = 0;
-  for (int i = tid; i < NB2; i += NT) s_acc[i] = 0;
+  for (int i = tid; i < copies * NB2; i += NT) s_hist[i] = 0;
   BinMap m;
   const bool sorted = build_binning(P.thr, T, s_thr, s_lut, m);
   if (!sorted) {
     if (blockIdx.x == 0 && tid == 0) atomicOr(P.status, TMB_STATUS_THRESHOLD_ORDER);
-    return;  // uniform over the grid; workspace untouched
+    return;
   }
   const UniformMap um = detect_uniform(s_thr, T);
 
   const float* __restrict__ preds = static_cast<const float*>(P.preds);
   const TT* __restrict__ target = static_cast<const TT*>(P.target);
   const long long n = P.n_rows;
-  const long long tile_elems = (long long)NT * 4;
-  const long long nfull = n / tile_elems;
+  const long long nvec = n >> 2;
+  const long long stride = (long long)gridDim.x * NT;
   const long long ignore = P.ignore;
-  u32* const my = s_hist + tid;
+  u32* const my = s_hist + (warp % copies) * NB2;
   int oor = 0;
 
-  // (score, target) -> counter index, or increments nothing when ignored.  The four lookups of a vector read
-  // only the threshold tables, so they overlap; the four counter updates that follow are serial RMWs.
-  auto index_of = [&](float p, TT tv, u32& inc, auto uniform_tag) -> int {
+  auto count = [&](float p, TT tv, auto uniform_tag) {
     const long long tl = as_i64(tv);
     bool valid = true;
     if constexpr (HAS_IGNORE) valid = tl != ignore;
@@ -234,108 +249,43 @@ __global__ void __launch_bounds__(MAXNT, 1) binned_private_kernel(const BinnedPa
     int cnt;
     if constexpr (decltype(uniform_tag)::value) {
       const float x = fmaf(p - um.lo, um.inv_step, 0.5f);
-      const unsigned j = min(__float2uint_rz(x), um.jmax);  // saturating: negative / NaN -> 0
+      const unsigned j = min(__float2uint_rz(x), um.jmax);
       cnt = (int)j + (int)(p >= s_thr[j]);
     } else {
       cnt = bin_of(p, m, s_thr, s_lut);
     }
-    const int idx = cnt + (tl == 1 ? NB : 0);
-    inc = (u32)valid << ((idx & 3) << 3);
-    return idx;
-  };
-  auto bump = [&](int idx, u32 inc) {
-    u32* w = my + (idx >> 2) * NT;
-    *w += inc;
-  };
-
-  // fold every thread's byte counters into the CTA's 64-bit totals and clear them
-  auto fold = [&]() {
-    __syncthreads();
-    const int warp = tid >> 5, lane = tid & 31, nwarps = NT >> 5;
-    for (int r = warp; r < W; r += nwarps) {
-      u32* row = s_hist + r * NT;
-      u32 lo = 0, hi = 0;  // 2 x 16-bit fields each: bytes 0,2 and bytes 1,3
-      for (int j = lane; j < NT; j += 32) {
-        u32 v = row[j];
-        row[j] = 0;
-        lo += v & 0x00ff00ffu;
-        hi += (v >> 8) & 0x00ff00ffu;
-      }
-      u32 c0 = __reduce_add_sync(0xffffffffu, lo & 0xffffu);
-      u32 c2 = __reduce_add_sync(0xffffffffu, lo >> 16);
-      u32 c1 = __reduce_add_sync(0xffffffffu, hi & 0xffffu);
-      u32 c3 = __reduce_add_sync(0xffffffffu, hi >> 16);
-      if (lane < 4) {
-        int b = 4 * r + lane;
-        u32 c = lane == 0 ? c0 : lane == 1 ? c1 : lane == 2 ? c2 : c3;
-        if (b < NB2) s_acc[b] += c;
-      }
-    }
-    __syncthreads();
+    if (valid) atomicAdd(my + cnt + (tl == 1 ? NB : 0), 1u);
   };
 
   auto run = [&](auto uniform_tag) {
-    const long long first = blockIdx.x;
-    const int my_tiles = first < nfull ? (int)((nfull - 1 - first) / gridDim.x) + 1 : 0;
-    const long long adv = (long long)gridDim.x * tile_elems;
-    const float* pp = preds + first * tile_elems + (long long)tid * 4;
-    const TT* tp = target + first * tile_elems + (long long)tid * 4;
-    Vec4<float> pb[NSLOT];
-    Vec4<TT> tb[NSLOT];
+    long long it = 0;
+    for (long long g = (long long)blockIdx.x * NT + tid; g < nvec; g += stride, ++it) {
+      const Vec4<float> p = load4(preds + 4 * g);
+      const Vec4<TT> t = load4(target + 4 * g);
 #pragma unroll
-    for (int s = 0; s < PF; ++s)
-      if (s < my_tiles) {
-        pb[s] = load4(pp + s * adv);
-        tb[s] = load4(tp + s * adv);
-      }
-    int since_fold = 0;
-    bool stop = false;
-    for (int k = 0; k < my_tiles && !stop; k += NSLOT) {
-#pragma unroll
-      for (int s = 0; s < NSLOT; ++s) {
-        if (k + s < my_tiles && !stop) {
-          if (k + s + PF < my_tiles) {
-            pb[(s + PF) % NSLOT] = load4(pp + (long long)(k + s + PF) * adv);
-            tb[(s + PF) % NSLOT] = load4(tp + (long long)(k + s + PF) * adv);
-          }
-          int idx[4];
-          u32 inc[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) idx[j] = index_of(pb[s].v[j], tb[s].v[j], inc[j], uniform_tag);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) bump(idx[j], inc[j]);
-          if (++since_fold == kTilesPerFold) {
-            since_fold = 0;
-            if constexpr (CHECK) {
-              if (oor) atomicOr(&ws->flag_oor, 1);
-              // a raised flag makes the rest of this pass useless: every CTA bails out at its next fold
-              stop = __syncthreads_or(oor | *(volatile int*)&ws->flag_oor) != 0;
-            }
-            fold();
-          }
+      for (int j = 0; j < 4; ++j) count(p.v[j], t.v[j], uniform_tag);
+      if constexpr (CHECK) {
+        if ((it & 31) == 31) {
+          if (oor) atomicOr(&ws->flag_oor, 1);
+          if (*(volatile int*)&ws->flag_oor) break;  // the pass is void: every thread leaves at its next check
         }
       }
     }
-    // ragged tail (< one tile): owned by the CTA that would have taken tile `nfull`
-    if ((long long)blockIdx.x == nfull % gridDim.x && !stop) {
-      const long long base = nfull * tile_elems + (long long)tid * 4;
-      if (since_fold == kTilesPerFold - 1) fold();
-      for (long long i = base; i < n && i < base + 4; ++i) {
-        u32 inc;
-        int idx = index_of(preds[i], target[i], inc, uniform_tag);
-        bump(idx, inc);
-      }
+    if (blockIdx.x == 0 && tid < (int)(n & 3)) {
+      const long long i = (nvec << 2) + tid;
+      count(preds[i], target[i], uniform_tag);
     }
   };
   if (um.ok) run(std::true_type{}); else run(std::false_type{});
-
   if (CHECK && oor) atomicOr(&ws->flag_oor, 1);
-  fold();
+  __syncthreads();
 
+  // copies -> global scratch (u32 counts cannot overflow: the launcher keeps a launch below 2^32 samples)
   u64* hist = reinterpret_cast<u64*>(ws + 1);
-  for (int i = tid; i < NB2; i += NT) {
-    u64 c = s_acc[i];
-    if (c) atomicAdd(hist + i, c);
+  for (int b = tid; b < NB2; b += NT) {
+    u64 c = 0;
+    for (int w = 0; w < copies; ++w) c += s_hist[w * NB2 + b];
+    if (c) atomicAdd(hist + b, c);
   }
   __threadfence();
   __syncthreads();
@@ -353,11 +303,20 @@ __global__ void __launch_bounds__(MAXNT, 1) binned_private_kernel(const BinnedPa
         atomicOr(P.status, P.status_bit_on_oor);
         ws->flag_oor = 0;
       }
-      // otherwise the flag stays up for pass 2, which lowers it
     } else if (P.only_if_flag) {
       ws->flag_oor = 0;
     }
   }
+}
+
+template <typename TT>
+static void (*pick_warphist(int mode, bool has_ignore))(const BinnedParams) {
+#define TMB_PICKW(MODE) \
+  return has_ignore ? binned_warphist_kernel<TT, MODE, true> : binned_warphist_kernel<TT, MODE, false>;
+  if (mode == kModeAsIs) { TMB_PICKW(kModeAsIs) }
+  if (mode == kModeAsIsCheck) { TMB_PICKW(kModeAsIsCheck) }
+  TMB_PICKW(kModeSigmoid)
+#undef TMB_PICKW
 }
 
 // =================================================================================================
@@ -472,61 +431,26 @@ __global__ void __launch_bounds__(kAtomicThreads) binned_atomic_kernel(const Bin
 }
 
 // ---- host -----------------------------------------------------------------------------------------
-static size_t private_smem_bytes(int T, int NT) {
-  const int NB = T + 1, NB2 = 2 * NB, W = (NB2 + 3) >> 2;
-  return (size_t)W * NT * 4 + (size_t)NB2 * 8 + (size_t)NB * 4 + kLutCells * 2 + 16;
-}
-
-// largest CTA (multiple of 32 threads) whose private histograms fit; 0 if fewer than 448 threads would
-static int private_threads(int T) {
-  const size_t budget = (size_t)max_optin_smem() - 64;  // static __shared__ s_last rides along
-  int cap = 1024;
-  if (const char* e = getenv("TMB_BINNED_NT")) cap = atoi(e);  // tuning knob (development only)
-  // below ~14 warps per SM the private kernel cannot hide its load latency and the atomic kernel wins (measured)
-  for (int nt = cap; nt >= 448; nt -= 32)
-    if (private_smem_bytes(T, nt) <= budget) {
-      // just above a register-budget step the extra warp or two is worth less than the deeper prefetch below it
-      if (nt > 512 && nt <= 576 && !getenv("TMB_BINNED_NT")) nt = 512;
-      return nt;
-    }
-  return 0;
-}
-
-template <typename TT>
-static void (*pick_private(int mode, bool has_ignore, int nt))(const BinnedParams) {
-#define TMB_PICK(MODE)                                                                     \
-  if (has_ignore)                                                                          \
-    return nt > 768 ? binned_private_kernel<TT, MODE, true, 1024>                          \
-                    : nt > 512 ? binned_private_kernel<TT, MODE, true, 768>                \
-                               : binned_private_kernel<TT, MODE, true, 512>;               \
-  return nt > 768 ? binned_private_kernel<TT, MODE, false, 1024>                           \
-                  : nt > 512 ? binned_private_kernel<TT, MODE, false, 768>                 \
-                             : binned_private_kernel<TT, MODE, false, 512>;
-  if (mode == kModeAsIs) { TMB_PICK(kModeAsIs) }
-  if (mode == kModeAsIsCheck) { TMB_PICK(kModeAsIsCheck) }
-  TMB_PICK(kModeSigmoid)
-#undef TMB_PICK
-}
-
 template <typename PT, typename TT>
 static int launch_binned(BinnedParams P, int prob_mode, cudaStream_t st) {
   const long long total = P.n_rows * P.num_columns;
   const int NB = P.T + 1;
   const long long nbins = P.num_columns * 2 * NB;
-  // the private-histogram kernel reads float32 scores; other score dtypes take the atomic kernel
-  const int nt_private = (std::is_same<PT, float>::value && P.num_columns == 1 && !P.target_is_class_index)
-                             ? private_threads(P.T) : 0;
+  // one column of float32 scores: warp-histogram kernel; everything else: the generic atomic kernel
+  const int copies = (std::is_same<PT, float>::value && P.num_columns == 1 && !P.target_is_class_index &&
+                      total < (1LL << 32)) ? warphist_copies(P.T) : 0;
 
   auto run = [&](bool sigmoid) -> int {
-    if (nt_private) {
-      const size_t smem = private_smem_bytes(P.T, nt_private);
-      const long long tile = (long long)nt_private * 4;
-      long long ntiles = (total + tile - 1) / tile;
-      int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
+    if (copies) {
+      P.hist_copies = copies;
+      const size_t smem = warphist_fixed_bytes(P.T) + (size_t)copies * 2 * NB * 4 + 8;
+      long long want = ((total >> 2) + kWarpHistThreads - 1) / kWarpHistThreads;
+      long long cap = (long long)sm_count() * 2;
+      int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
       const int mode = sigmoid ? kModeSigmoid : (P.check_range ? kModeAsIsCheck : kModeAsIs);
-      auto k = pick_private<TT>(mode, P.has_ignore != 0, nt_private);
+      auto k = pick_warphist<TT>(mode, P.has_ignore != 0);
       TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k<<<grid, nt_private, smem, st>>>(P);
+      k<<<grid, kWarpHistThreads, smem, st>>>(P);
     } else {
       const size_t fixed = (((size_t)NB * 4 + kLutCells * 2 + 7) & ~(size_t)7) + (size_t)2 * NB * 8;
       const size_t with_bins = fixed + (size_t)nbins * 4;
