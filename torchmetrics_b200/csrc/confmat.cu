@@ -5,8 +5,8 @@
 //   * large C (C*C bins do not fit shared memory; C = 1000 -> 10^6 bins = 8 MB, L2-resident on B200):
 //     one 64-bit RED (fire-and-forget atomic) per sample straight into the int64 state. No key tensor,
 //     no scratch, no second pass.
-//   * small C: bins privatised in shared memory as u32 (one copy per CTA), warp-level match-any
-//     aggregation when C is tiny (heavy same-address contention), one global RED per non-zero bin per CTA.
+//   * small C: bins privatised in shared memory as u32 (one copy per warp when they are few), shared-memory
+//     atomics, one global RED per non-zero bin per CTA.
 #include "common.cuh"
 
 namespace tmb {
@@ -104,64 +104,44 @@ confmat_global_kernel(const PT* __restrict__ preds, const TT* __restrict__ targe
 }
 
 // ---- small C: shared-memory privatised ----------------------------------------------------------
-template <bool AGG>
-__device__ __forceinline__ void smem_count(u32* hist, long long key, bool valid) {
-  if constexpr (AGG) {
-    // lanes with the same key elect a leader that adds the group size once
-    unsigned active = __ballot_sync(0xffffffffu, valid);
-    if (valid) {
-      unsigned peers = __match_any_sync(active, (int)key);
-      int leader = __ffs(peers) - 1;
-      if ((int)(threadIdx.x & 31) == leader) atomicAdd(hist + key, (u32)__popc(peers));
-    }
-  } else {
-    if (valid) atomicAdd(hist + key, 1u);
-  }
-}
+// u32 bins in shared memory, updated with shared-memory atomics (>1500 G/s chip-wide on B200, so no warp-level
+// aggregation: match.any costs ten times more than the atomics it would save).  When C*C is small the CTA keeps
+// several copies of the bins (copy = warp % copies) so that only lanes of one warp contend for a cell; 1024
+// threads per CTA, two CTAs per SM when they fit = 64 resident warps to hide the HBM latency.
+constexpr int kSmemThreads = 1024;
 
-template <typename PT, typename TT, bool AGG>
-__global__ void __launch_bounds__(kConfmatThreads)
+template <typename PT, typename TT>
+__global__ void __launch_bounds__(kSmemThreads)
 confmat_smem_kernel(const PT* __restrict__ preds, const TT* __restrict__ target, long long n, long long C,
-                    int has_ignore, long long ignore, u64* __restrict__ confmat, int* __restrict__ status) {
+                    int has_ignore, long long ignore, int copies, u64* __restrict__ confmat,
+                    int* __restrict__ status) {
   extern __shared__ u32 hist[];
   const int CC = (int)(C * C);
-  for (int i = threadIdx.x; i < CC; i += blockDim.x) hist[i] = 0;
+  for (int i = threadIdx.x; i < copies * CC; i += blockDim.x) hist[i] = 0;
   __syncthreads();
+  u32* const my = hist + ((threadIdx.x >> 5) % copies) * CC;
   const long long nvec = n >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   int bad = 0;
-  // every lane of a warp runs the same number of iterations (match_any needs converged warps)
-  const long long iters = (nvec + stride - 1) / stride;
-  long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  for (long long it = 0; it < iters; ++it, g += stride) {
-    const bool in = g < nvec;
-    Vec4<PT> p;
-    Vec4<TT> t;
-    if (in) {
-      p = load4(preds + 4 * g);
-      t = load4(target + 4 * g);
-    }
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nvec; g += stride) {
+    const Vec4<PT> p = load4(preds + 4 * g);
+    const Vec4<TT> t = load4(target + 4 * g);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       long long key = 0;
-      bool valid = in && make_key(p.v[j], t.v[j], C, (long long)CC, has_ignore, ignore, key, bad);
-      smem_count<AGG>(hist, key, valid);
+      if (make_key(p.v[j], t.v[j], C, (long long)CC, has_ignore, ignore, key, bad)) atomicAdd(my + key, 1u);
     }
   }
-  {
-    const bool in = blockIdx.x == 0 && threadIdx.x < (n & 3);
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const long long i = (nvec << 2) + threadIdx.x;
     long long key = 0;
-    bool valid = false;
-    if (in) {
-      long long i = (nvec << 2) + threadIdx.x;
-      valid = make_key(preds[i], target[i], C, (long long)CC, has_ignore, ignore, key, bad);
-    }
-    if (threadIdx.x < 32) smem_count<AGG>(hist, key, valid);
+    if (make_key(preds[i], target[i], C, (long long)CC, has_ignore, ignore, key, bad)) atomicAdd(my + key, 1u);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < CC; i += blockDim.x) {
-    u32 c = hist[i];
-    if (c) atomicAdd(confmat + i, (u64)c);
+    u64 c = 0;
+    for (int w = 0; w < copies; ++w) c += hist[w * CC + i];
+    if (c) atomicAdd(confmat + i, c);
   }
   if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
 }
@@ -263,19 +243,16 @@ static int launch_confmat(const PT* preds, const TT* target, long long n, long l
   } else if (algo != 2) {
     return TMB_ERR_ARG;
   } else {
-    int per_sm = smem > 0 ? (int)((size_t)(200 * 1024) / (smem + 1024)) : 8;
-    if (per_sm > 8) per_sm = 8;
-    if (per_sm < 1) per_sm = 1;
-    int grid = grid_for(nvec, kConfmatThreads, per_sm);
-    if (CC <= 1024) {
-      auto k = confmat_smem_kernel<PT, TT, true>;
-      TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k<<<grid, kConfmatThreads, smem, st>>>(preds, target, n, C, has_ignore, ignore, confmat, status);
-    } else {
-      auto k = confmat_smem_kernel<PT, TT, false>;
-      TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k<<<grid, kConfmatThreads, smem, st>>>(preds, target, n, C, has_ignore, ignore, confmat, status);
-    }
+    // as many copies of the bins as fit ~100 KB (two CTAs per SM), at most one per warp
+    const size_t budget = 100 * 1024;
+    int copies = smem <= budget ? (int)(budget / smem) : 1;
+    if (copies > kSmemThreads / 32) copies = kSmemThreads / 32;
+    const size_t dyn = smem * copies;
+    const int per_sm = dyn <= budget ? 2 : 1;
+    int grid = grid_for(nvec, kSmemThreads, per_sm);
+    auto k = confmat_smem_kernel<PT, TT>;
+    TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    k<<<grid, kSmemThreads, dyn, st>>>(preds, target, n, C, has_ignore, ignore, copies, confmat, status);
   }
   TMB_CUDA_CHECK(cudaGetLastError());
   return TMB_OK;
