@@ -16,7 +16,8 @@
  *     metric state can be passed directly; pass a zeroed buffer to get the bare update.
  *   - return value: TMB_OK or a negative TMB_ERR_* (argument / launch errors, detected on the host).
  *     Data errors (labels out of range, unsorted thresholds) are detected on the device and reported
- *     through the int32 `status_dev[0]` word as TMB_STATUS_* bits, which the caller reads when it wants
+ *     through `status_dev`, TWO int32 words: [0] collects error bits (LABEL_RANGE, THRESHOLD_ORDER,
+ *     OUT_OF_UNIT_RANGE), [1] the fused-validation findings (TARGET_VALUES, PREDS_VALUES); the caller reads them when it wants
  *     to pay for the synchronisation (the Python layer does so lazily, on compute()).
  *   - vector loads need natural alignment of the element type times the vector width: every data
  *     pointer must be 32-byte aligned (torch allocations are; offset views must be copied first).
@@ -51,6 +52,11 @@ extern "C" {
 #define TMB_STATUS_LABEL_RANGE 1      /* key = target*C + pred outside [0, C*C): the reference raises here */
 #define TMB_STATUS_THRESHOLD_ORDER 2  /* thresholds not ascending                                         */
 #define TMB_STATUS_OUT_OF_UNIT_RANGE 4 /* TMB_PROB_CHECK: a score outside [0,1] was seen, update discarded   */
+/* Fused input validation (what the reference's `_*_tensor_validation` spends torch.unique sorts on): every kernel
+ * also reports, for free, whether a label it read lies outside the legal set.  A clear bit proves the reference's
+ * value checks would pass; a set bit sends the caller to the exact (slow) check for the error message. */
+#define TMB_STATUS_TARGET_VALUES 8    /* a non-ignored target outside [0, C) (K1, class-index K3) or {0, 1} (K2, K3) */
+#define TMB_STATUS_PREDS_VALUES 16    /* an integer pred outside [0, C) (K1) or {0, 1} (K2)                         */
 
 /* element types (labels: I64, I32, U8; scores: F32, F16, BF16, F64 — cast anything else first) */
 #define TMB_I64 0
@@ -188,7 +194,7 @@ TMB_API size_t tmb_stat_scores_workspace_bytes(int64_t num_labels);
 TMB_API int tmb_stat_scores_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
                            int64_t n_rows, int64_t num_labels, double threshold, int prob_mode, int has_ignore,
                            int64_t ignore_index, int range_check_ignored, int64_t* out_dev, void* workspace_dev,
-                           size_t workspace_bytes, void* stream);
+                           size_t workspace_bytes, int32_t* status_dev /* may be NULL */, void* stream);
 
 #ifdef __cplusplus
 }

@@ -387,3 +387,122 @@ def test_metric_device_moves_and_pickle_on_gpu():
     assert m.state_dict() == {}
     with pytest.raises(RuntimeError, match="CUDA tensors only"):
         tm.BinaryAUROC(thresholds=50).update(p.cpu(), t.cpu())
+
+
+# ------------------------------------------------------------------ fused value validation (validate_args=True)
+def _count_slow_checks(monkeypatch):
+    """Instrument the reference-style value checks so a test can tell whether the slow path ran."""
+    from importlib import import_module
+
+    C = import_module("torchmetrics_b200.functional.classification._checks")
+    calls = {"n": 0}
+    for name in ("_check_binary_values_now", "_check_label_count_now"):
+        orig = getattr(C, name)
+
+        def wrapped(*a, _orig=orig, **k):
+            calls["n"] += 1
+            return _orig(*a, **k)
+
+        monkeypatch.setattr(C, name, wrapped)
+    return calls
+
+
+def test_fused_validation_skips_input_passes_on_good_data(monkeypatch):
+    tm = _tm()
+    calls = _count_slow_checks(monkeypatch)
+    g = torch.Generator().manual_seed(3)
+    n = 4096
+    t5 = torch.randint(0, 5, (n,), generator=g).to(DEV)
+    p5 = torch.randint(0, 5, (n,), generator=g).to(DEV)
+    tb = torch.randint(0, 2, (n,), generator=g).to(DEV)
+    ps = torch.rand(n, generator=g).to(DEV)
+    tl = torch.randint(0, 2, (n, 7), generator=g).to(DEV)
+    pl = torch.rand(n, 7, generator=g).to(DEV)
+    pc = torch.rand(n, 5, generator=g).to(DEV)
+    F = tm.functional
+    F.multiclass_confusion_matrix(p5, t5, 5)
+    F.binary_confusion_matrix(ps, tb)
+    F.binary_confusion_matrix((ps > 0.5).long(), tb)
+    F.multilabel_confusion_matrix(pl, tl, 7)
+    F.binary_stat_scores(ps, tb)
+    F.multiclass_stat_scores(p5, t5, 5, average="macro")
+    F.multilabel_stat_scores(pl, tl, 7)
+    F.multiclass_accuracy(p5, t5, 5, average="macro")
+    F.binary_auroc(ps, tb, thresholds=100)
+    F.multiclass_auroc(pc, t5, 5, thresholds=50)
+    F.multilabel_average_precision(pl, tl, 7, thresholds=50)
+    for m in (tm.MulticlassConfusionMatrix(5), tm.classification.MulticlassF1Score(5),
+              tm.classification.BinaryAUROC(thresholds=64)):
+        m = m.to(DEV)
+        if isinstance(m, tm.classification.BinaryAUROC):
+            m.update(ps, tb)
+        else:
+            m.update(p5, t5)
+        m.compute()
+    assert calls["n"] == 0, "value checks re-read the inputs although the kernels reported nothing"
+    # the paths whose kernels do not report values still validate up front
+    F.multiclass_stat_scores(p5, t5, 5, average="micro")
+    F.binary_auroc(ps, tb, thresholds=None)
+    assert calls["n"] > 0
+
+
+def test_fused_validation_raises_like_the_reference_and_restores_state(monkeypatch):
+    tm = _tm()
+    F = tm.functional
+    calls = _count_slow_checks(monkeypatch)
+    g = torch.Generator().manual_seed(4)
+    n = 2048
+    tb = torch.randint(0, 2, (n,), generator=g).to(DEV)
+    ps = torch.rand(n, generator=g).to(DEV)
+    bad_tb = tb.clone()
+    bad_tb[17] = 3
+    with pytest.raises(RuntimeError, match="Detected the following values in `target`"):
+        F.binary_stat_scores(ps, bad_tb)
+    with pytest.raises(RuntimeError, match="Detected the following values in `target`"):
+        F.binary_confusion_matrix(ps, bad_tb)
+    with pytest.raises(RuntimeError, match="Detected the following values in `target`"):
+        F.binary_auroc(ps, bad_tb, thresholds=20)
+    with pytest.raises(RuntimeError, match="Detected the following values in `preds`"):
+        F.binary_stat_scores(torch.full((n,), 2, device=DEV), tb)
+    assert calls["n"] >= 4
+    # with ignore_index the same value is legal
+    assert torch.equal(F.binary_stat_scores(ps, bad_tb, ignore_index=3),
+                       F.binary_stat_scores(ps, bad_tb, ignore_index=3, validate_args=False))
+
+    # multiclass: too many distinct values
+    t = torch.arange(n, device=DEV) % 9
+    p = torch.arange(n, device=DEV) % 5
+    with pytest.raises(RuntimeError, match="Detected more unique values in `target` than `num_classes`"):
+        F.multiclass_confusion_matrix(p, t, 5)
+    with pytest.raises(RuntimeError, match="Detected more unique values in `preds` than `num_classes`"):
+        F.multiclass_stat_scores(t, p, 5, average="macro")
+
+    # stateful metrics: a rejected batch leaves the state as it was
+    good_t = torch.randint(0, 5, (n,), generator=g).to(DEV)
+    good_p = torch.randint(0, 5, (n,), generator=g).to(DEV)
+    cm = tm.MulticlassConfusionMatrix(5).to(DEV)
+    cm.update(good_p, good_t)
+    before = cm.confmat.clone()
+    with pytest.raises(RuntimeError, match="Detected more unique values"):
+        cm.update(p, t)
+    assert torch.equal(cm.confmat, before)
+    cm.update(good_p, good_t)
+    assert torch.equal(cm.compute(), 2 * before)
+
+    au = tm.classification.BinaryAUROC(thresholds=32).to(DEV)
+    au.update(ps, tb)
+    before = au.confmat.clone()
+    with pytest.raises(RuntimeError, match="Detected the following values in `target`"):
+        au.update(ps, bad_tb)
+    assert torch.equal(au.confmat, before)
+
+    f1 = tm.classification.BinaryF1Score().to(DEV)
+    f1.update(ps, tb)
+    before = (f1.tp.clone(), f1.fn.clone())
+    with pytest.raises(RuntimeError, match="Detected the following values in `target`"):
+        f1.update(ps, bad_tb)
+    assert torch.equal(f1.tp, before[0]) and torch.equal(f1.fn, before[1])
+
+    # a stale finding left by an unvalidated call costs one slow check but raises nothing
+    F.binary_stat_scores(ps, bad_tb, validate_args=False)
+    F.binary_stat_scores(ps, tb)

@@ -464,3 +464,84 @@ def test_full_size_properties():
         above = preds >= thr[i]
         assert int(st[i, 1, 1]) == int((above & (target == 1)).sum())
         assert int(st[i, 0, 1]) == int((above & (target == 0)).sum())
+
+
+# --------------------------------------------------------------------------------- fused validation words
+def test_validation_findings_go_to_the_second_status_word():
+    N = _native()
+    dev = torch.device(DEV)
+    N.read_status_words(dev)
+    n = 1 << 12
+    g = torch.Generator().manual_seed(9)
+    t = torch.randint(0, 7, (n,), generator=g).to(DEV)
+    p = torch.randint(0, 7, (n,), generator=g).to(DEV)
+    cm = torch.zeros(7, 7, dtype=torch.int64, device=DEV)
+    N.confmat_update_(cm, p, t, 7)
+    assert N.read_status_words(dev) == (0, 0)
+    t2 = t.clone()
+    t2[5] = 7  # aliases into the next row's cell: counted like the reference, reported as a finding only
+    p2 = p.clone()
+    p2[5] = 0
+    N.confmat_update_(cm, p2, t2, 7)
+    assert N.read_status_words(dev) == (N.STATUS_LABEL_RANGE, N.STATUS_TARGET_VALUES)  # key 49 is outside 7x7
+    p3 = p.clone()
+    p3[9] = 8
+    t3 = t.clone()
+    t3[9] = 0
+    N.confmat_update_(cm, p3, t3, 7)
+    assert N.read_status_words(dev) == (0, N.STATUS_PREDS_VALUES)
+    # ignored samples are never findings
+    t4 = t.clone()
+    t4[3] = -100
+    N.confmat_update_(cm, p, t4, 7, ignore_index=-100)
+    assert N.read_status_words(dev) == (0, 0)
+    # partition path (algo 6)
+    C = 300
+    n = 1 << 16
+    tt = torch.randint(0, C, (n,), generator=g).to(DEV)
+    pp = torch.randint(0, C, (n,), generator=g).to(DEV)
+    big = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+    N.confmat_update_(big, pp, tt, C, algo=6)
+    assert N.read_status_words(dev) == (0, 0)
+    pp[77] = C + 3
+    tt[77] = 1
+    N.confmat_update_(big, pp, tt, C, algo=6)
+    assert N.read_status_words(dev) == (0, N.STATUS_PREDS_VALUES)
+
+    # K2
+    L = 5
+    tl = torch.randint(0, 2, (1000, L), generator=g).to(DEV)
+    sl = torch.rand(1000, L, generator=g).to(DEV)
+    out = torch.zeros(4, L, dtype=torch.int64, device=DEV)
+    N.stat_scores_update_(out, sl, tl, L)
+    assert N.read_status_words(dev) == (0, 0)
+    tl2 = tl.clone()
+    tl2[3, 2] = 2
+    N.stat_scores_update_(out, sl, tl2, L)
+    assert N.read_status_words(dev) == (0, N.STATUS_TARGET_VALUES)
+    N.stat_scores_update_(out, sl, tl2, L, ignore_index=2)
+    assert N.read_status_words(dev) == (0, 0)
+    N.stat_scores_update_(out, sl, tl2, L, report_values=False)
+    assert N.read_status_words(dev) == (0, 0)
+    N.stat_scores_update_(out, (sl > 0.5).long() * 3, tl, L)
+    assert N.read_status_words(dev) == (0, N.STATUS_PREDS_VALUES)
+
+    # K3, both kernels
+    thr = torch.linspace(0, 1, 50, device=DEV)
+    st = torch.zeros(50, 2, 2, dtype=torch.int64, device=DEV)
+    tb = tl[:, 0].contiguous()
+    N.binned_curve_update_(st, sl[:, 0].contiguous(), tb, thr)
+    assert N.read_status_words(dev) == (0, 0)
+    tb2 = tb.clone()
+    tb2[11] = 5
+    N.binned_curve_update_(st, sl[:, 0].contiguous(), tb2, thr)
+    assert N.read_status_words(dev) == (0, N.STATUS_TARGET_VALUES)
+    stc = torch.zeros(50, L, 2, 2, dtype=torch.int64, device=DEV)
+    cls = torch.randint(0, L, (1000,), generator=g).to(DEV)
+    N.binned_curve_update_(stc, sl, cls, thr, num_columns=L, target_is_class_index=True, prob_mode=N.PROB_AS_IS)
+    assert N.read_status_words(dev) == (0, 0)
+    cls[4] = L
+    N.binned_curve_update_(stc, sl, cls, thr, num_columns=L, target_is_class_index=True, prob_mode=N.PROB_AS_IS)
+    assert N.read_status_words(dev) == (0, N.STATUS_TARGET_VALUES)
+    N.binned_curve_update_(stc, sl, tl2, thr, num_columns=L)
+    assert N.read_status_words(dev) == (0, N.STATUS_TARGET_VALUES)

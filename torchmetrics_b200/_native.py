@@ -22,6 +22,9 @@ ERR_NAMES = {-1: "TMB_ERR_ARG", -2: "TMB_ERR_ALIGN", -3: "TMB_ERR_CUDA", -4: "TM
 STATUS_LABEL_RANGE = 1
 STATUS_THRESHOLD_ORDER = 2
 STATUS_OUT_OF_UNIT_RANGE = 4
+# fused-validation findings, reported in the second status word (include/tm_b200.h)
+STATUS_TARGET_VALUES = 8
+STATUS_PREDS_VALUES = 16
 
 PROB_AS_IS, PROB_AUTO, PROB_SIGMOID, PROB_CHECK = 0, 1, 2, 3
 
@@ -63,7 +66,7 @@ _SIGNATURES = {
     "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                           _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,
-                                          _c.c_void_p, _c.c_size_t, _c.c_void_p]),
+                                          _c.c_void_p, _c.c_size_t, _c.c_void_p, _c.c_void_p]),
 }
 
 _lib = None
@@ -192,17 +195,26 @@ def scratch(dev: torch.device) -> _Scratch:
     return s
 
 
-def read_status(dev: torch.device) -> int:
-    """Synchronising read-and-clear of the device status word for the current stream."""
+def read_status_words(dev: torch.device) -> Tuple[int, int]:
+    """Synchronising read-and-clear of (error bits, fused-validation findings) for the current stream: one 8-byte
+    device-to-host copy."""
     s = scratch(dev)
-    v = int(s.status[0].item())
-    if v:
+    err, val = s.status[:2].tolist()
+    if err or val:
         s.status.zero_()
-    return v
+    return err, val
+
+
+def read_status(dev: torch.device) -> int:
+    """Synchronising read-and-clear of the device status words; returns the error bits."""
+    return read_status_words(dev)[0]
 
 
 def raise_on_status(dev: torch.device, num_classes: Optional[int] = None) -> None:
-    v = read_status(dev)
+    raise_for_bits(read_status(dev), num_classes)
+
+
+def raise_for_bits(v: int, num_classes: Optional[int] = None) -> None:
     if v & STATUS_LABEL_RANGE:
         raise RuntimeError(
             "Detected label values outside the expected range in `preds`/`target`"
@@ -294,8 +306,9 @@ def binned_curve_update_(confmat: Tensor, preds: Tensor, target: Tensor, thresho
 
 def stat_scores_update_(out: Tensor, preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
                         ignore_index: Optional[int] = None, prob_mode: int = PROB_AUTO,
-                        range_check_ignored: bool = True) -> None:
-    """out (4, L) int64 [tp|fp|tn|fn] += per-label statistics of (n_rows, L) preds/target (K2)."""
+                        range_check_ignored: bool = True, report_values: bool = True) -> None:
+    """out (4, L) int64 [tp|fp|tn|fn] += per-label statistics of (n_rows, L) preds/target (K2).
+    `report_values`: let the kernel note target/label-preds values outside {0, 1} in the validation status word."""
     dev = require_cuda(out, preds, target)
     assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == 4 * num_labels
     preds = as_kernel_scores(preds.reshape(-1)) if preds.is_floating_point() else as_kernel_labels(preds.reshape(-1))
@@ -309,7 +322,8 @@ def stat_scores_update_(out: Tensor, preds: Tensor, target: Tensor, num_labels: 
         rc = lib.tmb_stat_scores_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
                                         n_rows, num_labels, float(threshold), prob_mode, ignore_index is not None,
                                         0 if ignore_index is None else int(ignore_index), bool(range_check_ignored),
-                                        out.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+                                        out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                        sc.status.data_ptr() if report_values else None, _stream_ptr(dev))
     _check(rc, "tmb_stat_scores_update")
 
 

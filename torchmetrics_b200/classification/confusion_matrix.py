@@ -9,6 +9,7 @@ from typing_extensions import Literal
 from torchmetrics_b200 import _native
 from torchmetrics_b200.classification.base import _ClassificationTaskWrapper
 F = import_module("torchmetrics_b200.functional.classification.confusion_matrix")
+C = import_module("torchmetrics_b200.functional.classification._checks")
 from torchmetrics_b200.metric import Metric
 from torchmetrics_b200.utilities.enums import ClassificationTask
 
@@ -41,9 +42,16 @@ class BinaryConfusionMatrix(_ConfmatBase):
         self.add_state("confmat", torch.zeros(2, 2, dtype=torch.long), dist_reduce_fx="sum")
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target)
         if self.validate_args:
-            F._binary_confusion_matrix_tensor_validation(preds, target, self.ignore_index)
-        F._binary_confusion_matrix_update_fused(preds, target, self.threshold, self.ignore_index, out=self.confmat)
+            with fv:
+                F._binary_confusion_matrix_tensor_validation(preds, target, self.ignore_index)
+
+        def step(out: Tensor) -> None:
+            F._binary_confusion_matrix_update_fused(preds, target, self.threshold, self.ignore_index, out=out)
+
+        step(self.confmat)
+        fv.finish(preds.device, 2, undo=lambda: C.rollback(self.confmat, step))
 
     def compute(self) -> Tensor:
         self._check_device_status(2)
@@ -66,10 +74,16 @@ class MulticlassConfusionMatrix(_ConfmatBase):
         self.add_state("confmat", torch.zeros(num_classes, num_classes, dtype=torch.long), dist_reduce_fx="sum")
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target)
         if self.validate_args:
-            F._multiclass_confusion_matrix_tensor_validation(preds, target, self.num_classes, self.ignore_index)
-        F._multiclass_confusion_matrix_update_fused(preds, target, self.num_classes, self.ignore_index,
-                                                    out=self.confmat)
+            with fv:
+                F._multiclass_confusion_matrix_tensor_validation(preds, target, self.num_classes, self.ignore_index)
+
+        def step(out: Tensor) -> None:
+            F._multiclass_confusion_matrix_update_fused(preds, target, self.num_classes, self.ignore_index, out=out)
+
+        step(self.confmat)
+        fv.finish(preds.device, self.num_classes, undo=lambda: C.rollback(self.confmat, step))
 
     def compute(self) -> Tensor:
         self._check_device_status(self.num_classes)
@@ -93,10 +107,17 @@ class MultilabelConfusionMatrix(_ConfmatBase):
         self.add_state("confmat", torch.zeros(num_labels, 2, 2, dtype=torch.long), dist_reduce_fx="sum")
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target)
         if self.validate_args:
-            F._multilabel_confusion_matrix_tensor_validation(preds, target, self.num_labels, self.ignore_index)
-        F._multilabel_confusion_matrix_update_fused(preds, target, self.num_labels, self.threshold, self.ignore_index,
-                                                    out=self.confmat)
+            with fv:
+                F._multilabel_confusion_matrix_tensor_validation(preds, target, self.num_labels, self.ignore_index)
+
+        def step(out: Tensor) -> None:
+            F._multilabel_confusion_matrix_update_fused(preds, target, self.num_labels, self.threshold,
+                                                        self.ignore_index, out=out)
+
+        step(self.confmat)
+        fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
 
     def compute(self) -> Tensor:
         return F._multilabel_confusion_matrix_compute(self.confmat, self.normalize)

@@ -14,6 +14,7 @@ from typing_extensions import Literal
 from torchmetrics_b200 import _native
 from torchmetrics_b200.classification.base import _ClassificationTaskWrapper
 F = import_module("torchmetrics_b200.functional.classification.precision_recall_curve")
+C = import_module("torchmetrics_b200.functional.classification._checks")
 from torchmetrics_b200.metric import Metric
 from torchmetrics_b200.utilities.data import dim_zero_cat
 from torchmetrics_b200.utilities.enums import ClassificationTask
@@ -59,15 +60,21 @@ class BinaryPrecisionRecallCurve(_CurveBase):
         self._init_curve_state(thresholds, (2, 2))
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target, self.thresholds is not None)
         if self.validate_args:
-            F._binary_precision_recall_curve_tensor_validation(preds, target, self.ignore_index)
+            with fv:
+                F._binary_precision_recall_curve_tensor_validation(preds, target, self.ignore_index)
         if self.thresholds is None:
             p, t, _ = F._binary_precision_recall_curve_format(preds, target, None, self.ignore_index)
             self.preds.append(p)
             self.target.append(t)
         else:
-            F._binary_precision_recall_curve_update_fused(preds, target, self.thresholds, self.ignore_index,
-                                                          out=self.confmat, assume_sorted=self._thresholds_ascending)
+            def step(out: Tensor) -> None:
+                F._binary_precision_recall_curve_update_fused(preds, target, self.thresholds, self.ignore_index,
+                                                              out=out, assume_sorted=self._thresholds_ascending)
+
+            step(self.confmat)
+            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
 
     def _state(self):
         if self.thresholds is None:
@@ -93,17 +100,24 @@ class MulticlassPrecisionRecallCurve(_CurveBase):
         self._init_curve_state(thresholds, (2, 2) if average == "micro" else (num_classes, 2, 2))
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target, self.thresholds is not None)
         if self.validate_args:
-            F._multiclass_precision_recall_curve_tensor_validation(preds, target, self.num_classes, self.ignore_index)
+            with fv:
+                F._multiclass_precision_recall_curve_tensor_validation(preds, target, self.num_classes,
+                                                                       self.ignore_index)
         if self.thresholds is None:
             p, t, _ = F._multiclass_precision_recall_curve_format(preds, target, self.num_classes, None,
                                                                   self.ignore_index, self.average)
             self.preds.append(p)
             self.target.append(t)
         else:
-            F._multiclass_precision_recall_curve_update_fused(preds, target, self.num_classes, self.thresholds,
-                                                              self.ignore_index, self.average, out=self.confmat,
-                                                              assume_sorted=self._thresholds_ascending)
+            def step(out: Tensor) -> None:
+                F._multiclass_precision_recall_curve_update_fused(preds, target, self.num_classes, self.thresholds,
+                                                                  self.ignore_index, self.average, out=out,
+                                                                  assume_sorted=self._thresholds_ascending)
+
+            step(self.confmat)
+            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
 
     def _state(self):
         if self.thresholds is None:
@@ -127,17 +141,24 @@ class MultilabelPrecisionRecallCurve(_CurveBase):
         self._init_curve_state(thresholds, (num_labels, 2, 2))
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target, self.thresholds is not None)
         if self.validate_args:
-            F._multilabel_precision_recall_curve_tensor_validation(preds, target, self.num_labels, self.ignore_index)
+            with fv:
+                F._multilabel_precision_recall_curve_tensor_validation(preds, target, self.num_labels,
+                                                                       self.ignore_index)
         if self.thresholds is None:
             p, t, _ = F._multilabel_precision_recall_curve_format(preds, target, self.num_labels, None,
                                                                   self.ignore_index)
             self.preds.append(p)
             self.target.append(t)
         else:
-            F._multilabel_precision_recall_curve_update_fused(preds, target, self.num_labels, self.thresholds,
-                                                              self.ignore_index, out=self.confmat,
-                                                              assume_sorted=self._thresholds_ascending)
+            def step(out: Tensor) -> None:
+                F._multilabel_precision_recall_curve_update_fused(preds, target, self.num_labels, self.thresholds,
+                                                                  self.ignore_index, out=out,
+                                                                  assume_sorted=self._thresholds_ascending)
+
+            step(self.confmat)
+            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
 
     def _state(self):
         if self.thresholds is None:

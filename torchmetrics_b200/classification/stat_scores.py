@@ -9,6 +9,7 @@ from typing_extensions import Literal
 from torchmetrics_b200 import _native
 from torchmetrics_b200.classification.base import _ClassificationTaskWrapper
 F = import_module("torchmetrics_b200.functional.classification.stat_scores")
+C = import_module("torchmetrics_b200.functional.classification._checks")
 from torchmetrics_b200.metric import Metric
 from torchmetrics_b200.utilities.data import dim_zero_cat
 from torchmetrics_b200.utilities.enums import ClassificationTask
@@ -66,10 +67,13 @@ class BinaryStatScores(_AbstractStatScores):
         self._create_state(size=1, multidim_average=multidim_average)
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target, self.multidim_average == "global")
         if self.validate_args:
-            F._binary_stat_scores_tensor_validation(preds, target, self.multidim_average, self.ignore_index)
+            with fv:
+                F._binary_stat_scores_tensor_validation(preds, target, self.multidim_average, self.ignore_index)
         tp, fp, tn, fn = F._binary_stat_scores_update_fused(preds, target, self.threshold, self.multidim_average,
                                                             self.ignore_index)
+        fv.finish(preds.device)  # before the state is touched, like the reference's up-front validation
         self._update_state(tp, fp, tn, fn)
 
     def compute(self) -> Tensor:
@@ -99,12 +103,16 @@ class MulticlassStatScores(_AbstractStatScores):
                            multidim_average=multidim_average)
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target, F._multiclass_stat_scores_reports_values(
+            self.top_k, self.average, self.multidim_average))
         if self.validate_args:
-            F._multiclass_stat_scores_tensor_validation(preds, target, self.num_classes, self.multidim_average,
-                                                        self.ignore_index)
+            with fv:
+                F._multiclass_stat_scores_tensor_validation(preds, target, self.num_classes, self.multidim_average,
+                                                            self.ignore_index)
         tp, fp, tn, fn = F._multiclass_stat_scores_update_fused(preds, target, self.num_classes, self.top_k,
                                                                 self.average, self.multidim_average,
                                                                 self.ignore_index)
+        fv.finish(preds.device, self.num_classes)
         self._update_state(tp, fp, tn, fn)
 
     def _final_state(self) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
@@ -139,11 +147,14 @@ class MultilabelStatScores(_AbstractStatScores):
         self._create_state(size=num_labels, multidim_average=multidim_average)
 
     def update(self, preds: Tensor, target: Tensor) -> None:
+        fv = C.FusedValidation(self.validate_args, preds, target, self.multidim_average == "global")
         if self.validate_args:
-            F._multilabel_stat_scores_tensor_validation(preds, target, self.num_labels, self.multidim_average,
-                                                        self.ignore_index)
+            with fv:
+                F._multilabel_stat_scores_tensor_validation(preds, target, self.num_labels, self.multidim_average,
+                                                            self.ignore_index)
         tp, fp, tn, fn = F._multilabel_stat_scores_update_fused(preds, target, self.num_labels, self.threshold,
                                                                 self.multidim_average, self.ignore_index)
+        fv.finish(preds.device)
         self._update_state(tp, fp, tn, fn)
 
     def compute(self) -> Tensor:

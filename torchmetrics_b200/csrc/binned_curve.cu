@@ -238,12 +238,13 @@ __global__ void __launch_bounds__(kWarpHistThreads, 2) binned_warphist_kernel(co
   const long long stride = (long long)gridDim.x * NT;
   const long long ignore = P.ignore;
   u32* const my = s_hist + (warp % copies) * NB2;
-  int oor = 0;
+  int oor = 0, vbits = 0;
 
   auto count = [&](float p, TT tv, auto uniform_tag) {
     const long long tl = as_i64(tv);
     bool valid = true;
     if constexpr (HAS_IGNORE) valid = tl != ignore;
+    vbits |= (valid && (u64)tl > 1ULL) ? TMB_STATUS_TARGET_VALUES : 0;  // fused validation: target not in {0, 1}
     if constexpr (CHECK) oor |= (int)(valid & !(p >= 0.f && p <= 1.f));
     if constexpr (SIGMOID) p = sigmoid_ref(p);
     int cnt;
@@ -278,6 +279,7 @@ __global__ void __launch_bounds__(kWarpHistThreads, 2) binned_warphist_kernel(co
   };
   if (um.ok) run(std::true_type{}); else run(std::false_type{});
   if (CHECK && oor) atomicOr(&ws->flag_oor, 1);
+  if (vbits) report_status(P.status, vbits);
   __syncthreads();
 
   // copies -> global scratch (u32 counts cannot overflow: the launcher keeps a launch below 2^32 samples)
@@ -357,7 +359,7 @@ __global__ void __launch_bounds__(kAtomicThreads) binned_atomic_kernel(const Bin
   const long long total = P.n_rows * C;
   const long long nvec = total >> 2;
   const long long stride = (long long)gridDim.x * NT;
-  int oor = 0;
+  int oor = 0, vbits = 0;
 
   auto count = [&](PT pv, long long tl, long long col) {
     // tl: multilabel -> the element's own target; class-index mode -> the row's class id
@@ -365,6 +367,8 @@ __global__ void __launch_bounds__(kAtomicThreads) binned_atomic_kernel(const Bin
     CT p = to_cmp(pv);
     if (P.check_range && (!ign || P.oor_counts_ignored)) oor |= out_of_unit(p);
     if (ign) return;
+    // fused validation: class id outside [0, C) / binary target outside {0, 1}
+    vbits |= ((u64)tl >= (u64)(P.target_is_class_index ? C : 2)) ? TMB_STATUS_TARGET_VALUES : 0;
     if constexpr (SIGMOID) p = round_to_storage<PT>(sigmoid_ref(p));
     const bool pos = P.target_is_class_index ? (tl == col) : (tl == 1);
     long long idx = (col * 2 + (pos ? 1 : 0)) * NB + bin_of(p, m, s_thr, s_lut);
@@ -401,6 +405,7 @@ __global__ void __launch_bounds__(kAtomicThreads) binned_atomic_kernel(const Bin
     count(preds[e], as_i64(P.target_is_class_index ? target[row] : target[e]), col);
   }
   if (P.check_range && oor) atomicOr(&ws->flag_oor, 1);
+  if (vbits) report_status(P.status, vbits);
   __syncthreads();
   if constexpr (SMEM_BINS) {
     for (long long i = tid; i < nbins; i += NT) {

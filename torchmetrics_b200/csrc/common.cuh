@@ -144,6 +144,14 @@ __device__ __forceinline__ long long as_i64(short x) { return x; }
 __device__ __forceinline__ long long as_i64(signed char x) { return x; }
 __device__ __forceinline__ long long as_i64(unsigned char x) { return x; }
 
+// status words: [0] errors that invalidate the update, [1] fused-validation findings (informational)
+__device__ __forceinline__ void report_status(int* status, int bits) {
+  const int err = bits & (TMB_STATUS_LABEL_RANGE | TMB_STATUS_THRESHOLD_ORDER | TMB_STATUS_OUT_OF_UNIT_RANGE);
+  const int val = bits & (TMB_STATUS_TARGET_VALUES | TMB_STATUS_PREDS_VALUES);
+  if (err) atomicOr(status, err);
+  if (val) atomicOr(status + 1, val);
+}
+
 // Dispatch helpers ------------------------------------------------------------------------------
 #define TMB_DISPATCH_INT(dt, T, ...)                                    \
   switch (dt) {                                                         \

@@ -16,11 +16,13 @@ constexpr int kConfmatThreads = 256;
 template <typename PT, typename TT>
 __device__ __forceinline__ bool make_key(PT p, TT t, long long C, long long CC, bool has_ignore, long long ignore,
                                          long long& key, int& bad) {
-  long long tl = as_i64(t);
+  const long long tl = as_i64(t), pl = as_i64(p);
   if (has_ignore && tl == ignore) return false;
-  key = tl * C + as_i64(p);
+  // fused validation: labels outside [0, C) (unsigned compare catches negatives too)
+  bad |= ((u64)tl >= (u64)C ? TMB_STATUS_TARGET_VALUES : 0) | ((u64)pl >= (u64)C ? TMB_STATUS_PREDS_VALUES : 0);
+  key = tl * C + pl;
   if (key < 0 || key >= CC) {
-    bad = 1;
+    bad |= TMB_STATUS_LABEL_RANGE;
     return false;
   }
   return true;
@@ -100,7 +102,7 @@ confmat_global_kernel(const PT* __restrict__ preds, const TT* __restrict__ targe
     long long key;
     if (make_key(preds[i], target[i], C, CC, has_ignore, ignore, key, bad)) atomicAdd(confmat + key, 1ULL);
   }
-  if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
+  if (bad) report_status(status, bad);
 }
 
 // ---- small C: shared-memory privatised ----------------------------------------------------------
@@ -143,7 +145,7 @@ confmat_smem_kernel(const PT* __restrict__ preds, const TT* __restrict__ target,
     for (int w = 0; w < copies; ++w) c += hist[w * CC + i];
     if (c) atomicAdd(confmat + i, c);
   }
-  if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
+  if (bad) report_status(status, bad);
 }
 
 // plain histogram of one label tensor (utilities/data.py:179-207 `_bincount`): global RED per element
@@ -165,7 +167,7 @@ bincount_kernel(const PT* __restrict__ x, long long n, long long nbins, u64* __r
     long long k = as_i64(x[(nvec << 2) + threadIdx.x]);
     if (k < 0 || k >= nbins) bad = 1; else atomicAdd(out + k, 1ULL);
   }
-  if (bad) atomicOr(status, TMB_STATUS_LABEL_RANGE);
+  if (bad) report_status(status, bad);
 }
 
 // n_valid / n_equal (multiclass micro statistics)

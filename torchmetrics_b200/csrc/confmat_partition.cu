@@ -71,17 +71,19 @@ constexpr u32 kNoSlot = (u32)kMaxBuckets << 12;  // "bucket" kMaxBuckets: a dumm
 
 template <typename PT, typename TT, bool HAS_IGNORE>
 __device__ __forceinline__ u32 slot_of(PT pv, TT tv, const PartParams& P, int& bad) {
-  const long long tl = as_i64(tv);
-  const long long k = tl * P.C + as_i64(pv);
+  const long long tl = as_i64(tv), pl = as_i64(pv);
+  const long long k = tl * P.C + pl;
   const bool in_range = (u64)k < (u64)P.CC;
+  // fused validation bits (TMB_STATUS_*): key range, target range, pred range
+  int flags = (in_range ? 0 : TMB_STATUS_LABEL_RANGE) | ((u64)tl >= (u64)P.C ? TMB_STATUS_TARGET_VALUES : 0) |
+              ((u64)pl >= (u64)P.C ? TMB_STATUS_PREDS_VALUES : 0);
   bool counted = in_range;
   if constexpr (HAS_IGNORE) {
     const bool ign = tl == P.ignore;
-    bad |= (int)(!in_range & !ign);
+    flags = ign ? 0 : flags;
     counted = in_range & !ign;
-  } else {
-    bad |= (int)!in_range;
   }
+  bad |= flags;
   const u32 packed = pack_slot((u32)k, P);
   return counted ? packed : kNoSlot;
 }
@@ -235,7 +237,7 @@ __global__ void __launch_bounds__(kPartThreads, kPartCtasPerSm) confmat_partitio
     const u32 b = kScanPer * tid + k;
     if (b < P.nb) P.fill[(size_t)b * P.G + blockIdx.x] = s_fill[b];
   }
-  if (bad) atomicOr(P.status, TMB_STATUS_LABEL_RANGE);
+  if (bad) report_status(P.status, bad);
 }
 
 __global__ void __launch_bounds__(kHistThreads) confmat_bucket_hist_kernel(const PartParams P) {

@@ -34,6 +34,7 @@ struct StatParams {
   int check_range;
   int only_if_flag;
   int range_check_ignored;  // 1: ignored positions take part in the [0,1] check (stat-scores _format order)
+  int* status;              // fused validation bits (may be null)
   u64* out;  // [4][L]
   StatWs* ws;
 };
@@ -62,8 +63,10 @@ struct Counts {
 
 template <typename PT, typename TT, bool SIGMOID>
 __device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typename CmpType<PT>::type thr, Counts& c,
-                                      int& oor) {
+                                      int& oor, int& vbits) {
   long long t = as_i64(tv);
+  // fused validation: a target that is neither 0, 1 nor the ignore value
+  vbits |= ((u64)t > 1ULL && !(P.has_ignore && t == P.ignore)) ? TMB_STATUS_TARGET_VALUES : 0;
   if constexpr (IsFloatScore<PT>::value) {
     using CT = typename CmpType<PT>::type;
     CT p = to_cmp(pv);
@@ -79,8 +82,9 @@ __device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typenam
     c.fp += (t == 0) & pb;
     c.tn += (t == 0) & !pb;
   } else {
-    if (P.has_ignore && t == P.ignore) return;
     long long p = as_i64(pv);
+    vbits |= (u64)p > 1ULL ? TMB_STATUS_PREDS_VALUES : 0;
+    if (P.has_ignore && t == P.ignore) return;
     const bool eq = (t == p);
     c.tp += (t == 1) & eq;
     c.fn += (t == 1) & !eq;
@@ -104,7 +108,7 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
   const CT thr = threshold_as<PT>(P.threshold);
   const long long L = P.L;
   u64* acc = reinterpret_cast<u64*>(ws + 1);
-  int oor = 0;
+  int oor = 0, vbits = 0;
   Counts c[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) c[j] = Counts{0, 0, 0, 0};
@@ -128,7 +132,7 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
       Vec4<PT> p = load4(preds + 4 * g);
       Vec4<TT> t = load4(target + 4 * g);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[0], oor);
+      for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[0], oor, vbits);
       if (P.check_range && (it & 63) == 63) {
         if (oor) atomicOr(&ws->flag_oor, 1);
         if (*(volatile int*)&ws->flag_oor) break;
@@ -136,7 +140,7 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
     }
     if (blockIdx.x == 0 && tid < (n & 3)) {
       long long i = (nvec << 2) + tid;
-      tally<PT, TT, SIGMOID>(preds[i], target[i], P, thr, c[0], oor);
+      tally<PT, TT, SIGMOID>(preds[i], target[i], P, thr, c[0], oor, vbits);
     }
   } else {
     const int r0 = tid / CW;
@@ -151,9 +155,9 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
           Vec4<PT> p = load4(preds + e);
           Vec4<TT> t = load4(target + e);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[j], oor);
+          for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[j], oor, vbits);
         } else {
-          tally<PT, TT, SIGMOID>(preds[e], target[e], P, thr, c[0], oor);
+          tally<PT, TT, SIGMOID>(preds[e], target[e], P, thr, c[0], oor, vbits);
         }
         if (P.check_range && (it & 63) == 63) {
           if (oor) atomicOr(&ws->flag_oor, 1);
@@ -163,6 +167,7 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
     }
   }
   if (P.check_range && oor) atomicOr(&ws->flag_oor, 1);
+  if (vbits && P.status) report_status(P.status, vbits);
 
   // merge: registers -> shared (per CTA) -> global scratch
   if (active) {
@@ -269,7 +274,7 @@ extern "C" size_t tmb_stat_scores_workspace_bytes(int64_t num_labels) {
 extern "C" int tmb_stat_scores_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
                                       int64_t n_rows, int64_t num_labels, double threshold, int prob_mode,
                                       int has_ignore, int64_t ignore_index, int range_check_ignored, int64_t* out,
-                                      void* workspace, size_t workspace_bytes, void* stream) {
+                                      void* workspace, size_t workspace_bytes, int32_t* status, void* stream) {
   if (n_rows < 0 || num_labels < 1 || !out || !workspace) return TMB_ERR_ARG;
   if (workspace_bytes < tmb_stat_scores_workspace_bytes(num_labels)) return TMB_ERR_ARG;
   if (n_rows == 0) return TMB_OK;
@@ -285,6 +290,7 @@ extern "C" int tmb_stat_scores_update(const void* preds, int preds_dtype, const 
   P.ignore = ignore_index;
   P.range_check_ignored = range_check_ignored ? 1 : 0;
   P.out = (u64*)out;
+  P.status = status;
   P.ws = (StatWs*)workspace;
   cudaStream_t st = (cudaStream_t)stream;
   if (is_float_dtype(preds_dtype)) {

@@ -6,11 +6,13 @@ precision_recall_curve.py:94-159, :360-420, :684-736).  Value checks avoid the r
 the passing path: labels inside the legal set cannot have too many distinct values, so one min/max (or one masked
 `any`) pass decides; only an input that is about to fail pays for the exact unique count used in the message.
 """
-from typing import List, Optional, Sequence, Union
+import threading
+from typing import Callable, List, Optional, Sequence, Union
 
 import torch
 from torch import Tensor
 
+from torchmetrics_b200 import _native
 from torchmetrics_b200.utilities.checks import _check_same_shape
 
 
@@ -54,8 +56,85 @@ def check_thresholds_arg(thresholds: Optional[Union[int, List[float], Tensor]]) 
         raise ValueError("If argument `thresholds` is an tensor, expected the tensor to be 1d")
 
 
+# ------------------------------------------------------------------------------------------------------------
+# Fused value validation.  The reference validates label values in separate passes over the
+# inputs before every update (torch.unique, e.g. stat_scores.py:67-87, confusion_matrix.py:98-115).  The update
+# kernels look at every label anyway, so they note "target outside its value set" / "label preds outside theirs"
+# in a device status word; the host then reads 8 bytes after the kernel instead of re-reading the inputs, and
+# only when a bit is set runs the reference-style check below to produce the reference's verdict and message.
+# ------------------------------------------------------------------------------------------------------------
+_tls = threading.local()
+
+
+class FusedValidation:
+    """Collects the value checks of one `_tensor_validation` call and settles them after the update kernel.
+
+        fv = FusedValidation(validate_args, preds, target)
+        with fv:
+            _xxx_tensor_validation(preds, target, ...)   # shape/dtype checks run now, value checks are recorded
+        ... launch the fused update ...
+        fv.finish(device, num_classes, undo)            # status word -> run the recorded checks only if flagged
+
+    When not enabled (CPU tensors, or an update path whose kernel does not report values) the checks run
+    immediately and `finish` does nothing.
+    """
+
+    def __init__(self, validate_args: bool, preds: Tensor, target: Tensor, fused_path: bool = True) -> None:
+        self.enabled = bool(validate_args and fused_path and preds.is_cuda and target.is_cuda)
+        self.pending: List[Callable[[], None]] = []
+
+    def __enter__(self) -> "FusedValidation":
+        if self.enabled:
+            _tls.sink = self.pending
+        return self
+
+    def __exit__(self, *exc) -> None:
+        _tls.sink = None
+
+    def finish(self, dev: torch.device, num_classes: Optional[int] = None,
+               undo: Optional[Callable[[], None]] = None, errors: bool = False) -> None:
+        """`errors`: also settle the kernel's error bits (label outside the matrix) when validation is off."""
+        if not self.enabled:
+            if errors and dev.type == "cuda":
+                _native.raise_on_status(dev, num_classes)
+            return
+        err, val = _native.read_status_words(dev)
+        if val:
+            try:
+                for chk in self.pending:
+                    chk()
+            except Exception:
+                if undo is not None:
+                    undo()
+                raise
+        _native.raise_for_bits(err, num_classes)
+
+
+def _deferred(fn: Callable, t: Tensor, *args) -> bool:
+    sink = getattr(_tls, "sink", None)
+    if sink is None or not t.is_cuda:
+        return False
+    sink.append(lambda: fn(t, *args))
+    return True
+
+
+def rollback(state: Tensor, redo: Callable[[Tensor], object]) -> None:
+    """Remove one batch from an int64 accumulator that a fused update already touched: its counts are a
+    deterministic function of the inputs, so computing them again into zeros and subtracting is exact."""
+    tmp = torch.zeros_like(state)
+    redo(tmp)
+    state -= tmp
+    _native.read_status_words(state.device)
+
+
 def check_binary_values(t: Tensor, name: str, ignore_index: Optional[int] = None, what: str = "") -> None:
     """Every value must be 0, 1 (or ignore_index); one fused elementwise pass + any()."""
+    if _deferred(_check_binary_values_now, t, name, ignore_index, what):
+        return
+    _check_binary_values_now(t, name, ignore_index, what)
+
+
+def _check_binary_values_now(t: Tensor, name: str, ignore_index: Optional[int] = None, what: str = "") -> None:
     bad = (t != 0) & (t != 1)
     if ignore_index is not None:
         bad &= t != ignore_index
@@ -74,6 +153,12 @@ def check_binary_values(t: Tensor, name: str, ignore_index: Optional[int] = None
 
 def check_label_count(t: Tensor, name: str, num_classes: int, ignore_index: Optional[int] = None) -> None:
     """The reference rejects tensors with more distinct values than classes (+1 for ignore_index)."""
+    if _deferred(_check_label_count_now, t, name, num_classes, ignore_index):
+        return
+    _check_label_count_now(t, name, num_classes, ignore_index)
+
+
+def _check_label_count_now(t: Tensor, name: str, num_classes: int, ignore_index: Optional[int] = None) -> None:
     if t.numel() == 0:
         return
     allowed = num_classes + (1 if (ignore_index is not None and name == "target") else 0)

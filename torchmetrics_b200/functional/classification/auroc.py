@@ -72,8 +72,7 @@ def binary_auroc(preds: Tensor, target: Tensor, max_fpr: Optional[float] = None,
                  validate_args: bool = True) -> Tensor:
     if validate_args:
         _binary_auroc_arg_validation(max_fpr, thresholds, ignore_index)
-        P._binary_precision_recall_curve_tensor_validation(preds, target, ignore_index)
-    state, thr = P._binary_curve_state(preds, target, thresholds, ignore_index)
+    state, thr = P._binary_curve_state(preds, target, thresholds, ignore_index, validate=validate_args)
     return _binary_auroc_compute(state, thr, max_fpr)
 
 
@@ -100,8 +99,8 @@ def multiclass_auroc(preds: Tensor, target: Tensor, num_classes: int,
                      validate_args: bool = True) -> Tensor:
     if validate_args:
         _multiclass_auroc_arg_validation(num_classes, average, thresholds, ignore_index)
-        P._multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
-    state, thr = P._multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index)
+    state, thr = P._multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index,
+                                           validate=validate_args)
     return _multiclass_auroc_compute(state, num_classes, average, thr)
 
 
@@ -135,8 +134,8 @@ def multilabel_auroc(preds: Tensor, target: Tensor, num_labels: int,
                      validate_args: bool = True) -> Tensor:
     if validate_args:
         _multilabel_auroc_arg_validation(num_labels, average, thresholds, ignore_index)
-        P._multilabel_precision_recall_curve_tensor_validation(preds, target, num_labels, ignore_index)
-    state, thr = P._multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index)
+    state, thr = P._multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index,
+                                           validate=validate_args)
     return _multilabel_auroc_compute(state, num_labels, average, thr, ignore_index)
 
 

@@ -47,8 +47,7 @@ def binary_average_precision(preds: Tensor, target: Tensor,
                              ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
     if validate_args:
         P._binary_precision_recall_curve_arg_validation(thresholds, ignore_index)
-        P._binary_precision_recall_curve_tensor_validation(preds, target, ignore_index)
-    state, thr = P._binary_curve_state(preds, target, thresholds, ignore_index)
+    state, thr = P._binary_curve_state(preds, target, thresholds, ignore_index, validate=validate_args)
     return _binary_average_precision_compute(state, thr)
 
 
@@ -75,8 +74,8 @@ def multiclass_average_precision(preds: Tensor, target: Tensor, num_classes: int
                                  ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
     if validate_args:
         _multiclass_average_precision_arg_validation(num_classes, average, thresholds, ignore_index)
-        P._multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
-    state, thr = P._multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index)
+    state, thr = P._multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index,
+                                           validate=validate_args)
     return _multiclass_average_precision_compute(state, num_classes, average, thr)
 
 
@@ -113,8 +112,8 @@ def multilabel_average_precision(preds: Tensor, target: Tensor, num_labels: int,
                                  ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
     if validate_args:
         _multilabel_average_precision_arg_validation(num_labels, average, thresholds, ignore_index)
-        P._multilabel_precision_recall_curve_tensor_validation(preds, target, num_labels, ignore_index)
-    state, thr = P._multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index)
+    state, thr = P._multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index,
+                                           validate=validate_args)
     return _multilabel_average_precision_compute(state, num_labels, average, thr, ignore_index)
 
 

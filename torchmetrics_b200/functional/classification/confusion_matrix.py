@@ -106,11 +106,13 @@ def _binary_confusion_matrix_compute(confmat: Tensor, normalize: Optional[str] =
 def binary_confusion_matrix(preds: Tensor, target: Tensor, threshold: float = 0.5,
                             normalize: Optional[Literal["true", "pred", "all", "none"]] = None,
                             ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    fv = C.FusedValidation(validate_args, preds, target)
     if validate_args:
         _binary_confusion_matrix_arg_validation(threshold, ignore_index, normalize)
-        _binary_confusion_matrix_tensor_validation(preds, target, ignore_index)
+        with fv:
+            _binary_confusion_matrix_tensor_validation(preds, target, ignore_index)
     confmat = _binary_confusion_matrix_update_fused(preds, target, threshold, ignore_index)
-    _native.raise_on_status(preds.device, 2)
+    fv.finish(preds.device, 2, errors=True)
     return _binary_confusion_matrix_compute(confmat, normalize)
 
 
@@ -168,11 +170,13 @@ def _multiclass_confusion_matrix_compute(confmat: Tensor, normalize: Optional[st
 def multiclass_confusion_matrix(preds: Tensor, target: Tensor, num_classes: int,
                                 normalize: Optional[Literal["true", "pred", "all", "none"]] = None,
                                 ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    fv = C.FusedValidation(validate_args, preds, target)
     if validate_args:
         _multiclass_confusion_matrix_arg_validation(num_classes, ignore_index, normalize)
-        _multiclass_confusion_matrix_tensor_validation(preds, target, num_classes, ignore_index)
+        with fv:
+            _multiclass_confusion_matrix_tensor_validation(preds, target, num_classes, ignore_index)
     confmat = _multiclass_confusion_matrix_update_fused(preds, target, num_classes, ignore_index)
-    _native.raise_on_status(preds.device, num_classes)
+    fv.finish(preds.device, num_classes, errors=True)
     return _multiclass_confusion_matrix_compute(confmat, normalize)
 
 
@@ -226,7 +230,7 @@ def _multilabel_confusion_matrix_update(preds: Tensor, target: Tensor, num_label
     entries negative — K2 counts an element only when target is 0 or 1."""
     stats = torch.zeros(4, num_labels, dtype=torch.int64, device=preds.device)
     _native.stat_scores_update_(stats, preds.to(torch.int64) if preds.dtype == torch.bool else preds, target,
-                                num_labels, 0.5, None, _native.PROB_AS_IS)
+                                num_labels, 0.5, None, _native.PROB_AS_IS, report_values=False)
     return _stats_to_confmat(stats)
 
 
@@ -254,10 +258,13 @@ def _multilabel_confusion_matrix_compute(confmat: Tensor, normalize: Optional[st
 def multilabel_confusion_matrix(preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
                                 normalize: Optional[Literal["true", "pred", "all", "none"]] = None,
                                 ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    fv = C.FusedValidation(validate_args, preds, target)
     if validate_args:
         _multilabel_confusion_matrix_arg_validation(num_labels, threshold, ignore_index, normalize)
-        _multilabel_confusion_matrix_tensor_validation(preds, target, num_labels, ignore_index)
+        with fv:
+            _multilabel_confusion_matrix_tensor_validation(preds, target, num_labels, ignore_index)
     confmat = _multilabel_confusion_matrix_update_fused(preds, target, num_labels, threshold, ignore_index)
+    fv.finish(preds.device)
     return _multilabel_confusion_matrix_compute(confmat, normalize)
 
 

@@ -163,20 +163,25 @@ def binary_precision_recall_curve(preds: Tensor, target: Tensor,
                                   ) -> Tuple[Tensor, Tensor, Tensor]:
     if validate_args:
         _binary_precision_recall_curve_arg_validation(thresholds, ignore_index)
-        _binary_precision_recall_curve_tensor_validation(preds, target, ignore_index)
-    state, thr = _binary_curve_state(preds, target, thresholds, ignore_index)
+    state, thr = _binary_curve_state(preds, target, thresholds, ignore_index, validate=validate_args)
     return _binary_precision_recall_curve_compute(state, thr)
 
 
-def _binary_curve_state(preds: Tensor, target: Tensor, thresholds, ignore_index: Optional[int]):
-    """State + threshold tensor for the one-shot functionals (binned -> fused K3, exact -> formatted inputs)."""
+def _binary_curve_state(preds: Tensor, target: Tensor, thresholds, ignore_index: Optional[int],
+                        validate: bool = False):
+    """State + threshold tensor for the one-shot functionals (binned -> fused K3, exact -> formatted inputs).
+    `validate`: run `_tensor_validation` too — its target-value check rides on the K3 pass in binned mode."""
+    fv = C.FusedValidation(validate, preds, target, thresholds is not None)
+    if validate:
+        with fv:
+            _binary_precision_recall_curve_tensor_validation(preds, target, ignore_index)
     if thresholds is None:
         p, t, _ = _binary_precision_recall_curve_format(preds, target, None, ignore_index)
         return (p, t), None
     thr = _adjust_threshold_arg(thresholds, preds.device)
     state = _binary_precision_recall_curve_update_fused(preds, target, thr, ignore_index,
                                                         assume_sorted=isinstance(thresholds, int))
-    _native.raise_on_status(preds.device)
+    fv.finish(preds.device, errors=True)
     return state, thr
 
 
@@ -325,13 +330,19 @@ def _multiclass_precision_recall_curve_compute(state: Union[Tensor, Tuple[Tensor
     return precision_list, recall_list, thres_list
 
 
-def _multiclass_curve_state(preds: Tensor, target: Tensor, num_classes: int, thresholds, ignore_index, average=None):
+def _multiclass_curve_state(preds: Tensor, target: Tensor, num_classes: int, thresholds, ignore_index, average=None,
+                            validate: bool = False):
+    fv = C.FusedValidation(validate, preds, target, thresholds is not None)
+    if validate:
+        with fv:
+            _multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
     if thresholds is None:
         p, t, _ = _multiclass_precision_recall_curve_format(preds, target, num_classes, None, ignore_index, average)
         return (p, t), None
     thr = _adjust_threshold_arg(thresholds, preds.device)
     state = _multiclass_precision_recall_curve_update_fused(preds, target, num_classes, thr, ignore_index, average,
                                                             assume_sorted=isinstance(thresholds, int))
+    fv.finish(preds.device)
     return state, thr
 
 
@@ -341,8 +352,8 @@ def multiclass_precision_recall_curve(preds: Tensor, target: Tensor, num_classes
                                       ignore_index: Optional[int] = None, validate_args: bool = True):
     if validate_args:
         _multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index, average)
-        _multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
-    state, thr = _multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index, average)
+    state, thr = _multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index, average,
+                                         validate=validate_args)
     return _multiclass_precision_recall_curve_compute(state, num_classes, thr, average)
 
 
@@ -425,14 +436,19 @@ def _multilabel_precision_recall_curve_compute(state: Union[Tensor, Tuple[Tensor
     return precision_list, recall_list, thres_list
 
 
-def _multilabel_curve_state(preds: Tensor, target: Tensor, num_labels: int, thresholds, ignore_index):
+def _multilabel_curve_state(preds: Tensor, target: Tensor, num_labels: int, thresholds, ignore_index,
+                            validate: bool = False):
+    fv = C.FusedValidation(validate, preds, target, thresholds is not None)
+    if validate:
+        with fv:
+            _multilabel_precision_recall_curve_tensor_validation(preds, target, num_labels, ignore_index)
     if thresholds is None:
         p, t, _ = _multilabel_precision_recall_curve_format(preds, target, num_labels, None, ignore_index)
         return (p, t), None
     thr = _adjust_threshold_arg(thresholds, preds.device)
     state = _multilabel_precision_recall_curve_update_fused(preds, target, num_labels, thr, ignore_index,
                                                             assume_sorted=isinstance(thresholds, int))
-    _native.raise_on_status(preds.device)
+    fv.finish(preds.device, errors=True)
     return state, thr
 
 
@@ -441,8 +457,7 @@ def multilabel_precision_recall_curve(preds: Tensor, target: Tensor, num_labels:
                                       ignore_index: Optional[int] = None, validate_args: bool = True):
     if validate_args:
         _multilabel_precision_recall_curve_arg_validation(num_labels, thresholds, ignore_index)
-        _multilabel_precision_recall_curve_tensor_validation(preds, target, num_labels, ignore_index)
-    state, thr = _multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index)
+    state, thr = _multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index, validate=validate_args)
     return _multilabel_precision_recall_curve_compute(state, num_labels, thr, ignore_index)
 
 

@@ -50,8 +50,7 @@ def binary_roc(preds: Tensor, target: Tensor, thresholds: Optional[Union[int, Li
                ignore_index: Optional[int] = None, validate_args: bool = True) -> Tuple[Tensor, Tensor, Tensor]:
     if validate_args:
         P._binary_precision_recall_curve_arg_validation(thresholds, ignore_index)
-        P._binary_precision_recall_curve_tensor_validation(preds, target, ignore_index)
-    state, thr = P._binary_curve_state(preds, target, thresholds, ignore_index)
+    state, thr = P._binary_curve_state(preds, target, thresholds, ignore_index, validate=validate_args)
     return _binary_roc_compute(state, thr)
 
 
@@ -96,8 +95,8 @@ def multiclass_roc(preds: Tensor, target: Tensor, num_classes: int,
                    validate_args: bool = True):
     if validate_args:
         P._multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index, average)
-        P._multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
-    state, thr = P._multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index, average)
+    state, thr = P._multiclass_curve_state(preds, target, num_classes, thresholds, ignore_index, average,
+                                           validate=validate_args)
     return _multiclass_roc_compute(state, num_classes, thr, average)
 
 
@@ -127,8 +126,8 @@ def multilabel_roc(preds: Tensor, target: Tensor, num_labels: int,
                    validate_args: bool = True):
     if validate_args:
         P._multilabel_precision_recall_curve_arg_validation(num_labels, thresholds, ignore_index)
-        P._multilabel_precision_recall_curve_tensor_validation(preds, target, num_labels, ignore_index)
-    state, thr = P._multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index)
+    state, thr = P._multilabel_curve_state(preds, target, num_labels, thresholds, ignore_index,
+                                           validate=validate_args)
     return _multilabel_roc_compute(state, num_labels, thr, ignore_index)
 
 

@@ -71,7 +71,7 @@ def _binary_stat_scores_update(preds: Tensor, target: Tensor, multidim_average: 
     """Counts over formatted label tensors (stat_scores.py:120-131); global -> K2 with one label."""
     if multidim_average == "global":
         stats = torch.zeros(4, 1, dtype=torch.int64, device=preds.device)
-        _native.stat_scores_update_(stats, preds, target, 1, 0.5, None, _native.PROB_AS_IS)
+        _native.stat_scores_update_(stats, preds, target, 1, 0.5, None, _native.PROB_AS_IS, report_values=False)
         return stats[0, 0], stats[1, 0], stats[2, 0], stats[3, 0]
     tp, fp, tn, fn = _four_masked_sums(preds, target, [1])
     return tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze()
@@ -97,10 +97,13 @@ def _binary_stat_scores_compute(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor,
 def binary_stat_scores(preds: Tensor, target: Tensor, threshold: float = 0.5,
                        multidim_average: Literal["global", "samplewise"] = "global",
                        ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    fv = C.FusedValidation(validate_args, preds, target, multidim_average == "global")
     if validate_args:
         _binary_stat_scores_arg_validation(threshold, multidim_average, ignore_index)
-        _binary_stat_scores_tensor_validation(preds, target, multidim_average, ignore_index)
+        with fv:
+            _binary_stat_scores_tensor_validation(preds, target, multidim_average, ignore_index)
     tp, fp, tn, fn = _binary_stat_scores_update_fused(preds, target, threshold, multidim_average, ignore_index)
+    fv.finish(preds.device)
     return _binary_stat_scores_compute(tp, fp, tn, fn, multidim_average)
 
 
@@ -187,6 +190,11 @@ def _multiclass_stat_scores_onehot(preds: Tensor, target: Tensor, num_classes: i
     return _four_masked_sums(preds_oh, target_oh, [0, 1] if multidim_average == "global" else [1])
 
 
+def _multiclass_stat_scores_reports_values(top_k: int, average: Optional[str], multidim_average: str) -> bool:
+    """True when `_multiclass_stat_scores_update` goes through K1, whose kernel validates label values as it counts."""
+    return multidim_average == "global" and top_k == 1 and average != "micro"
+
+
 def _multiclass_stat_scores_update_fused(preds: Tensor, target: Tensor, num_classes: int, top_k: int = 1,
                                          average: Optional[str] = "macro", multidim_average: str = "global",
                                          ignore_index: Optional[int] = None):
@@ -217,12 +225,15 @@ def multiclass_stat_scores(preds: Tensor, target: Tensor, num_classes: int,
                            average: Optional[Literal["micro", "macro", "weighted", "none"]] = "macro", top_k: int = 1,
                            multidim_average: Literal["global", "samplewise"] = "global",
                            ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    fv = C.FusedValidation(validate_args, preds, target,
+                           _multiclass_stat_scores_reports_values(top_k, average, multidim_average))
     if validate_args:
         _multiclass_stat_scores_arg_validation(num_classes, top_k, average, multidim_average, ignore_index)
-        _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
+        with fv:
+            _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
     tp, fp, tn, fn = _multiclass_stat_scores_update_fused(preds, target, num_classes, top_k, average,
                                                           multidim_average, ignore_index)
-    _native.raise_on_status(preds.device, num_classes)
+    fv.finish(preds.device, num_classes, errors=True)
     return _multiclass_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
 
 
@@ -267,7 +278,7 @@ def _multilabel_stat_scores_update(preds: Tensor, target: Tensor, multidim_avera
         L = preds.shape[1]
         stats = torch.zeros(4, L, dtype=torch.int64, device=preds.device)
         _native.stat_scores_update_(stats, _label_major(preds, L), _label_major(target, L), L, 0.5, None,
-                                    _native.PROB_AS_IS)
+                                    _native.PROB_AS_IS, report_values=False)
         return stats[0], stats[1], stats[2], stats[3]
     tp, fp, tn, fn = _four_masked_sums(preds, target, [-1])
     return tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze()
@@ -306,11 +317,14 @@ def multilabel_stat_scores(preds: Tensor, target: Tensor, num_labels: int, thres
                            average: Optional[Literal["micro", "macro", "weighted", "none"]] = "macro",
                            multidim_average: Literal["global", "samplewise"] = "global",
                            ignore_index: Optional[int] = None, validate_args: bool = True) -> Tensor:
+    fv = C.FusedValidation(validate_args, preds, target, multidim_average == "global")
     if validate_args:
         _multilabel_stat_scores_arg_validation(num_labels, threshold, average, multidim_average, ignore_index)
-        _multilabel_stat_scores_tensor_validation(preds, target, num_labels, multidim_average, ignore_index)
+        with fv:
+            _multilabel_stat_scores_tensor_validation(preds, target, num_labels, multidim_average, ignore_index)
     tp, fp, tn, fn = _multilabel_stat_scores_update_fused(preds, target, num_labels, threshold, multidim_average,
                                                           ignore_index)
+    fv.finish(preds.device)
     return _multilabel_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
 
 
