@@ -106,6 +106,58 @@ __device__ __forceinline__ Vec4<T> load4(const T* p) {
   return r;
 }
 
+// ---- L2 residency hints -------------------------------------------------------------------------------------
+// A batch streamed once should not push out the few MB a kernel pair hands over through the L2 (K1's queues):
+// the stream is read "evict first", the hand-over is written "evict last" and read back "evict first".
+__device__ __forceinline__ u64 l2_policy_evict_first() {
+  u64 pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ u64 l2_policy_evict_last() {
+  u64 pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+template <typename T>
+__device__ __forceinline__ Vec4<T> load4_hint(const T* p, u64 pol) {
+  Vec4<T> r;
+  if constexpr (sizeof(T) == 8) {
+    u64 a, b, c, d;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u64 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=l"(a), "=l"(b), "=l"(c), "=l"(d)
+                 : "l"(p), "l"(pol));
+    r.v[0] = *reinterpret_cast<T*>(&a);
+    r.v[1] = *reinterpret_cast<T*>(&b);
+    r.v[2] = *reinterpret_cast<T*>(&c);
+    r.v[3] = *reinterpret_cast<T*>(&d);
+  } else if constexpr (sizeof(T) == 4) {
+    u32 a, b, c, d;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
+                 : "l"(p), "l"(pol));
+    r.v[0] = *reinterpret_cast<T*>(&a);
+    r.v[1] = *reinterpret_cast<T*>(&b);
+    r.v[2] = *reinterpret_cast<T*>(&c);
+    r.v[3] = *reinterpret_cast<T*>(&d);
+  } else {
+    r = load4(p);
+  }
+  return r;
+}
+__device__ __forceinline__ void store16_hint(void* p, const uint4& w, u64 pol) {
+  asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1,%2,%3,%4}, %5;"
+               :: "l"(p), "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ uint4 load16_hint(const void* p, u64 pol) {
+  uint4 r;
+  asm volatile("ld.global.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p), "l"(pol));
+  return r;
+}
+
 // Scores are compared in float (f32/f16/bf16 convert exactly) or in double (f64), which is what torch's
 // type promotion does for `preds >= thresholds` with float32 thresholds.
 template <typename T>

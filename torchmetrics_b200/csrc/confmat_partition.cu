@@ -40,6 +40,8 @@ struct PartParams {
   long long CC;
   u32 nb;          // number of buckets
   u32 magic;       // ceil(2^32 / nb): key / nb == __umulhi(key, magic) for key < 2^22, nb <= 1024
+  u32 lognb;       // streaming phase A: nb is a power of two
+  u32 cap;         // streaming phase A: FIFO entries per bucket
   int has_ignore;
   long long ignore;
   u32 G;           // CTAs of phase A == segments per bucket
@@ -240,9 +242,150 @@ __global__ void __launch_bounds__(kPartThreads, kPartCtasPerSm) confmat_partitio
   if (bad) report_status(P.status, bad);
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Phase A, streaming variant: per-bucket FIFOs in shared memory instead of rank / scan / stage.
+//   A sample reserves a FIFO slot with one shared-memory atomic on its bucket's counter and stores its 12-bit local
+//   bin there; nothing is kept in registers across a barrier.  After every tile one thread per bucket copies the
+//   bucket's full 8-entry chunks (16-byte vector stores) to this CTA's segment of the bucket and moves the < 8
+//   leftover entries to the front of the FIFO, so segments only ever grow by aligned chunks.  An entry that finds
+//   its FIFO full (a bucket far heavier than the others) is counted with a direct RED, lanes merged first.
+//   Here nb is a power of two: bucket = group & (nb - 1), local bin = ((group >> lognb) << 4) | (key & 15).
+// ------------------------------------------------------------------------------------------------------------
+constexpr int kFifoThreads = 512;
+constexpr int kFifoItems = 16;
+constexpr int kFifoTile = kFifoThreads * kFifoItems;
+constexpr int kFifoCtasPerSm = 2;
+constexpr int kFifoEntries = 24576;  // u16 FIFO entries per CTA, split evenly over the buckets
+
+template <typename PT, typename TT, bool HAS_IGNORE>
+__global__ void __launch_bounds__(kFifoThreads, kFifoCtasPerSm) confmat_fifo_partition_kernel(const PartParams P) {
+  extern __shared__ uint4 smem_dyn[];
+  u32* const s_cnt = reinterpret_cast<u32*>(smem_dyn);               // [nb] entries waiting in each FIFO
+  u32* const s_fill = s_cnt + kMaxBuckets;                           // [nb] entries appended to each segment so far
+  unsigned short* const s_fifo = reinterpret_cast<unsigned short*>(s_fill + kMaxBuckets);  // [nb][cap]
+  const int tid = threadIdx.x;
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  const long long n = P.n;
+  const long long ntiles = (n + kFifoTile - 1) / kFifoTile;
+  const u32 nb = P.nb, lognb = P.lognb, cap = P.cap, nbmask = nb - 1;
+  const u32 C32 = (u32)P.C;
+  int bad = 0;
+  const u64 pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
+  for (u32 b = tid; b < nb; b += kFifoThreads) {
+    s_cnt[b] = 0;
+    s_fill[b] = 0;
+  }
+  __syncthreads();
+
+  auto push = [&](PT pv, TT tv) {
+    const long long tl = as_i64(tv), pl = as_i64(pv);
+    bool counted = true;
+    if constexpr (HAS_IGNORE) counted = tl != P.ignore;
+    u32 key = (u32)tl * C32 + (u32)pl;
+    if (((u64)tl >= (u64)P.C) | ((u64)pl >= (u64)P.C)) {  // rare: the reference still counts a key that aliases
+      if (counted) {
+        const long long k = tl * P.C + pl;
+        const bool in_range = (u64)k < (u64)P.CC;
+        bad |= (in_range ? 0 : TMB_STATUS_LABEL_RANGE) | ((u64)tl >= (u64)P.C ? TMB_STATUS_TARGET_VALUES : 0) |
+               ((u64)pl >= (u64)P.C ? TMB_STATUS_PREDS_VALUES : 0);
+        counted = in_range;
+        key = (u32)k;
+      }
+    }
+    if (counted) {
+      const u32 group = key >> 4;
+      const u32 b = group & nbmask;
+      const u32 lbin = ((group >> lognb) << 4) | (key & 15u);
+      const u32 pos = atomicAdd(&s_cnt[b], 1u);
+      if (pos < cap) {
+        s_fifo[b * cap + pos] = (unsigned short)lbin;
+      } else {
+        const unsigned peers = __match_any_sync(__activemask(), key);
+        if ((threadIdx.x & 31) == (u32)(__ffs(peers) - 1)) atomicAdd(P.confmat + key, (u64)__popc(peers));
+      }
+    }
+  };
+
+  unsigned short* const myq = P.queue + (size_t)blockIdx.x * P.segcap;
+  const u32 bstride = P.G * P.segcap;
+  // copy the full chunks of every FIFO to the segments; `final` also writes the partial chunk
+  auto flush = [&](bool final) {
+    for (u32 b = tid; b < nb; b += kFifoThreads) {
+      u32 c = s_cnt[b];
+      c = c < cap ? c : cap;
+      u32 off = s_fill[b];
+      const uint4* src = reinterpret_cast<const uint4*>(s_fifo + b * cap);
+      const u32 nchunks = final ? (c + 7) >> 3 : c >> 3;
+      unsigned short* seg = myq + b * bstride;
+      for (u32 k = 0; k < nchunks; ++k) {
+        const uint4 w = src[k];
+        const u32 cnt = (k * 8 + 8 <= c) ? 8u : (c - k * 8);
+        if (off + 8 <= P.segcap) {
+          store16_hint(seg + off, w, pol_keep);
+          off += cnt;
+        } else {  // segment full: this CTA saw far more than its share of the bucket
+          const u32 e[4] = {w.x, w.y, w.z, w.w};
+          for (u32 i = 0; i < cnt; ++i) {
+            const u32 lbin = (e[i >> 1] >> ((i & 1) * 16)) & 0xffffu;
+            atomicAdd(P.confmat + cell_of(b, lbin, nb), 1ULL);
+          }
+        }
+      }
+      if (!final) {
+        if (nchunks && (c & 7u)) reinterpret_cast<uint4*>(s_fifo + b * cap)[0] = src[nchunks];  // leftovers to the front
+        s_cnt[b] = c & 7u;
+      }
+      s_fill[b] = off;
+    }
+  };
+
+  Vec4<PT> pn;
+  Vec4<TT> tn;
+  long long tile = blockIdx.x;
+  if (tile < ntiles && tile * kFifoTile + kFifoTile <= n) {
+    pn = load4_hint(preds + tile * kFifoTile + (long long)tid * 4, pol_stream);
+    tn = load4_hint(target + tile * kFifoTile + (long long)tid * 4, pol_stream);
+  }
+  for (; tile < ntiles; tile += gridDim.x) {
+    const long long base = tile * kFifoTile;
+    if (base + kFifoTile <= n) {
+      const PT* pp = preds + base + (long long)tid * 4;
+      const TT* tp = target + base + (long long)tid * 4;
+#pragma unroll
+      for (int v = 0; v < kFifoItems / 4; ++v) {
+        const Vec4<PT> pc = pn;
+        const Vec4<TT> tc = tn;
+        if (v + 1 < kFifoItems / 4) {
+          pn = load4_hint(pp + (long long)(v + 1) * kFifoThreads * 4, pol_stream);
+          tn = load4_hint(tp + (long long)(v + 1) * kFifoThreads * 4, pol_stream);
+        } else {
+          // first vector of this CTA's next tile: in flight while the FIFOs are flushed
+          const long long nbase = (tile + gridDim.x) * kFifoTile;
+          if (nbase + kFifoTile <= n) {
+            pn = load4_hint(preds + nbase + (long long)tid * 4, pol_stream);
+            tn = load4_hint(target + nbase + (long long)tid * 4, pol_stream);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) push(pc.v[j], tc.v[j]);
+      }
+    } else {
+      for (long long e = base + tid; e < n; e += kFifoThreads) push(preds[e], target[e]);
+    }
+    __syncthreads();
+    flush(false);
+    __syncthreads();
+  }
+  flush(true);
+  for (u32 b = tid; b < nb; b += kFifoThreads) P.fill[(size_t)b * P.G + blockIdx.x] = s_fill[b];
+  if (bad) report_status(P.status, bad);
+}
+
 __global__ void __launch_bounds__(kHistThreads) confmat_bucket_hist_kernel(const PartParams P) {
   __shared__ u32 h[kBinsPerBucket];
   const u32 b = blockIdx.x;
+  const u64 pol_done = l2_policy_evict_first();  // the queue is dead once read
   for (int i = threadIdx.x; i < kBinsPerBucket; i += kHistThreads) h[i] = 0;
   __syncthreads();
   auto count8 = [&](const uint4& w) {
@@ -265,7 +408,7 @@ __global__ void __launch_bounds__(kHistThreads) confmat_bucket_hist_kernel(const
     const unsigned short* q = P.queue + ((size_t)b * P.G + seg) * P.segcap;  // 16-byte aligned (segcap % 8 == 0)
     const uint4* qv = reinterpret_cast<const uint4*>(q);
     const u32 nvec = len >> 3;
-    for (u32 i = lane; i < nvec; i += 32) count8(qv[i]);
+    for (u32 i = lane; i < nvec; i += 32) count8(load16_hint(qv + i, pol_done));
     for (u32 k = (nvec << 3) + lane; k < len; k += 32) atomicAdd(&h[q[k]], 1u);
   }
   __syncthreads();
@@ -275,7 +418,20 @@ __global__ void __launch_bounds__(kHistThreads) confmat_bucket_hist_kernel(const
   }
 }
 
-static u32 part_ctas() { return (u32)sm_count() * kPartCtasPerSm; }
+static int part_mode() {
+  static const int m = getenv("TMB_PARTA") ? atoi(getenv("TMB_PARTA")) : 1;
+  return m;
+}
+static u32 part_ctas() { return (u32)sm_count() * (part_mode() ? kFifoCtasPerSm : kPartCtasPerSm); }
+// buckets for a CC-cell matrix; 0 = not served by the partition path
+static long long part_buckets(long long CC) {
+  const long long need = (((CC + 15) >> 4) + (kBinsPerBucket / 16) - 1) / (kBinsPerBucket / 16);
+  if (need > kMaxBuckets) return 0;
+  if (!part_mode() || need < 2) return need;
+  long long nb = 256;  // few buckets mean many lanes of a warp on one counter
+  while (nb < need) nb <<= 1;
+  return nb;
+}
 static size_t part_header_bytes(u32 nb, u32 G) { return ((size_t)nb * G * 4 + 255) & ~(size_t)255; }
 
 }  // namespace tmb
@@ -285,8 +441,8 @@ using namespace tmb;
 extern "C" size_t tmb_confmat_workspace_bytes(int64_t n, int64_t num_classes) {
   if (n < 1 || num_classes < 1) return 0;
   const long long CC = (long long)num_classes * num_classes;
-  const long long nb = (((CC + 15) >> 4) + (kBinsPerBucket / 16) - 1) / (kBinsPerBucket / 16);
-  if (nb > kMaxBuckets) return 0;  // not served by the partition path
+  const long long nb = part_buckets(CC);
+  if (nb == 0) return 0;  // not served by the partition path
   const long long G = part_ctas();
   // per (bucket, CTA) segment: twice the uniform share plus slack, rounded to 8 entries (16 bytes)
   long long segcap = 2 * ((n + nb * G - 1) / (nb * G)) + 64;
@@ -303,8 +459,8 @@ extern "C" int tmb_confmat_update_ws(const void* preds, int preds_dtype, const v
   if (!preds || !target || !workspace) return TMB_ERR_ARG;
   if (!aligned32(preds) || !aligned32(target) || !aligned32(workspace)) return TMB_ERR_ALIGN;
   const long long CC = (long long)num_classes * num_classes;
-  const long long nb = (((CC + 15) >> 4) + (kBinsPerBucket / 16) - 1) / (kBinsPerBucket / 16);
-  if (nb > kMaxBuckets || n >= (1LL << 32)) return TMB_ERR_TOO_LARGE;
+  const long long nb = part_buckets(CC);
+  if (nb == 0 || n >= (1LL << 32)) return TMB_ERR_TOO_LARGE;
   if (nb < 2)  // everything fits one shared-memory histogram: the direct kernels are the right tool
     return tmb_confmat_update(preds, preds_dtype, target, target_dtype, n, num_classes, has_ignore, ignore_index,
                               confmat, status, 0, stream);
@@ -332,6 +488,29 @@ extern "C" int tmb_confmat_update_ws(const void* preds, int preds_dtype, const v
   P.confmat = (u64*)confmat;
   P.status = status;
   cudaStream_t st = (cudaStream_t)stream;
+  if (part_mode()) {
+    u32 lg = 0;
+    while ((1u << lg) < (u32)nb) ++lg;
+    P.lognb = lg;
+    P.cap = ((u32)kFifoEntries / (u32)nb) & ~7u;
+    const size_t smem = (size_t)kMaxBuckets * 8 + (size_t)kFifoEntries * 2 + 16;
+    TMB_DISPATCH_INT(preds_dtype, PT, {
+      TMB_DISPATCH_INT(target_dtype, TT, {
+        auto launch = [&](auto kern) -> int {
+          TMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          kern<<<G, kFifoThreads, smem, st>>>(P);
+          return TMB_OK;
+        };
+        const int rc = P.has_ignore ? launch(confmat_fifo_partition_kernel<PT, TT, true>)
+                                    : launch(confmat_fifo_partition_kernel<PT, TT, false>);
+        if (rc != TMB_OK) return rc;
+        confmat_bucket_hist_kernel<<<dim3((unsigned)nb, kHistSplit), kHistThreads, 0, st>>>(P);
+        TMB_CUDA_CHECK(cudaGetLastError());
+        return TMB_OK;
+      })
+    })
+    return TMB_ERR_ARG;
+  }
   // always G CTAs: the ones without a tile still publish their (zero) fill counts
   TMB_DISPATCH_INT(preds_dtype, PT, {
     TMB_DISPATCH_INT(target_dtype, TT, {
