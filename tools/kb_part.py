@@ -8,7 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from torchmetrics_b200 import _native as N  # noqa: E402
 from tools.kbench import timeit, report, DEV  # noqa: E402
 
-tag = "PARTA=" + os.environ.get("TMB_PARTA", "1")
+tag = ""
 for C, n in [(1000, 1 << 24), (1000, 1 << 26), (1000, 1 << 23), (300, 1 << 24), (2000, 1 << 24), (1000, (1 << 24) + 12345)]:
     g = torch.Generator(device=DEV).manual_seed(1)
     p = torch.randint(0, C, (n,), device=DEV, generator=g)
