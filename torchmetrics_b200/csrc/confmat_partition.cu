@@ -70,6 +70,7 @@ struct Fifos {
   u32* hot_key;          // [kHotSlots]
   u32* hot_cnt;
   u32 nb, lognb, nbmask, cap, C32;
+  u32 cnt_addr, fifo_addr;  // 32-bit shared-window addresses of cnt / fifo
   int bad;
   u64 pol_keep;
 
@@ -79,6 +80,8 @@ struct Fifos {
     nbmask = P.nb - 1;
     cap = P.cap;
     C32 = (u32)P.C;
+    cnt_addr = (u32)__cvta_generic_to_shared(cnt);
+    fifo_addr = (u32)__cvta_generic_to_shared(fifo);
     bad = 0;
     pol_keep = l2_policy_evict_last();
     for (u32 b = tid; b < nb; b += nthreads) {
@@ -122,7 +125,9 @@ struct Fifos {
   }
 
   // K samples of one thread: keys first, then the K atomics back to back, then the K stores, so the atomics'
-  // latencies overlap; everything rare is collected in a mask and handled after the batch.
+  // latencies overlap; everything rare is collected in a mask and handled after the batch.  The common path is
+  // straight-line predicated code on 32-bit shared-memory addresses (the compiler's version of the same loop
+  // branches around every atomic and store and re-derives the shared window each time).
   template <int K, typename PT, typename TT, bool HAS_IGNORE>
   __device__ __forceinline__ void push(const PartParams& P, const PT (&pv)[K], const TT (&tv)[K]) {
     u32 key[K], pos[K];
@@ -132,7 +137,12 @@ struct Fifos {
       const long long tl = as_i64(tv[j]), pl = as_i64(pv[j]);
       bool counted = true;
       if constexpr (HAS_IGNORE) counted = tl != P.ignore;
-      const bool oob = ((u64)tl >= (u64)P.C) | ((u64)pl >= (u64)P.C);
+      // outside [0, C) <=> a high word is set or a low word is >= C (C <= 2048 here)
+      const u32 lo_max = max((u32)tl, (u32)pl);
+      u32 hi = 0;
+      if constexpr (sizeof(TT) == 8) hi |= (u32)((u64)tl >> 32);
+      if constexpr (sizeof(PT) == 8) hi |= (u32)((u64)pl >> 32);
+      const bool oob = (lo_max >= C32) | (hi != 0);
       key[j] = (u32)tl * C32 + (u32)pl;
       ok |= (u32)(counted & !oob) << j;
       rare |= (u32)(counted & oob) << j;
@@ -140,14 +150,24 @@ struct Fifos {
 #pragma unroll
     for (int j = 0; j < K; ++j) {
       pos[j] = 0xffffffffu;
-      if ((ok >> j) & 1u) pos[j] = atomicAdd(&cnt[(key[j] >> 4) & nbmask], 1u);
+      const u32 addr = cnt_addr + (((key[j] >> 4) & nbmask) << 2);
+      asm volatile(
+          "{\n.reg .pred q;\nsetp.ne.u32 q, %2, 0;\n@q atom.shared.add.u32 %0, [%1], 1;\n}"
+          : "+r"(pos[j])
+          : "r"(addr), "r"((ok >> j) & 1u)
+          : "memory");
     }
 #pragma unroll
     for (int j = 0; j < K; ++j) {
       const u32 group = key[j] >> 4;
       const u32 b = group & nbmask;
-      if (pos[j] < cap) fifo[b * cap + pos[j]] = (unsigned short)(((group >> lognb) << 4) | (key[j] & 15u));
-      else rare |= ((ok >> j) & 1u) << (K + j);
+      const u32 lbin = ((group >> lognb) << 4) | (key[j] & 15u);
+      const u32 addr = fifo_addr + ((b * cap + pos[j]) << 1);
+      const u32 fits = pos[j] < cap;  // pos is 0xffffffff for a sample that is not counted here
+      asm volatile("{\n.reg .pred q;\nsetp.ne.u32 q, %2, 0;\n@q st.shared.u16 [%0], %1;\n}" ::"r"(addr),
+                   "h"((unsigned short)lbin), "r"(fits)
+                   : "memory");
+      rare |= ((ok >> j) & (fits ^ 1u)) << (K + j);
     }
     if (rare) {
 #pragma unroll
