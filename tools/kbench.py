@@ -129,3 +129,26 @@ def bench_exact():
 
 if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "exact"):
     bench_exact()
+
+
+def bench_binned_multi():
+    thr = torch.linspace(0, 1, 200, device=DEV)
+    for rows, cols in [(1 << 18, 100), (1 << 20, 10), (1 << 22, 4)]:
+        g = torch.Generator(device=DEV).manual_seed(1)
+        preds = torch.rand(rows, cols, device=DEV, generator=g)
+        tl = torch.randint(0, 2, (rows, cols), device=DEV, generator=g)
+        st = torch.zeros(200, cols, 2, 2, dtype=torch.int64, device=DEV)
+        med, best = timeit(lambda: N.binned_curve_update_(st, preds, tl, thr, num_columns=cols, prob_mode=N.PROB_AS_IS),
+                           iters=10)
+        report(f"binned multilabel T=200 rows=2^{rows.bit_length()-1} L={cols} f32+i64", rows * cols * 12, med, best,
+               rows * cols)
+        tc = torch.randint(0, cols, (rows,), device=DEV, generator=g)
+        med, best = timeit(lambda: N.binned_curve_update_(st, preds, tc, thr, num_columns=cols,
+                                                          target_is_class_index=True, prob_mode=N.PROB_AS_IS), iters=10)
+        report(f"binned multiclass T=200 rows=2^{rows.bit_length()-1} C={cols} f32+i64", rows * (cols * 4 + 8), med,
+               best, rows * cols)
+        del preds, tl, tc
+
+
+if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "binned_multi"):
+    bench_binned_multi()
