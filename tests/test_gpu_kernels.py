@@ -332,6 +332,40 @@ def test_binned_large_columns_global_bins():
     assert np.array_equal(_np(state), want)
 
 
+@pytest.mark.parametrize("C,n,T", [(3, 1001, 7), (7, 4099, 200), (10, 50000, 200), (130, 3000, 50), (100, 20011, 200)])
+@pytest.mark.parametrize("uniform", [True, False])
+def test_binned_multicolumn_seeded(C, n, T, uniform):
+    """The shared-memory multi-column kernel + warp-per-column finalize: rows that wrap inside a 4-element vector,
+    ignore_index, evenly spaced and arbitrary sorted thresholds, both target layouts, two updates into one state."""
+    N = _native()
+    g = torch.Generator().manual_seed(C * 1000 + T)
+    thr = torch.linspace(0, 1, T) if uniform else torch.sort(torch.rand(T, generator=g)).values
+    # multiclass: class-index target, scores already in [0, 1]
+    p = torch.rand(n, C, generator=g)
+    p[::17, 0] = thr[min(3, T - 1)]  # scores exactly on a threshold
+    t = torch.randint(0, C, (n,), generator=g)
+    t[::13] = -1
+    state = torch.zeros(T, C, 2, 2, dtype=torch.int64, device=DEV)
+    for _ in range(2):
+        N.binned_curve_update_(state, p.to(DEV), t.to(DEV), thr.to(DEV), num_columns=C, target_is_class_index=True,
+                               ignore_index=-1, prob_mode=N.PROB_CHECK)
+    keep = t != -1
+    want = O.multiclass_precision_recall_curve_update_loop(p.numpy()[keep.numpy()], t.numpy()[keep.numpy()], C,
+                                                           thr.numpy())
+    assert np.array_equal(_np(state), 2 * want)
+    assert N.read_status_words(torch.device(DEV)) == (0, 0)
+    # multilabel: per-element targets, logits -> the all-or-nothing sigmoid pass
+    pl = torch.randn(n, C, generator=g) * 3
+    tl = torch.randint(0, 2, (n, C), generator=g)
+    tl[::11, C // 2] = -1
+    state = torch.zeros(T, C, 2, 2, dtype=torch.int64, device=DEV)
+    N.binned_curve_update_(state, pl.to(DEV), tl.to(DEV), thr.to(DEV), num_columns=C, ignore_index=-1)
+    sp = _np(pl.to(DEV).sigmoid())
+    want = O.multilabel_precision_recall_curve_update(sp, tl.numpy(), tl.numpy() == -1, C, thr.numpy())
+    assert np.array_equal(_np(state), want)
+    assert N.read_status_words(torch.device(DEV)) == (0, 0)
+
+
 # =========================================================================== K2 stat scores
 def _stat(N, preds, target, L, threshold=0.5, ignore_index=None, prob_mode=None):
     out = torch.zeros(4, L, dtype=torch.int64, device=DEV)

@@ -133,7 +133,7 @@ if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "exact"):
 
 def bench_binned_multi():
     thr = torch.linspace(0, 1, 200, device=DEV)
-    for rows, cols in [(1 << 18, 100), (1 << 20, 10), (1 << 22, 4)]:
+    for rows, cols in [(1 << 18, 100), (1 << 20, 100), (1 << 20, 10), (1 << 23, 10), (1 << 22, 4), (1 << 24, 4)]:
         g = torch.Generator(device=DEV).manual_seed(1)
         preds = torch.rand(rows, cols, device=DEV, generator=g)
         tl = torch.randint(0, 2, (rows, cols), device=DEV, generator=g)

@@ -333,7 +333,7 @@ static void (*pick_warphist(int mode, bool has_ignore))(const BinnedParams) {
 constexpr int kMultiThreads = 1024;
 
 template <typename TT, int MODE, bool HAS_IGNORE, bool CLASS_INDEX>
-__global__ void __launch_bounds__(kMultiThreads, 1) binned_multicol_kernel(const BinnedParams P) {
+__global__ void __launch_bounds__(kMultiThreads, 2) binned_multicol_kernel(const BinnedParams P) {
   constexpr bool CHECK = MODE == kModeAsIsCheck;
   constexpr bool SIGMOID = MODE == kModeSigmoid;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -676,12 +676,14 @@ static int launch_binned(BinnedParams P, int prob_mode, cudaStream_t st) {
 
   auto run = [&](bool sigmoid) -> int {
     if (multicol) {
-      size_t room = (size_t)max_optin_smem() - 1024 - multi_fixed;
+      // two CTAs per SM (64 resident warps) when at least four copies of the bins fit in half an SM's shared memory
+      const bool two = multi_fixed + (size_t)nbins * 4 * 4 <= kWarpHistSmemBudget;
+      size_t room = (two ? kWarpHistSmemBudget : (size_t)max_optin_smem() - 1024) - multi_fixed;
       size_t c = room / ((size_t)nbins * 4);
       P.hist_copies = (int)(c > kMultiThreads / 32 ? kMultiThreads / 32 : c);
       const size_t smem = multi_fixed + (size_t)P.hist_copies * nbins * 4;
       long long want = ((total >> 2) + kMultiThreads - 1) / kMultiThreads;
-      long long cap = (long long)sm_count();
+      long long cap = (long long)sm_count() * (two ? 2 : 1);
       int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
       const int mode = sigmoid ? kModeSigmoid : (P.check_range ? kModeAsIsCheck : kModeAsIs);
       auto k = pick_multicol<TT>(mode, P.has_ignore != 0, P.target_is_class_index != 0);
