@@ -205,7 +205,7 @@ def main():
             traffic = json.load(f).get("confmat_partition_plus_hist_bytes_per_update")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "confmat_partition_kernel<int64,int64> + confmat_bucket_hist_kernel (2 launches per update)", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "confmat_partition_tma_kernel<int64,int64> + confmat_bucket_hist_kernel (2 launches per update)", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": BATCH * BYTES_PER_SAMPLE, "kernel_ms": kernel_ms,
                 "frac_of_nominal_8TBps": achieved / 8000.0}
