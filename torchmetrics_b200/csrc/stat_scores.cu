@@ -60,13 +60,20 @@ __device__ __forceinline__ typename CmpType<PT>::type threshold_as(double thr) {
 struct Counts {
   u32 tp, fp, tn, fn;
 };
+// per-thread bookkeeping of the fused validation
+struct Seen {
+  u32 elements;  // elements handed to tally()
+  u32 ignored;   // of which equal to ignore_index
+  u64 preds_or;  // OR of the label preds (integer preds only)
+};
 
 template <typename PT, typename TT, bool SIGMOID>
 __device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typename CmpType<PT>::type thr, Counts& c,
-                                      int& oor, int& vbits) {
+                                      int& oor, Seen& seen) {
   long long t = as_i64(tv);
-  // fused validation: a target that is neither 0, 1 nor the ignore value
-  vbits |= ((u64)t > 1ULL && !(P.has_ignore && t == P.ignore)) ? TMB_STATUS_TARGET_VALUES : 0;
+  // Fused validation costs nothing per element on the common path: a target that is neither 0, 1 nor the ignore
+  // value lands in none of the four counters, so "counted + ignored != elements seen" at the end of the thread
+  // says one was there.
   if constexpr (IsFloatScore<PT>::value) {
     using CT = typename CmpType<PT>::type;
     CT p = to_cmp(pv);
@@ -74,7 +81,10 @@ __device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typenam
     // :657); the binary confusion-matrix _format drops ignored samples first (confusion_matrix.py:133-142)
     const bool ign = P.has_ignore && t == P.ignore;
     if (P.check_range && (P.range_check_ignored || !ign)) oor |= !(p >= (CT)0 && p <= (CT)1);
-    if (ign) return;
+    if (ign) {
+      ++seen.ignored;
+      return;
+    }
     if constexpr (SIGMOID) p = round_to_storage<PT>(sigmoid_ref(p));
     const bool pb = p > thr;
     c.tp += (t == 1) & pb;
@@ -83,8 +93,11 @@ __device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typenam
     c.tn += (t == 0) & !pb;
   } else {
     long long p = as_i64(pv);
-    vbits |= (u64)p > 1ULL ? TMB_STATUS_PREDS_VALUES : 0;
-    if (P.has_ignore && t == P.ignore) return;
+    seen.preds_or |= (u64)p;  // label preds outside {0, 1} leave a bit above bit 0
+    if (P.has_ignore && t == P.ignore) {
+      ++seen.ignored;
+      return;
+    }
     const bool eq = (t == p);
     c.tp += (t == 1) & eq;
     c.fn += (t == 1) & !eq;
@@ -108,7 +121,8 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
   const CT thr = threshold_as<PT>(P.threshold);
   const long long L = P.L;
   u64* acc = reinterpret_cast<u64*>(ws + 1);
-  int oor = 0, vbits = 0;
+  int oor = 0;
+  Seen seen{0, 0, 0};
   Counts c[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) c[j] = Counts{0, 0, 0, 0};
@@ -132,15 +146,20 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
       Vec4<PT> p = load4(preds + 4 * g);
       Vec4<TT> t = load4(target + 4 * g);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[0], oor, vbits);
+      for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[0], oor, seen);
       if (P.check_range && (it & 63) == 63) {
         if (oor) atomicOr(&ws->flag_oor, 1);
-        if (*(volatile int*)&ws->flag_oor) break;
+        if (*(volatile int*)&ws->flag_oor) {
+          ++it;
+          break;
+        }
       }
     }
+    seen.elements = (u32)it * 4;
     if (blockIdx.x == 0 && tid < (n & 3)) {
       long long i = (nvec << 2) + tid;
-      tally<PT, TT, SIGMOID>(preds[i], target[i], P, thr, c[0], oor, vbits);
+      tally<PT, TT, SIGMOID>(preds[i], target[i], P, thr, c[0], oor, seen);
+      seen.elements += 1;
     }
   } else {
     const int r0 = tid / CW;
@@ -155,19 +174,30 @@ __global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const Stat
           Vec4<PT> p = load4(preds + e);
           Vec4<TT> t = load4(target + e);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[j], oor, vbits);
+          for (int j = 0; j < 4; ++j) tally<PT, TT, SIGMOID>(p.v[j], t.v[j], P, thr, c[j], oor, seen);
         } else {
-          tally<PT, TT, SIGMOID>(preds[e], target[e], P, thr, c[0], oor, vbits);
+          tally<PT, TT, SIGMOID>(preds[e], target[e], P, thr, c[0], oor, seen);
         }
         if (P.check_range && (it & 63) == 63) {
           if (oor) atomicOr(&ws->flag_oor, 1);
-          if (*(volatile int*)&ws->flag_oor) break;
+          if (*(volatile int*)&ws->flag_oor) {
+            ++it;
+            break;
+          }
         }
       }
+      seen.elements = (u32)it * V;
     }
   }
   if (P.check_range && oor) atomicOr(&ws->flag_oor, 1);
-  if (vbits && P.status) report_status(P.status, vbits);
+  if (P.status) {
+    u32 counted = seen.ignored;
+#pragma unroll
+    for (int j = 0; j < V; ++j) counted += c[j].tp + c[j].fp + c[j].tn + c[j].fn;
+    const int vbits = (counted != seen.elements ? TMB_STATUS_TARGET_VALUES : 0) |
+                      (seen.preds_or > 1ULL ? TMB_STATUS_PREDS_VALUES : 0);
+    if (vbits) report_status(P.status, vbits);
+  }
 
   // merge: registers -> shared (per CTA) -> global scratch
   if (active) {
