@@ -178,6 +178,24 @@ TMB_API int tmb_exact_curve(const float* preds_dev, const void* target_dev, int 
                             int64_t* counts2_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * K4b  exact AUROC and average precision without materialising the curve.
+ * Replaces: `_binary_clf_curve` (precision_recall_curve.py:28-80) FOLLOWED BY the reductions of
+ *           functional/classification/roc.py:60-78 + utilities/compute.py `_auc_compute_without_check`
+ *           (trapezoid area under (fpr, tpr) with the (0, 0) point prepended) and
+ *           functional/classification/average_precision.py:39-46 (-sum(diff(recall) * precision[:-1]))
+ *           for thresholds=None, max_fpr=None.  Same sort as tmb_exact_curve; the three n-sized outputs and the
+ *           torch passes over them are replaced by two sums over the run ends, exact integer terms added in fp64.
+ * out4_dev: double[4] = { sum_k (FP_k-FP_{k-1})(TP_k+TP_{k-1}),  sum_k (TP_k-TP_{k-1}) TP_k/(TP_k+FP_k),
+ *                         number of positives,  number of distinct scores }
+ *           AUROC = out4[0] / (2 * Npos * Nneg),  AP = out4[1] / Npos   (Nneg = n - Npos); the caller handles
+ *           Npos == 0 / Nneg == 0 the way the reference does (warnings, zeros / nan).
+ * workspace_dev: tmb_exact_curve_workspace_bytes(n) bytes, contents irrelevant.  n < 2^32 - 4096.
+ * ------------------------------------------------------------------------------------------- */
+TMB_API int tmb_exact_auroc_ap(const float* preds_dev, const void* target_dev, int target_dtype, int64_t n,
+                               int64_t pos_label, double* out4_dev, void* workspace_dev, size_t workspace_bytes,
+                               void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * K2  tp / fp / tn / fn per label.
  * Replaces: functional/classification/stat_scores.py:120-131 `_binary_stat_scores_update` and :672-681
  *           `_multilabel_stat_scores_update` (multidim_average="global"), fused with `_format`

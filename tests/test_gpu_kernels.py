@@ -579,3 +579,79 @@ def test_validation_findings_go_to_the_second_status_word():
     assert N.read_status_words(dev) == (0, N.STATUS_TARGET_VALUES)
     N.binned_curve_update_(stc, sl, tl2, thr, num_columns=L)
     assert N.read_status_words(dev) == (0, N.STATUS_TARGET_VALUES)
+
+
+# =========================================================================== K4b fused exact AUROC / AP
+def _auroc_ap_from_curve(N, p, t):
+    """The same two scalars from the materialised curve, in float64 (what the fused kernel must reproduce)."""
+    fps, tps, _ = N.exact_curve(p, t, 1)
+    fps, tps = fps.double().cpu().numpy(), tps.double().cpu().numpy()
+    fp0, tp0 = np.concatenate([[0.0], fps[:-1]]), np.concatenate([[0.0], tps[:-1]])
+    area2 = float(((fps - fp0) * (tps + tp0)).sum())
+    apsum = float(((tps - tp0) * tps / (tps + fps)).sum())
+    return area2, apsum, float(tps[-1]), float(len(tps))
+
+
+@pytest.mark.parametrize("case", ["random", "ties", "constant", "long_runs", "tiny", "ragged", "nan_inf", "two_values"])
+def test_exact_auroc_ap_fused_matches_curve(case):
+    N = _native()
+    g = torch.Generator().manual_seed(11)
+    if case == "random":
+        n = 200_003
+        p = torch.rand(n, generator=g)
+    elif case == "ties":
+        n = 100_000
+        p = torch.randint(0, 50, (n,), generator=g).float() / 50
+    elif case == "constant":
+        n = 30_000
+        p = torch.full((n,), 0.25)
+    elif case == "long_runs":  # runs of equal scores far longer than a 4096-key tile, plus singletons
+        n = 150_000
+        p = torch.cat([torch.full((60_000,), 0.9), torch.rand(10_000, generator=g) * 0.5,
+                       torch.full((70_000,), 0.1), torch.rand(10_000, generator=g) * 0.05])
+    elif case == "tiny":
+        n = 3
+        p = torch.tensor([0.2, 0.9, 0.2])
+    elif case == "ragged":
+        n = 4096 * 3 + 1
+        p = torch.rand(n, generator=g).round(decimals=3)
+    elif case == "nan_inf":
+        n = 10_000
+        p = torch.randn(n, generator=g)
+        p[::97] = float("nan")
+        p[5::101] = float("inf")
+        p[7::103] = float("-inf")
+    else:
+        n = 50_000
+        p = (torch.rand(n, generator=g) < 0.5).float()
+    t = (torch.rand(n, generator=g) < 0.4).long()
+    if case == "tiny":
+        t = torch.tensor([0, 1, 1])
+    p, t = p.to(DEV), t.to(DEV)
+    got = N.exact_auroc_ap(p, t, 1)
+    want = _auroc_ap_from_curve(N, p, t)
+    assert got[2] == want[2] and got[3] == want[3]
+    assert got[0] == want[0], (got[0], want[0])  # integer-valued terms below 2^53: exact in float64
+    assert abs(got[1] - want[1]) <= 1e-9 * max(1.0, abs(want[1]))
+    again = N.exact_auroc_ap(p, t, 1)
+    assert again == got  # fixed summation order: bit-reproducible
+
+
+def test_exact_auroc_ap_functional_agrees_with_curve_path_and_sklearn():
+    import torchmetrics_b200.functional as F
+    from sklearn.metrics import average_precision_score, roc_auc_score
+
+    g = torch.Generator().manual_seed(5)
+    n = 300_000
+    p = torch.rand(n, generator=g).round(decimals=4)
+    t = (torch.rand(n, generator=g) < 0.2 + 0.5 * p).long()
+    au = float(F.binary_auroc(p.to(DEV), t.to(DEV), thresholds=None))
+    ap = float(F.binary_average_precision(p.to(DEV), t.to(DEV), thresholds=None))
+    assert abs(au - roc_auc_score(t.numpy(), p.numpy())) < 1e-6
+    assert abs(ap - average_precision_score(t.numpy(), p.numpy())) < 1e-6
+    # the curve path (what runs for max_fpr / degenerate targets) gives the same numbers
+    fpr, tpr, _ = F.binary_roc(p.to(DEV), t.to(DEV), thresholds=None)
+    assert abs(au - float(torch.trapz(tpr.double(), fpr.double()))) < 1e-6
+    # degenerate targets fall back to the reference behaviour
+    with pytest.warns(UserWarning):
+        assert float(F.binary_auroc(p.to(DEV), torch.zeros(n, dtype=torch.long, device=DEV), thresholds=None)) == 0.0

@@ -32,5 +32,10 @@ elif what == "stat":
     out = torch.zeros(4, L, dtype=torch.int64, device=DEV)
     for _ in range(4):
         N.stat_scores_update_(out, p, t, L, 0.5, None, N.PROB_AS_IS)
+elif what == "exact":
+    preds = torch.rand(n, device=DEV, generator=g)
+    target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
+    for _ in range(2):
+        N.exact_curve(preds, target, 1)
 torch.cuda.synchronize()
 print("done", what, n)

@@ -63,6 +63,8 @@ _SIGNATURES = {
     "tmb_exact_curve_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_exact_curve": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_void_p,
                                    _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
+    "tmb_exact_auroc_ap": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p,
+                                      _c.c_void_p, _c.c_size_t, _c.c_void_p]),
     "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                           _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,
@@ -347,6 +349,25 @@ def exact_curve(preds: Tensor, target: Tensor, pos_label: int = 1):
     _check(rc, "tmb_exact_curve")
     d = int(counts[1].item())  # the reference syncs at the same point (torch.where)
     return fps[:d], tps[:d], thr[:d]
+
+
+def exact_auroc_ap(preds: Tensor, target: Tensor, pos_label: int = 1) -> Tuple[float, float, float, float]:
+    """(sum_k dFP_k (TP_k + TP_{k-1}),  sum_k dTP_k TP_k / (TP_k + FP_k),  positives,  distinct scores) of the exact
+    curve, reduced on the device (K4b): the curve itself is never written.  One 32-byte read back."""
+    dev = require_cuda(preds, target)
+    preds = _aligned(preds.detach().reshape(-1).to(torch.float32))
+    target = as_kernel_labels(target.reshape(-1))
+    n = preds.numel()
+    assert target.numel() == n
+    lib = load()
+    out4 = torch.empty(4, dtype=torch.float64, device=dev)
+    ws = torch.empty(lib.tmb_exact_curve_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.tmb_exact_auroc_ap(preds.data_ptr(), target.data_ptr(), dtype_code(target), n, int(pos_label),
+                                    out4.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _check(rc, "tmb_exact_auroc_ap")
+    a, b, c, d = out4.tolist()
+    return a, b, c, d
 
 
 def binned_curve_update_static_(confmat: Tensor, preds: Tensor, target: Tensor, thresholds: Tensor,

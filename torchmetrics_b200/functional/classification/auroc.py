@@ -7,6 +7,7 @@ from torch import Tensor, tensor
 from typing_extensions import Literal
 
 P = import_module("torchmetrics_b200.functional.classification.precision_recall_curve")
+from torchmetrics_b200.functional.classification._exact import fused_binary_auroc
 from torchmetrics_b200.functional.classification.roc import (
     _binary_roc_compute,
     _multiclass_roc_compute,
@@ -52,7 +53,12 @@ def _binary_auroc_arg_validation(max_fpr: Optional[float] = None,
 
 def _binary_auroc_compute(state: Union[Tensor, Tuple[Tensor, Tensor]], thresholds: Optional[Tensor],
                           max_fpr: Optional[float] = None, pos_label: int = 1) -> Tensor:
-    """Full or partial (McClish-corrected) AUROC (auroc.py:82-106)."""
+    """Full or partial (McClish-corrected) AUROC (auroc.py:82-106).  Exact mode without `max_fpr` never builds the
+    curve: the trapezoid sum is reduced next to the sort (K4b)."""
+    if thresholds is None and (max_fpr is None or max_fpr == 1):
+        fused = fused_binary_auroc(state, pos_label)
+        if fused is not None:
+            return fused
     fpr, tpr, _ = _binary_roc_compute(state, thresholds, pos_label)
     if max_fpr is None or max_fpr == 1 or fpr.sum() == 0 or tpr.sum() == 0:
         return _auc_compute_without_check(fpr, tpr, 1.0)

@@ -7,6 +7,7 @@ from torch import Tensor
 from typing_extensions import Literal
 
 P = import_module("torchmetrics_b200.functional.classification.precision_recall_curve")
+from torchmetrics_b200.functional.classification._exact import fused_binary_average_precision
 from torchmetrics_b200.utilities.compute import _safe_divide
 from torchmetrics_b200.utilities.data import _bincount
 from torchmetrics_b200.utilities.enums import ClassificationTask
@@ -38,6 +39,10 @@ def _reduce_average_precision(precision: Union[Tensor, List[Tensor]], recall: Un
 
 
 def _binary_average_precision_compute(state: Union[Tensor, Tuple[Tensor, Tensor]], thresholds: Optional[Tensor]) -> Tensor:
+    if thresholds is None:
+        fused = fused_binary_average_precision(state)  # exact mode: reduced next to the sort (K4b)
+        if fused is not None:
+            return fused
     precision, recall, _ = P._binary_precision_recall_curve_compute(state, thresholds)
     return -torch.sum((recall[1:] - recall[:-1]) * precision[:-1])
 
