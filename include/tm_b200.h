@@ -196,6 +196,25 @@ TMB_API int tmb_exact_auroc_ap(const float* preds_dev, const void* target_dev, i
                                void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * K1c  per-class tp / fp / tn / fn of multiclass label pairs, without the C x C matrix.
+ * Replaces: functional/classification/stat_scores.py:395-419, the non-one-hot branch of
+ *           `_multiclass_stat_scores_update` (multidim_average="global", top_k=1, average != "micro"):
+ *           bincount(target * C + preds, minlength=C*C).reshape(C, C) followed by diag / sum(0) / sum(1) / sum().
+ *           The four vectors are three histograms of length C (tp, column sums, row sums) and a count.
+ * preds_dev/target_dev: n integer labels each.  A target equal to ignore_index (when has_ignore) drops the sample,
+ * as the reference's `_format` + update do.  Labels outside [0, C) follow the reference's key arithmetic: the pair
+ * is counted in cell (key / C, key % C) when key = target*C + pred is inside [0, C*C), otherwise
+ * TMB_STATUS_LABEL_RANGE is raised; TMB_STATUS_TARGET_VALUES / _PREDS_VALUES are reported as for K1.
+ * out_dev: int64[4 * C] laid out [tp | fp | tn | fn], accumulated.
+ * workspace_dev: tmb_class_stats_workspace_bytes(C) bytes, zero on first use, left zero.  n < 2^32.
+ * ------------------------------------------------------------------------------------------- */
+TMB_API size_t tmb_class_stats_workspace_bytes(int64_t num_classes);
+TMB_API int tmb_class_stats_update(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
+                                   int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index,
+                                   int64_t* out_dev, void* workspace_dev, size_t workspace_bytes,
+                                   int32_t* status_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * K2  tp / fp / tn / fn per label.
  * Replaces: functional/classification/stat_scores.py:120-131 `_binary_stat_scores_update` and :672-681
  *           `_multilabel_stat_scores_update` (multidim_average="global"), fused with `_format`

@@ -581,6 +581,49 @@ def test_validation_findings_go_to_the_second_status_word():
     assert N.read_status_words(dev) == (0, N.STATUS_TARGET_VALUES)
 
 
+# =========================================================================== K1c per-class stats without the matrix
+@pytest.mark.parametrize("C,n", [(2, 1), (5, 1000), (10, 4097), (1000, 100_003), (3000, 50_000), (20_000, 70_001)])
+@pytest.mark.parametrize("ignore_index", [None, -1, 1])
+@pytest.mark.parametrize("dt", [torch.int64, torch.int32])
+def test_class_stats_matches_confusion_matrix_reduction(C, n, ignore_index, dt):
+    """tp/fp/tn/fn from three length-C histograms == the reference's reduction of the C x C matrix
+    (stat_scores.py:395-419), including ignore_index inside and outside [0, C) and two accumulating updates."""
+    N = _native()
+    g = torch.Generator().manual_seed(C + n)
+    t = torch.randint(0, C, (n,), generator=g)
+    p = torch.where(torch.rand(n, generator=g) < 0.6, t, torch.randint(0, C, (n,), generator=g))
+    if ignore_index is not None:
+        t[::7] = ignore_index
+    out = torch.zeros(4, C, dtype=torch.int64, device=DEV)
+    for _ in range(2):
+        N.class_stats_update_(out, p.to(dt).to(DEV), t.to(dt).to(DEV), C, ignore_index)
+    keep = (t != ignore_index) if ignore_index is not None else torch.ones(n, dtype=torch.bool)
+    tp, fp, tn, fn = O.multiclass_stat_scores_update(p[keep].numpy(), t[keep].numpy(), C, average="macro")
+    want = 2 * np.stack([tp, fp, tn, fn])
+    assert np.array_equal(_np(out), want)
+    assert N.read_status_words(torch.device(DEV)) == (0, 0)
+
+
+def test_class_stats_out_of_range_labels_follow_the_key_arithmetic():
+    N = _native()
+    dev = torch.device(DEV)
+    C = 7
+    t = torch.tensor([0, 1, 2, 6, 3, 3])
+    p = torch.tensor([1, 1, 9, 0, -2, 3])  # (2, 9) aliases to cell (3, 2); (3, -2) to cell (2, 6)
+    out = torch.zeros(4, C, dtype=torch.int64, device=DEV)
+    N.class_stats_update_(out, p.to(DEV), t.to(DEV), C)
+    cm = np.bincount(t.numpy() * C + p.numpy(), minlength=C * C).reshape(C, C)
+    tp = np.diag(cm)
+    fp, fn = cm.sum(0) - tp, cm.sum(1) - tp
+    want = np.stack([tp, fp, cm.sum() - tp - fp - fn, fn])
+    assert np.array_equal(_np(out), want)
+    assert N.read_status_words(dev) == (0, N.STATUS_PREDS_VALUES)
+    # a key outside the matrix is what makes the reference's reshape fail: flagged, not counted
+    N.class_stats_update_(out, torch.tensor([0, 50], device=DEV), torch.tensor([0, 6], device=DEV), C)
+    assert N.read_status_words(dev) == (N.STATUS_LABEL_RANGE, N.STATUS_PREDS_VALUES)
+    assert int(out.sum()) == int(want.sum()) + C  # one more counted sample adds C to tp+fp+tn+fn
+
+
 # =========================================================================== K4b fused exact AUROC / AP
 def _auroc_ap_from_curve(N, p, t):
     """The same two scalars from the materialised curve, in float64 (what the fused kernel must reproduce)."""

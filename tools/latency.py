@@ -1,0 +1,49 @@
+"""Per-call latency of typical small-batch updates (host wall clock, 300 calls, sync at the end)."""
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torchmetrics_b200 as tm  # noqa: E402
+
+DEV = "cuda:0"
+g = torch.Generator(device=DEV).manual_seed(0)
+
+
+def bench(name, fn, reps=300):
+    for _ in range(20):
+        fn()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    torch.cuda.synchronize()
+    print(f"{name:70s} {(time.perf_counter() - t0) / reps * 1e6:8.1f} us/call", flush=True)
+
+
+B, C = 256, 1000
+logits = torch.randn(B, C, device=DEV, generator=g)
+labels = torch.randint(0, C, (B,), device=DEV, generator=g)
+pl = logits.argmax(1)
+for va in (True, False):
+    m = tm.classification.MulticlassAccuracy(num_classes=C, validate_args=va).to(DEV)
+    bench(f"MulticlassAccuracy(C=1000).update(logits[256,1000]) validate={va}", lambda: m.update(logits, labels))
+    m = tm.classification.MulticlassAccuracy(num_classes=C, validate_args=va).to(DEV)
+    bench(f"MulticlassAccuracy(C=1000).update(labels[256]) validate={va}", lambda: m.update(pl, labels))
+    m = tm.MulticlassConfusionMatrix(num_classes=100, validate_args=va).to(DEV)
+    l100 = labels % 100
+    bench(f"MulticlassConfusionMatrix(C=100).update(labels[256]) validate={va}", lambda: m.update(l100, l100))
+    p = torch.rand(4096, device=DEV, generator=g)
+    t = (torch.rand(4096, device=DEV, generator=g) < 0.5).long()
+    m = tm.classification.BinaryAUROC(thresholds=200, validate_args=va).to(DEV)
+    bench(f"BinaryAUROC(thresholds=200).update(p[4096]) validate={va}", lambda: m.update(p, t))
+    m = tm.classification.BinaryF1Score(validate_args=va).to(DEV)
+    bench(f"BinaryF1Score.update(p[4096]) validate={va}", lambda: m.update(p, t))
+    coll = tm.MetricCollection([tm.classification.MulticlassAccuracy(num_classes=C, validate_args=va),
+                                tm.classification.MulticlassPrecision(num_classes=C, validate_args=va),
+                                tm.classification.MulticlassRecall(num_classes=C, validate_args=va),
+                                tm.classification.MulticlassF1Score(num_classes=C, validate_args=va)]).to(DEV)
+    bench(f"MetricCollection[Acc,P,R,F1](C=1000).update(logits[256,1000]) validate={va}", lambda: coll.update(logits, labels))
+    bench(f"MetricCollection[Acc,P,R,F1](C=1000).forward(logits[256,1000]) validate={va}", lambda: coll(logits, labels))

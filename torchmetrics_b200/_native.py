@@ -53,6 +53,9 @@ _SIGNATURES = {
                                        _c.c_void_p]),
     "tmb_match_count_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int,
                                           _c.c_int64, _c.c_void_p, _c.c_void_p]),
+    "tmb_class_stats_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
+    "tmb_class_stats_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_int,
+                                          _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p, _c.c_void_p]),
     "tmb_binned_curve_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int64]),
     "tmb_binned_curve_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                            _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int64, _c.c_int,
@@ -280,6 +283,24 @@ def match_count_update_(out2: Tensor, preds: Tensor, target: Tensor, ignore_inde
                                            0 if ignore_index is None else int(ignore_index), out2.data_ptr(),
                                            _stream_ptr(dev))
     _check(rc, "tmb_match_count_update")
+
+
+def class_stats_update_(out: Tensor, preds: Tensor, target: Tensor, num_classes: int,
+                        ignore_index: Optional[int] = None) -> None:
+    """out (4, C) int64 [tp|fp|tn|fn] += per-class statistics of multiclass label tensors (K1c), no C x C matrix."""
+    dev = require_cuda(out, preds, target)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == 4 * num_classes
+    preds, target = as_kernel_labels(preds.reshape(-1)), as_kernel_labels(target.reshape(-1))
+    assert preds.numel() == target.numel()
+    lib = load()
+    sc = scratch(dev)
+    ws = sc.workspace("class_stats", lib.tmb_class_stats_workspace_bytes(num_classes), dev)
+    with torch.cuda.device(dev):
+        rc = lib.tmb_class_stats_update(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                        preds.numel(), num_classes, ignore_index is not None,
+                                        0 if ignore_index is None else int(ignore_index), out.data_ptr(),
+                                        ws.data_ptr(), ws.numel(), sc.status.data_ptr(), _stream_ptr(dev))
+    _check(rc, "tmb_class_stats_update")
 
 
 def binned_curve_update_(confmat: Tensor, preds: Tensor, target: Tensor, thresholds: Tensor, num_columns: int = 1,

@@ -1,0 +1,188 @@
+// K1c — per-class tp / fp / tn / fn of multiclass label pairs without the C x C matrix (contract:
+// tmb_class_stats_update in include/tm_b200.h).
+//
+// The reference derives them from a full confusion matrix (functional/classification/stat_scores.py:395-419:
+// bincount(target * C + preds, minlength=C*C).reshape(C, C), then diag / column sums / row sums) — C*C counters
+// zeroed, filled and reduced per update (8 MB at C = 1000) to produce 4*C numbers.  The same numbers are three
+// histograms of length C:
+//     tp[c] = #(target == c and pred == c)      colsum[c] = #(pred == c)      rowsum[c] = #(target == c)
+//     fp = colsum - tp,   fn = rowsum - tp,   tn = counted - tp - fp - fn
+// Labels outside [0, C) follow the reference's arithmetic exactly: a pair whose key target*C + pred still lands in
+// [0, C*C) is counted in cell (key / C, key % C); any other key raises the label-range status bit.
+#include "common.cuh"
+
+namespace tmb {
+
+constexpr int kClassThreads = 512;
+constexpr size_t kClassSmemBudget = 48 * 1024;  // bins per CTA: 3 * C u32 per copy
+
+struct ClassStatsWs {
+  int ticket;
+  int pad;
+  u64 total;  // counted samples of the update in flight
+  // followed by u64 hist[3 * C]: tp | colsum | rowsum
+};
+
+struct ClassParams {
+  const void* preds;
+  const void* target;
+  long long n;
+  long long C;
+  long long CC;
+  int has_ignore;
+  long long ignore;
+  int copies;  // shared-memory copies of the bins per CTA (0: straight to the global scratch)
+  u64* out;    // [4][C] tp | fp | tn | fn, accumulated
+  ClassStatsWs* ws;
+  int* status;
+};
+
+template <typename PT, typename TT, bool HAS_IGNORE, bool SMEM>
+__global__ void __launch_bounds__(kClassThreads) class_stats_kernel(const ClassParams P) {
+  extern __shared__ u32 s_bins[];  // [copies][3][C]
+  __shared__ int s_last;
+  __shared__ u32 s_valid;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const u32 C = (u32)P.C;
+  u64* const hist = reinterpret_cast<u64*>(P.ws + 1);
+  if constexpr (SMEM)
+    for (u32 i = tid; i < (u32)P.copies * 3u * C; i += kClassThreads) s_bins[i] = 0;
+  if (tid == 0) s_valid = 0;
+  __syncthreads();
+  u32* const my = SMEM ? s_bins + (u32)(warp % P.copies) * 3u * C : nullptr;
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  u32 valid = 0;
+  int bad = 0;
+
+  auto count = [&](PT pv, TT tv) {
+    const long long tl = as_i64(tv), pl = as_i64(pv);
+    if constexpr (HAS_IGNORE)
+      if (tl == P.ignore) return;
+    u32 r = (u32)tl, c = (u32)pl;
+    if (((u64)tl >= (u64)P.C) | ((u64)pl >= (u64)P.C)) {  // rare: the reference still counts a key that aliases
+      const long long k = tl * P.C + pl;
+      bad |= ((u64)tl >= (u64)P.C ? TMB_STATUS_TARGET_VALUES : 0) | ((u64)pl >= (u64)P.C ? TMB_STATUS_PREDS_VALUES : 0);
+      if ((u64)k >= (u64)P.CC) {
+        bad |= TMB_STATUS_LABEL_RANGE;
+        return;
+      }
+      r = (u32)(k / P.C);
+      c = (u32)(k - (long long)r * P.C);
+    }
+    ++valid;
+    if constexpr (SMEM) {
+      atomicAdd(my + C + c, 1u);
+      atomicAdd(my + 2 * C + r, 1u);
+      if (r == c) atomicAdd(my + c, 1u);
+    } else {
+      atomicAdd(hist + C + c, 1ULL);
+      atomicAdd(hist + 2 * C + r, 1ULL);
+      if (r == c) atomicAdd(hist + c, 1ULL);
+    }
+  };
+
+  const long long nvec = P.n >> 2;
+  const long long stride = (long long)gridDim.x * kClassThreads;
+  for (long long g = (long long)blockIdx.x * kClassThreads + tid; g < nvec; g += stride) {
+    const Vec4<PT> p = load4(preds + 4 * g);
+    const Vec4<TT> t = load4(target + 4 * g);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) count(p.v[j], t.v[j]);
+  }
+  if (blockIdx.x == 0 && tid < (int)(P.n & 3)) {
+    const long long i = (nvec << 2) + tid;
+    count(preds[i], target[i]);
+  }
+  if (bad) report_status(P.status, bad);
+  valid = __reduce_add_sync(0xffffffffu, valid);
+  if ((tid & 31) == 0 && valid) atomicAdd(&s_valid, valid);
+  __syncthreads();
+  if constexpr (SMEM) {
+    for (u32 b = tid; b < 3u * C; b += kClassThreads) {
+      u64 v = 0;
+      for (int w = 0; w < P.copies; ++w) v += s_bins[(u32)w * 3u * C + b];
+      if (v) atomicAdd(hist + b, v);
+    }
+  }
+  if (tid == 0 && s_valid) atomicAdd(&P.ws->total, (u64)s_valid);
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(&P.ws->ticket, 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  // last CTA: histograms -> tp / fp / tn / fn, added to the caller's accumulator; scratch left zero
+  __threadfence();
+  const u64 total = __ldcg(&P.ws->total);
+  for (u32 c = tid; c < C; c += kClassThreads) {
+    const u64 tp = __ldcg(hist + c), col = __ldcg(hist + C + c), row = __ldcg(hist + 2 * C + c);
+    hist[c] = 0;
+    hist[C + c] = 0;
+    hist[2 * C + c] = 0;
+    const u64 fp = col - tp, fn = row - tp;
+    P.out[c] += tp;
+    P.out[C + c] += fp;
+    P.out[2 * (u64)C + c] += total - tp - fp - fn;
+    P.out[3 * (u64)C + c] += fn;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    P.ws->total = 0;
+    P.ws->ticket = 0;
+  }
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" size_t tmb_class_stats_workspace_bytes(int64_t num_classes) {
+  if (num_classes < 1) return 0;
+  return sizeof(ClassStatsWs) + (size_t)num_classes * 3 * sizeof(u64);
+}
+
+extern "C" int tmb_class_stats_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                      int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index,
+                                      int64_t* out, void* workspace, size_t workspace_bytes, int32_t* status,
+                                      void* stream) {
+  if (n < 0 || num_classes < 1 || num_classes > (1LL << 31) - 1 || !out || !workspace || !status) return TMB_ERR_ARG;
+  if (workspace_bytes < tmb_class_stats_workspace_bytes(num_classes)) return TMB_ERR_ARG;
+  if (n == 0) return TMB_OK;
+  if (!preds || !target) return TMB_ERR_ARG;
+  if (n >= (1LL << 32)) return TMB_ERR_TOO_LARGE;  // u32 per-CTA counters
+  if (!aligned32(preds) || !aligned32(target) || !aligned32(workspace)) return TMB_ERR_ALIGN;
+  ClassParams P{};
+  P.preds = preds;
+  P.target = target;
+  P.n = n;
+  P.C = num_classes;
+  P.CC = (long long)num_classes * num_classes;
+  P.has_ignore = has_ignore ? 1 : 0;
+  P.ignore = ignore_index;
+  P.out = (u64*)out;
+  P.ws = (ClassStatsWs*)workspace;
+  P.status = status;
+  const size_t per_copy = (size_t)num_classes * 3 * 4;
+  size_t copies = per_copy <= kClassSmemBudget ? kClassSmemBudget / per_copy : 0;
+  if (copies > kClassThreads / 32) copies = kClassThreads / 32;
+  P.copies = (int)copies;
+  const size_t smem = copies * per_copy;
+  long long want = ((n >> 2) + kClassThreads - 1) / kClassThreads;
+  const long long cap = (long long)sm_count() * 4;
+  const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  TMB_DISPATCH_INT(preds_dtype, PT, {
+    TMB_DISPATCH_INT(target_dtype, TT, {
+      if (copies) {
+        if (P.has_ignore) class_stats_kernel<PT, TT, true, true><<<grid, kClassThreads, smem, st>>>(P);
+        else class_stats_kernel<PT, TT, false, true><<<grid, kClassThreads, smem, st>>>(P);
+      } else {
+        if (P.has_ignore) class_stats_kernel<PT, TT, true, false><<<grid, kClassThreads, 0, st>>>(P);
+        else class_stats_kernel<PT, TT, false, false><<<grid, kClassThreads, 0, st>>>(P);
+      }
+      TMB_CUDA_CHECK(cudaGetLastError());
+      return TMB_OK;
+    })
+  })
+  return TMB_ERR_ARG;
+}

@@ -155,13 +155,11 @@ def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: i
         fn = fp.clone()
         tn = num_classes * n_valid - (fp + fn + tp)
         return tp, fp, tn, fn
-    cm = torch.zeros(num_classes, num_classes, dtype=torch.int64, device=dev)
-    _native.confmat_update_(cm, preds, target, num_classes, ignore_index)
-    tp = cm.diag()
-    fp = cm.sum(0) - tp
-    fn = cm.sum(1) - tp
-    tn = cm.sum() - (fp + fn + tp)
-    return tp, fp, tn, fn
+    # the reference fills a C x C confusion matrix and reduces it (:395-419); the four vectors only need three
+    # length-C histograms (K1c), so nothing of size C*C is allocated, zeroed or summed
+    stats = torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
+    _native.class_stats_update_(stats, preds, target, num_classes, ignore_index)
+    return stats[0], stats[1], stats[2], stats[3]
 
 
 def _multiclass_stat_scores_onehot(preds: Tensor, target: Tensor, num_classes: int, top_k: int,
