@@ -152,3 +152,18 @@ def bench_binned_multi():
 
 if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "binned_multi"):
     bench_binned_multi()
+
+
+def bench_class_stats():
+    for C, n in [(1000, 1 << 24), (1000, 1 << 26), (10, 1 << 24), (100, 1 << 24), (20000, 1 << 24)]:
+        g = torch.Generator(device=DEV).manual_seed(1)
+        t = torch.randint(0, C, (n,), device=DEV, generator=g)
+        p = torch.where(torch.rand(n, device=DEV, generator=g) < 0.7, t, torch.randint(0, C, (n,), device=DEV, generator=g))
+        out = torch.zeros(4, C, dtype=torch.int64, device=DEV)
+        med, best = timeit(lambda: N.class_stats_update_(out, p, t, C))
+        report(f"class_stats C={C} n=2^{n.bit_length()-1} i64 (70% correct)", n * 16, med, best, n)
+        del p, t
+
+
+if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "class_stats"):
+    bench_class_stats()

@@ -403,6 +403,13 @@ class Metric(Module, ABC):
     def __setattr__(self, name: str, value: Any) -> None:
         if name in _CONSTANTS:
             raise RuntimeError(f"Can't change const `{name}`.")
+        # Metric states and bookkeeping flags are plain attributes that are rebound several times per update /
+        # forward; nn.Module.__setattr__ walks its parameter / buffer / module tables on every one of them.  A name
+        # that already lives directly in __dict__ is none of those, so a non-Parameter, non-Module value can go
+        # straight in.
+        if name in self.__dict__ and not isinstance(value, (torch.nn.Parameter, torch.nn.Module)):
+            object.__setattr__(self, name, value)
+            return
         super().__setattr__(name, value)
 
     # ------------------------------------------------------------------ device / dtype
