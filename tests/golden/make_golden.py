@@ -439,6 +439,77 @@ def make_doctests():
     b.save()
 
 
+# ------------------------------------------------------------------ consumers of the same update kernels
+def make_derived():
+    """specificity / hamming distance (stat-scores state) and jaccard / cohen kappa / matthews corrcoef (confusion-matrix
+    state): reference outputs of the public functionals on seeded inputs, every task, averaging and ignore_index."""
+    b = Book("derived_metrics")
+    g = rng(77)
+    n, C, L = 257, 6, 5
+    # binary: probabilities, logits, labels
+    bt = torch.randint(0, 2, (n,), generator=g)
+    binary_inputs = {"probs": torch.rand(n, generator=g), "logits": torch.randn(n, generator=g) * 3,
+                     "labels": torch.randint(0, 2, (n,), generator=g)}
+    for kind, bp in binary_inputs.items():
+        for ii in (None, -1):
+            t = bt.clone()
+            if ii is not None:
+                t[::9] = ii
+            out = {
+                "specificity": F.binary_specificity(bp, t, ignore_index=ii),
+                "hamming": F.binary_hamming_distance(bp, t, ignore_index=ii),
+                "jaccard": F.binary_jaccard_index(bp, t, ignore_index=ii),
+                "kappa_none": F.binary_cohen_kappa(bp, t, ignore_index=ii),
+                "kappa_linear": F.binary_cohen_kappa(bp, t, weights="linear", ignore_index=ii),
+                "kappa_quadratic": F.binary_cohen_kappa(bp, t, weights="quadratic", ignore_index=ii),
+                "mcc": F.binary_matthews_corrcoef(bp, t, ignore_index=ii),
+            }
+            b.add({"task": "binary", "kind": kind, "ignore_index": ii}, preds=bp, target=t, **out)
+    # multiclass: labels and (N, C) scores; ignore_index outside and inside the class range
+    mt = torch.randint(0, C, (n,), generator=g)
+    multiclass_inputs = {"labels": torch.where(torch.rand(n, generator=g) < 0.6, mt, torch.randint(0, C, (n,), generator=g)),
+                         "scores": torch.randn(n, C, generator=g)}
+    for kind, mp in multiclass_inputs.items():
+        for ii in (None, -1, 2):
+            t = mt.clone()
+            if ii is not None:
+                t[::7] = ii
+            out = {}
+            for avg in ("micro", "macro", "weighted", "none"):
+                out[f"specificity_{avg}"] = F.multiclass_specificity(mp, t, C, average=avg, ignore_index=ii)
+                out[f"hamming_{avg}"] = F.multiclass_hamming_distance(mp, t, C, average=avg, ignore_index=ii)
+                out[f"jaccard_{avg}"] = F.multiclass_jaccard_index(mp, t, C, average=avg, ignore_index=ii)
+            for w in ("none", "linear", "quadratic"):
+                out[f"kappa_{w}"] = F.multiclass_cohen_kappa(mp, t, C, weights=w, ignore_index=ii)
+            out["mcc"] = F.multiclass_matthews_corrcoef(mp, t, C, ignore_index=ii)
+            b.add({"task": "multiclass", "kind": kind, "num_classes": C, "ignore_index": ii}, preds=mp, target=t, **out)
+    # multilabel
+    lt = torch.randint(0, 2, (n, L), generator=g)
+    multilabel_inputs = {"probs": torch.rand(n, L, generator=g), "logits": torch.randn(n, L, generator=g) * 2}
+    for kind, lp in multilabel_inputs.items():
+        for ii in (None, -1):
+            t = lt.clone()
+            if ii is not None:
+                t[::5, 1] = ii
+            out = {}
+            for avg in ("micro", "macro", "weighted", "none"):
+                out[f"specificity_{avg}"] = F.multilabel_specificity(lp, t, L, average=avg, ignore_index=ii)
+                out[f"hamming_{avg}"] = F.multilabel_hamming_distance(lp, t, L, average=avg, ignore_index=ii)
+                out[f"jaccard_{avg}"] = F.multilabel_jaccard_index(lp, t, L, average=avg, ignore_index=ii)
+            out["mcc"] = F.multilabel_matthews_corrcoef(lp, t, L, ignore_index=ii)
+            b.add({"task": "multilabel", "kind": kind, "num_labels": L, "ignore_index": ii}, preds=lp, target=t, **out)
+    # degenerate tables the reducers special-case: perfect, all wrong, single class
+    ones, zeros = torch.ones(40, dtype=torch.long), torch.zeros(40, dtype=torch.long)
+    half = torch.cat([ones[:20], zeros[:20]])
+    for name, (p, t) in {"perfect": (half, half), "all_wrong": (half, 1 - half), "only_pos": (ones, ones),
+                         "pred_const": (ones, half)}.items():
+        b.add({"task": "binary", "kind": "degenerate_" + name, "ignore_index": None}, preds=p, target=t,
+              specificity=F.binary_specificity(p, t), hamming=F.binary_hamming_distance(p, t),
+              jaccard=F.binary_jaccard_index(p, t), kappa_none=F.binary_cohen_kappa(p, t),
+              mcc=F.binary_matthews_corrcoef(p, t))
+    b.save()
+
+
 if __name__ == "__main__":
     make_readme()
     make_confmat()
@@ -446,3 +517,4 @@ if __name__ == "__main__":
     make_binned()
     make_exact()
     make_doctests()
+    make_derived()

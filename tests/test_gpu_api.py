@@ -506,3 +506,98 @@ def test_fused_validation_raises_like_the_reference_and_restores_state(monkeypat
     # a stale finding left by an unvalidated call costs one slow check but raises nothing
     F.binary_stat_scores(ps, bad_tb, validate_args=False)
     F.binary_stat_scores(ps, tb)
+
+
+# ------------------------------------------------------------------ N2: consumers of the same update kernels
+_AVGS = ("micro", "macro", "weighted", "none")
+
+
+@pytest.mark.parametrize("c", load_golden("derived_metrics"), ids=case_id)
+def test_derived_metrics_match_reference(c):
+    """specificity / hamming (stat-scores state), jaccard / cohen kappa / matthews (confusion-matrix state): functional
+    and class results against the unmodified reference's outputs, plus two-batch accumulation in the classes."""
+    tm = _tm()
+    F = tm.functional
+    task, ii = c.meta["task"], c.meta["ignore_index"]
+    p, t = _t(c["preds"]), _t(c["target"])
+    h = p.shape[0] // 2
+
+    def cls_value(metric):
+        metric = metric.to(DEV)
+        metric.update(p[:h], t[:h])
+        metric.update(p[h:], t[h:])
+        return metric.compute()
+
+    def check(name, fn_value, metric):
+        want = c[name]
+        _close(fn_value, want, atol=2e-6)
+        _close(cls_value(metric), want, atol=2e-6)
+
+    if task == "binary":
+        check("specificity", F.binary_specificity(p, t, ignore_index=ii), tm.BinarySpecificity(ignore_index=ii))
+        check("hamming", F.binary_hamming_distance(p, t, ignore_index=ii), tm.BinaryHammingDistance(ignore_index=ii))
+        check("jaccard", F.binary_jaccard_index(p, t, ignore_index=ii), tm.BinaryJaccardIndex(ignore_index=ii))
+        check("mcc", F.binary_matthews_corrcoef(p, t, ignore_index=ii), tm.BinaryMatthewsCorrCoef(ignore_index=ii))
+        for w in ("none", "linear", "quadratic"):
+            if f"kappa_{w}" in c:
+                check(f"kappa_{w}", F.binary_cohen_kappa(p, t, weights=w, ignore_index=ii),
+                      tm.BinaryCohenKappa(weights=w, ignore_index=ii))
+        # task wrappers reach the same classes
+        _close(F.jaccard_index(p, t, task="binary", ignore_index=ii), c["jaccard"], atol=2e-6)
+        assert isinstance(tm.MatthewsCorrCoef(task="binary"), tm.BinaryMatthewsCorrCoef)
+    elif task == "multiclass":
+        C = c.meta["num_classes"]
+        for a in _AVGS:
+            check(f"specificity_{a}", F.multiclass_specificity(p, t, C, average=a, ignore_index=ii),
+                  tm.MulticlassSpecificity(C, average=a, ignore_index=ii))
+            check(f"hamming_{a}", F.multiclass_hamming_distance(p, t, C, average=a, ignore_index=ii),
+                  tm.MulticlassHammingDistance(C, average=a, ignore_index=ii))
+            check(f"jaccard_{a}", F.multiclass_jaccard_index(p, t, C, average=a, ignore_index=ii),
+                  tm.MulticlassJaccardIndex(C, average=a, ignore_index=ii))
+        for w in ("none", "linear", "quadratic"):
+            check(f"kappa_{w}", F.multiclass_cohen_kappa(p, t, C, weights=w, ignore_index=ii),
+                  tm.MulticlassCohenKappa(C, weights=w, ignore_index=ii))
+        check("mcc", F.multiclass_matthews_corrcoef(p, t, C, ignore_index=ii),
+              tm.MulticlassMatthewsCorrCoef(C, ignore_index=ii))
+        _close(F.cohen_kappa(p, t, task="multiclass", num_classes=C, ignore_index=ii), c["kappa_none"], atol=2e-6)
+        _close(F.specificity(p, t, task="multiclass", num_classes=C, average="macro", ignore_index=ii),
+               c["specificity_macro"], atol=2e-6)
+    else:
+        L = c.meta["num_labels"]
+        for a in _AVGS:
+            check(f"specificity_{a}", F.multilabel_specificity(p, t, L, average=a, ignore_index=ii),
+                  tm.MultilabelSpecificity(L, average=a, ignore_index=ii))
+            check(f"hamming_{a}", F.multilabel_hamming_distance(p, t, L, average=a, ignore_index=ii),
+                  tm.MultilabelHammingDistance(L, average=a, ignore_index=ii))
+            check(f"jaccard_{a}", F.multilabel_jaccard_index(p, t, L, average=a, ignore_index=ii),
+                  tm.MultilabelJaccardIndex(L, average=a, ignore_index=ii))
+        check("mcc", F.multilabel_matthews_corrcoef(p, t, L, ignore_index=ii),
+              tm.MultilabelMatthewsCorrCoef(L, ignore_index=ii))
+        _close(F.hamming_distance(p, t, task="multilabel", num_labels=L, average="macro", ignore_index=ii),
+               c["hamming_macro"], atol=2e-6)
+
+
+def test_derived_metrics_share_compute_groups_and_validate():
+    tm = _tm()
+    g = torch.Generator().manual_seed(8)
+    C = 7
+    t = torch.randint(0, C, (500,), generator=g).to(DEV)
+    p = torch.randint(0, C, (500,), generator=g).to(DEV)
+    coll = tm.MetricCollection([tm.MulticlassConfusionMatrix(C), tm.MulticlassJaccardIndex(C),
+                                tm.MulticlassCohenKappa(C), tm.MulticlassMatthewsCorrCoef(C),
+                                tm.MulticlassSpecificity(C), tm.MulticlassHammingDistance(C),
+                                tm.MulticlassAccuracy(C)]).to(DEV)
+    coll.update(p, t)
+    coll.update(p, t)
+    groups = sorted(len(v) for v in coll.compute_groups.values())
+    assert groups == [3, 4]  # one confusion-matrix group, one stat-scores group: two update kernels per batch
+    out = coll.compute()
+    F = tm.functional
+    _close(out["MulticlassJaccardIndex"], F.multiclass_jaccard_index(p, t, C).cpu().numpy())
+    _close(out["MulticlassSpecificity"], F.multiclass_specificity(p, t, C).cpu().numpy())
+    with pytest.raises(ValueError, match="Expected argument `weight` to be one of"):
+        tm.MulticlassCohenKappa(C, weights="cubic")
+    with pytest.raises(ValueError, match="Expected argument `average` to be one of"):
+        tm.MulticlassJaccardIndex(C, average="samples")
+    with pytest.raises(RuntimeError, match="Detected more unique values in `target`"):
+        F.multiclass_matthews_corrcoef(p, t + C * (torch.arange(500, device=DEV) % 2), C)

@@ -6,6 +6,19 @@ from torchmetrics_b200.classification.average_precision import (
     MulticlassAveragePrecision,
     MultilabelAveragePrecision,
 )
+from torchmetrics_b200.classification.confmat_derived import (
+    BinaryCohenKappa,
+    BinaryJaccardIndex,
+    BinaryMatthewsCorrCoef,
+    CohenKappa,
+    JaccardIndex,
+    MatthewsCorrCoef,
+    MulticlassCohenKappa,
+    MulticlassJaccardIndex,
+    MulticlassMatthewsCorrCoef,
+    MultilabelJaccardIndex,
+    MultilabelMatthewsCorrCoef,
+)
 from torchmetrics_b200.classification.confusion_matrix import (
     BinaryConfusionMatrix,
     ConfusionMatrix,
@@ -21,6 +34,12 @@ from torchmetrics_b200.classification.f_beta import (
     MulticlassFBetaScore,
     MultilabelF1Score,
     MultilabelFBetaScore,
+)
+from torchmetrics_b200.classification.hamming import (
+    BinaryHammingDistance,
+    HammingDistance,
+    MulticlassHammingDistance,
+    MultilabelHammingDistance,
 )
 from torchmetrics_b200.classification.precision_recall import (
     BinaryPrecision,
@@ -39,6 +58,12 @@ from torchmetrics_b200.classification.precision_recall_curve import (
     PrecisionRecallCurve,
 )
 from torchmetrics_b200.classification.roc import ROC, BinaryROC, MulticlassROC, MultilabelROC
+from torchmetrics_b200.classification.specificity import (
+    BinarySpecificity,
+    MulticlassSpecificity,
+    MultilabelSpecificity,
+    Specificity,
+)
 from torchmetrics_b200.classification.stat_scores import (
     BinaryStatScores,
     MulticlassStatScores,

@@ -11,6 +11,7 @@ from torchmetrics_b200.functional.classification.average_precision import (
     multiclass_average_precision,
     multilabel_average_precision,
 )
+from torchmetrics_b200.functional.classification.cohen_kappa import binary_cohen_kappa, cohen_kappa, multiclass_cohen_kappa
 from torchmetrics_b200.functional.classification.confusion_matrix import (
     binary_confusion_matrix,
     confusion_matrix,
@@ -26,6 +27,24 @@ from torchmetrics_b200.functional.classification.f_beta import (
     multiclass_fbeta_score,
     multilabel_f1_score,
     multilabel_fbeta_score,
+)
+from torchmetrics_b200.functional.classification.hamming import (
+    binary_hamming_distance,
+    hamming_distance,
+    multiclass_hamming_distance,
+    multilabel_hamming_distance,
+)
+from torchmetrics_b200.functional.classification.jaccard import (
+    binary_jaccard_index,
+    jaccard_index,
+    multiclass_jaccard_index,
+    multilabel_jaccard_index,
+)
+from torchmetrics_b200.functional.classification.matthews_corrcoef import (
+    binary_matthews_corrcoef,
+    matthews_corrcoef,
+    multiclass_matthews_corrcoef,
+    multilabel_matthews_corrcoef,
 )
 from torchmetrics_b200.functional.classification.precision_recall import (
     binary_precision,
@@ -44,6 +63,12 @@ from torchmetrics_b200.functional.classification.precision_recall_curve import (
     precision_recall_curve,
 )
 from torchmetrics_b200.functional.classification.roc import binary_roc, multiclass_roc, multilabel_roc, roc
+from torchmetrics_b200.functional.classification.specificity import (
+    binary_specificity,
+    multiclass_specificity,
+    multilabel_specificity,
+    specificity,
+)
 from torchmetrics_b200.functional.classification.stat_scores import (
     binary_stat_scores,
     multiclass_stat_scores,
