@@ -214,6 +214,18 @@ TMB_API int tmb_class_stats_update(const void* preds_dev, int preds_dtype, const
                                    int64_t* out_dev, void* workspace_dev, size_t workspace_bytes,
                                    int32_t* status_dev, void* stream);
 
+/* K1c with top_k > 1.  Replaces the one-hot branch of `_multiclass_stat_scores_update` (stat_scores.py:363-393,
+ * multidim_average="global"): `select_topk` one-hot of the scores, one-hot of the target and four masked sums over two
+ * (N, C) tensors.  topk_dev: (n, top_k) class ids, row-major — the indices of `preds.topk(top_k, dim=1)`, which is what
+ * `select_topk` (utilities/data.py:113-149) uses, so ties resolve identically.  target_dev: n class ids.
+ * tp[c] counts samples whose target c is among their k ids, fp[c] samples that list c without it being the target,
+ * fn[c] samples with target c not listed.  A target outside [0, C) that is not ignore_index raises
+ * TMB_STATUS_LABEL_RANGE (the reference's one_hot fails on it).  Same out / workspace contract as above. */
+TMB_API int tmb_class_stats_topk_update(const void* topk_dev, int topk_dtype, const void* target_dev, int target_dtype,
+                                        int64_t n, int64_t num_classes, int64_t top_k, int has_ignore,
+                                        int64_t ignore_index, int64_t* out_dev, void* workspace_dev,
+                                        size_t workspace_bytes, int32_t* status_dev, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * K2  tp / fp / tn / fn per label.
  * Replaces: functional/classification/stat_scores.py:120-131 `_binary_stat_scores_update` and :672-681

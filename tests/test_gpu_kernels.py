@@ -624,6 +624,37 @@ def test_class_stats_out_of_range_labels_follow_the_key_arithmetic():
     assert int(out.sum()) == int(want.sum()) + C  # one more counted sample adds C to tp+fp+tn+fn
 
 
+@pytest.mark.parametrize("C,k,shape", [(5, 2, (100,)), (10, 3, (64, 7)), (1000, 5, (2048,)), (3000, 10, (300,)),
+                                       (20_000, 5, (513,))])
+@pytest.mark.parametrize("ignore_index", [None, -1, 1])
+def test_class_stats_topk_matches_the_one_hot_branch(C, k, shape, ignore_index):
+    """top-k form of K1c == the reference's select_topk / one_hot / four masked sums (stat_scores.py:363-393),
+    restated with torch ops on the device (`_multiclass_stat_scores_onehot`), for (N, C) and (N, C, X) scores."""
+    from importlib import import_module
+
+    S = import_module("torchmetrics_b200.functional.classification.stat_scores")
+    N = _native()
+    g = torch.Generator().manual_seed(C * 31 + k)
+    n = shape[0]
+    preds = torch.randn(n, C, *shape[1:], generator=g).to(DEV)
+    preds[: n // 4] = preds[: n // 4].round()  # ties among the scores
+    target = torch.randint(0, C, shape, generator=g).to(DEV)
+    if ignore_index is not None:
+        target[::5] = ignore_index
+    p3, t2 = S._multiclass_stat_scores_format(preds, target, k)
+    want = S._multiclass_stat_scores_onehot(p3, t2, C, k, "global", ignore_index)
+    got = S._multiclass_stat_scores_update(p3, t2, C, k, "macro", "global", ignore_index)
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+    assert N.read_status_words(torch.device(DEV)) == (0, 0)
+    # a target outside [0, C) is what the reference's one_hot rejects
+    bad = target.clone()
+    bad.view(-1)[3] = C + 2
+    p3, t2 = S._multiclass_stat_scores_format(preds, bad, k)
+    S._multiclass_stat_scores_update(p3, t2, C, k, "macro", "global", ignore_index)
+    assert N.read_status_words(torch.device(DEV))[0] == N.STATUS_LABEL_RANGE
+
+
 # =========================================================================== K4b fused exact AUROC / AP
 def _auroc_ap_from_curve(N, p, t):
     """The same two scalars from the materialised curve, in float64 (what the fused kernel must reproduce)."""

@@ -47,3 +47,15 @@ for va in (True, False):
                                 tm.classification.MulticlassF1Score(num_classes=C, validate_args=va)]).to(DEV)
     bench(f"MetricCollection[Acc,P,R,F1](C=1000).update(logits[256,1000]) validate={va}", lambda: coll.update(logits, labels))
     bench(f"MetricCollection[Acc,P,R,F1](C=1000).forward(logits[256,1000]) validate={va}", lambda: coll(logits, labels))
+for va in (True, False):
+    m = tm.classification.MulticlassAccuracy(num_classes=C, top_k=5, validate_args=va).to(DEV)
+    bench(f"MulticlassAccuracy(C=1000, top_k=5).update(logits[256,1000]) validate={va}", lambda: m.update(logits, labels))
+big = torch.randn(8192, C, device=DEV, generator=g)
+bigl = torch.randint(0, C, (8192,), device=DEV, generator=g)
+m = tm.classification.MulticlassAccuracy(num_classes=C, top_k=5, validate_args=False).to(DEV)
+bench("MulticlassAccuracy(C=1000, top_k=5).update(logits[8192,1000]) validate=False", lambda: m.update(big, bigl), reps=100)
+from importlib import import_module
+S = import_module("torchmetrics_b200.functional.classification.stat_scores")
+p3, t2 = S._multiclass_stat_scores_format(big, bigl, 5)
+bench("  reference's one-hot branch (torch ops on the device), same input", lambda: S._multiclass_stat_scores_onehot(p3, t2, C, 5, "global", None), reps=100)
+bench("  torch.topk alone", lambda: big.topk(5, dim=1), reps=100)

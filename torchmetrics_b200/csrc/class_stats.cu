@@ -32,10 +32,57 @@ struct ClassParams {
   int has_ignore;
   long long ignore;
   int copies;  // shared-memory copies of the bins per CTA (0: straight to the global scratch)
+  int top_k;   // predicted classes per sample (preds is (n, top_k)); 1 for plain label predictions
   u64* out;    // [4][C] tp | fp | tn | fn, accumulated
   ClassStatsWs* ws;
   int* status;
 };
+
+// Shared tail of the two kernels: per-CTA bins -> global scratch, last CTA turns the three histograms into
+// tp / fp / tn / fn, adds them to the caller's accumulator and leaves the scratch zero.
+template <bool SMEM>
+__device__ __forceinline__ void finish(const ClassParams& P, u32* s_bins, u32* s_valid, int* s_last, u32 valid,
+                                       int bad) {
+  const int tid = threadIdx.x;
+  const u32 C = (u32)P.C;
+  u64* const hist = reinterpret_cast<u64*>(P.ws + 1);
+  if (bad) report_status(P.status, bad);
+  valid = __reduce_add_sync(0xffffffffu, valid);
+  if ((tid & 31) == 0 && valid) atomicAdd(s_valid, valid);
+  __syncthreads();
+  if constexpr (SMEM) {
+    for (u32 b = tid; b < 3u * C; b += kClassThreads) {
+      u64 v = 0;
+      for (int w = 0; w < P.copies; ++w) v += s_bins[(u32)w * 3u * C + b];
+      if (v) atomicAdd(hist + b, v);
+    }
+  }
+  if (tid == 0 && (*s_valid)) atomicAdd(&P.ws->total, (u64)(*s_valid));
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) *s_last = (atomicAdd(&P.ws->ticket, 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (!*s_last) return;
+  // last CTA: histograms -> tp / fp / tn / fn, added to the caller's accumulator; scratch left zero
+  __threadfence();
+  const u64 total = __ldcg(&P.ws->total);
+  for (u32 c = tid; c < C; c += kClassThreads) {
+    const u64 tp = __ldcg(hist + c), col = __ldcg(hist + C + c), row = __ldcg(hist + 2 * C + c);
+    hist[c] = 0;
+    hist[C + c] = 0;
+    hist[2 * C + c] = 0;
+    const u64 fp = col - tp, fn = row - tp;
+    P.out[c] += tp;
+    P.out[C + c] += fp;
+    P.out[2 * (u64)C + c] += total - tp - fp - fn;
+    P.out[3 * (u64)C + c] += fn;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    P.ws->total = 0;
+    P.ws->ticket = 0;
+  }
+}
 
 template <typename PT, typename TT, bool HAS_IGNORE, bool SMEM>
 __global__ void __launch_bounds__(kClassThreads) class_stats_kernel(const ClassParams P) {
@@ -94,42 +141,58 @@ __global__ void __launch_bounds__(kClassThreads) class_stats_kernel(const ClassP
     const long long i = (nvec << 2) + tid;
     count(preds[i], target[i]);
   }
-  if (bad) report_status(P.status, bad);
-  valid = __reduce_add_sync(0xffffffffu, valid);
-  if ((tid & 31) == 0 && valid) atomicAdd(&s_valid, valid);
+  finish<SMEM>(P, s_bins, &s_valid, &s_last, valid, bad);
+}
+
+// top_k > 1 (reference: the one-hot branch, stat_scores.py:363-393, with select_topk): every sample carries the k
+// class ids of its highest scores.  The same three histograms with "c is among the k" in place of "pred == c":
+//     tp[c] = #(target == c and c in topk)   colsum[c] = #(c in topk)   rowsum[c] = #(target == c)
+// so a sample costs k + 1 (+1) increments instead of two C-wide one-hot rows.  A target outside [0, C) that is not the
+// ignore value is what makes the reference's one_hot fail: label-range status bit.
+template <typename PT, typename TT, bool HAS_IGNORE, bool SMEM>
+__global__ void __launch_bounds__(kClassThreads) class_stats_topk_kernel(const ClassParams P) {
+  extern __shared__ u32 s_bins[];
+  __shared__ int s_last;
+  __shared__ u32 s_valid;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const u32 C = (u32)P.C;
+  const int k = P.top_k;
+  u64* const hist = reinterpret_cast<u64*>(P.ws + 1);
+  if constexpr (SMEM)
+    for (u32 i = tid; i < (u32)P.copies * 3u * C; i += kClassThreads) s_bins[i] = 0;
+  if (tid == 0) s_valid = 0;
   __syncthreads();
-  if constexpr (SMEM) {
-    for (u32 b = tid; b < 3u * C; b += kClassThreads) {
-      u64 v = 0;
-      for (int w = 0; w < P.copies; ++w) v += s_bins[(u32)w * 3u * C + b];
-      if (v) atomicAdd(hist + b, v);
+  u32* const my = SMEM ? s_bins + (u32)(warp % P.copies) * 3u * C : nullptr;
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  u32 valid = 0;
+  int bad = 0;
+  auto bump = [&](u32 idx) {
+    if constexpr (SMEM) atomicAdd(my + idx, 1u); else atomicAdd(hist + idx, 1ULL);
+  };
+  const long long stride = (long long)gridDim.x * kClassThreads;
+  for (long long i = (long long)blockIdx.x * kClassThreads + tid; i < P.n; i += stride) {
+    const long long tl = as_i64(target[i]);
+    if constexpr (HAS_IGNORE)
+      if (tl == P.ignore) continue;
+    if ((u64)tl >= (u64)P.C) {
+      bad |= TMB_STATUS_LABEL_RANGE | TMB_STATUS_TARGET_VALUES;
+      continue;
+    }
+    ++valid;
+    bump(2 * C + (u32)tl);
+    const PT* row = preds + i * k;
+    for (int j = 0; j < k; ++j) {
+      const long long pl = as_i64(row[j]);
+      if ((u64)pl >= (u64)P.C) {  // cannot come out of a top-k over C scores
+        bad |= TMB_STATUS_PREDS_VALUES;
+        continue;
+      }
+      bump(C + (u32)pl);
+      if (pl == tl) bump((u32)pl);
     }
   }
-  if (tid == 0 && s_valid) atomicAdd(&P.ws->total, (u64)s_valid);
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) s_last = (atomicAdd(&P.ws->ticket, 1) == (int)gridDim.x - 1);
-  __syncthreads();
-  if (!s_last) return;
-  // last CTA: histograms -> tp / fp / tn / fn, added to the caller's accumulator; scratch left zero
-  __threadfence();
-  const u64 total = __ldcg(&P.ws->total);
-  for (u32 c = tid; c < C; c += kClassThreads) {
-    const u64 tp = __ldcg(hist + c), col = __ldcg(hist + C + c), row = __ldcg(hist + 2 * C + c);
-    hist[c] = 0;
-    hist[C + c] = 0;
-    hist[2 * C + c] = 0;
-    const u64 fp = col - tp, fn = row - tp;
-    P.out[c] += tp;
-    P.out[C + c] += fp;
-    P.out[2 * (u64)C + c] += total - tp - fp - fn;
-    P.out[3 * (u64)C + c] += fn;
-  }
-  __syncthreads();
-  if (tid == 0) {
-    P.ws->total = 0;
-    P.ws->ticket = 0;
-  }
+  finish<SMEM>(P, s_bins, &s_valid, &s_last, valid, bad);
 }
 
 }  // namespace tmb
@@ -141,10 +204,10 @@ extern "C" size_t tmb_class_stats_workspace_bytes(int64_t num_classes) {
   return sizeof(ClassStatsWs) + (size_t)num_classes * 3 * sizeof(u64);
 }
 
-extern "C" int tmb_class_stats_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
-                                      int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index,
-                                      int64_t* out, void* workspace, size_t workspace_bytes, int32_t* status,
-                                      void* stream) {
+static int class_stats_launch(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n,
+                              int64_t num_classes, int64_t top_k, int has_ignore, int64_t ignore_index, int64_t* out,
+                              void* workspace, size_t workspace_bytes, int32_t* status, void* stream) {
+  if (top_k < 1 || top_k > num_classes) return TMB_ERR_ARG;
   if (n < 0 || num_classes < 1 || num_classes > (1LL << 31) - 1 || !out || !workspace || !status) return TMB_ERR_ARG;
   if (workspace_bytes < tmb_class_stats_workspace_bytes(num_classes)) return TMB_ERR_ARG;
   if (n == 0) return TMB_OK;
@@ -162,18 +225,27 @@ extern "C" int tmb_class_stats_update(const void* preds, int preds_dtype, const 
   P.out = (u64*)out;
   P.ws = (ClassStatsWs*)workspace;
   P.status = status;
+  P.top_k = (int)top_k;
   const size_t per_copy = (size_t)num_classes * 3 * 4;
   size_t copies = per_copy <= kClassSmemBudget ? kClassSmemBudget / per_copy : 0;
   if (copies > kClassThreads / 32) copies = kClassThreads / 32;
   P.copies = (int)copies;
   const size_t smem = copies * per_copy;
-  long long want = ((n >> 2) + kClassThreads - 1) / kClassThreads;
+  long long want = ((top_k > 1 ? n : (n >> 2)) + kClassThreads - 1) / kClassThreads;
   const long long cap = (long long)sm_count() * 4;
   const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
   cudaStream_t st = (cudaStream_t)stream;
   TMB_DISPATCH_INT(preds_dtype, PT, {
     TMB_DISPATCH_INT(target_dtype, TT, {
-      if (copies) {
+      if (top_k > 1) {
+        if (copies) {
+          if (P.has_ignore) class_stats_topk_kernel<PT, TT, true, true><<<grid, kClassThreads, smem, st>>>(P);
+          else class_stats_topk_kernel<PT, TT, false, true><<<grid, kClassThreads, smem, st>>>(P);
+        } else {
+          if (P.has_ignore) class_stats_topk_kernel<PT, TT, true, false><<<grid, kClassThreads, 0, st>>>(P);
+          else class_stats_topk_kernel<PT, TT, false, false><<<grid, kClassThreads, 0, st>>>(P);
+        }
+      } else if (copies) {
         if (P.has_ignore) class_stats_kernel<PT, TT, true, true><<<grid, kClassThreads, smem, st>>>(P);
         else class_stats_kernel<PT, TT, false, true><<<grid, kClassThreads, smem, st>>>(P);
       } else {
@@ -185,4 +257,20 @@ extern "C" int tmb_class_stats_update(const void* preds, int preds_dtype, const 
     })
   })
   return TMB_ERR_ARG;
+}
+
+extern "C" int tmb_class_stats_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                      int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index,
+                                      int64_t* out, void* workspace, size_t workspace_bytes, int32_t* status,
+                                      void* stream) {
+  return class_stats_launch(preds, preds_dtype, target, target_dtype, n, num_classes, 1, has_ignore, ignore_index, out,
+                            workspace, workspace_bytes, status, stream);
+}
+
+extern "C" int tmb_class_stats_topk_update(const void* topk, int topk_dtype, const void* target, int target_dtype,
+                                           int64_t n, int64_t num_classes, int64_t top_k, int has_ignore,
+                                           int64_t ignore_index, int64_t* out, void* workspace, size_t workspace_bytes,
+                                           int32_t* status, void* stream) {
+  return class_stats_launch(topk, topk_dtype, target, target_dtype, n, num_classes, top_k, has_ignore, ignore_index,
+                            out, workspace, workspace_bytes, status, stream);
 }

@@ -144,9 +144,18 @@ def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: i
                                    average: Optional[str] = "macro", multidim_average: str = "global",
                                    ignore_index: Optional[int] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
     """stat_scores.py:344-419."""
+    dev = preds.device
+    if (multidim_average == "global" and top_k > 1 and preds.is_cuda and preds.is_floating_point()
+            and preds.ndim == target.ndim + 1):
+        # the reference one-hots the top-k scores and the target and takes four masked sums over (N, X, C) tensors
+        # (:363-393); the class ids of the k highest scores are all the kernel needs (K1c, top-k form)
+        idx = preds.topk(top_k, dim=1).indices  # same call as select_topk: ties resolve identically
+        idx = torch.movedim(idx, 1, -1).reshape(-1, top_k)
+        stats = torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
+        _native.class_stats_topk_update_(stats, idx, target.reshape(-1), num_classes, ignore_index)
+        return stats[0], stats[1], stats[2], stats[3]
     if multidim_average == "samplewise" or top_k != 1:
         return _multiclass_stat_scores_onehot(preds, target, num_classes, top_k, multidim_average, ignore_index)
-    dev = preds.device
     if average == "micro":
         cnt = torch.zeros(2, dtype=torch.int64, device=dev)
         _native.match_count_update_(cnt, preds, target, ignore_index)
