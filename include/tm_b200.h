@@ -226,6 +226,15 @@ TMB_API int tmb_class_stats_topk_update(const void* topk_dev, int topk_dtype, co
                                         int64_t ignore_index, int64_t* out_dev, void* workspace_dev,
                                         size_t workspace_bytes, int32_t* status_dev, void* stream);
 
+/* K1c fused with the argmax of `_multiclass_stat_scores_format` (stat_scores.py:333-334) for score inputs, top_k = 1:
+ * scores_dev is (n, C) row-major float32 / float16 / bfloat16 / float64; the predicted class of a row is the index of
+ * its first maximum with NaN counting as the maximum (torch.argmax's rule).  One warp per row; the (n,) label tensor
+ * the reference materialises is never written.  target_dev, out_dev, workspace_dev, status_dev as above. */
+TMB_API int tmb_class_stats_argmax_update(const void* scores_dev, int scores_dtype, const void* target_dev,
+                                          int target_dtype, int64_t n, int64_t num_classes, int has_ignore,
+                                          int64_t ignore_index, int64_t* out_dev, void* workspace_dev,
+                                          size_t workspace_bytes, int32_t* status_dev, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * K2  tp / fp / tn / fn per label.
  * Replaces: functional/classification/stat_scores.py:120-131 `_binary_stat_scores_update` and :672-681

@@ -655,6 +655,32 @@ def test_class_stats_topk_matches_the_one_hot_branch(C, k, shape, ignore_index):
     assert N.read_status_words(torch.device(DEV))[0] == N.STATUS_LABEL_RANGE
 
 
+@pytest.mark.parametrize("C,n", [(2, 5), (5, 1000), (10, 4099), (1000, 3001), (1001, 777), (20_000, 130)])
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16, torch.bfloat16, torch.float64])
+@pytest.mark.parametrize("ignore_index", [None, -1])
+def test_class_stats_argmax_matches_argmax_then_count(C, n, dt, ignore_index):
+    """argmax form of K1c == torch.argmax followed by the label kernel: ties (first maximum wins), NaN (counts as the
+    maximum), +-inf, vector (C % 4 == 0) and scalar rows, ignore_index."""
+    N = _native()
+    g = torch.Generator().manual_seed(C + n)
+    s = torch.randn(n, C, generator=g)
+    s[::3] = s[::3].round()  # many exact ties, more so in the 16-bit dtypes
+    s[1::17, C // 2] = float("nan")
+    s[2::19, 0] = float("inf")
+    s[4::23] = float("-inf")  # whole rows of -inf: the first index wins
+    s = s.to(dt).to(DEV)
+    t = torch.randint(0, C, (n,), generator=g).to(DEV)
+    if ignore_index is not None:
+        t[::6] = ignore_index
+    got = torch.zeros(4, C, dtype=torch.int64, device=DEV)
+    N.class_stats_argmax_update_(got, s, t, C, ignore_index)
+    N.class_stats_argmax_update_(got, s, t, C, ignore_index)
+    want = torch.zeros(4, C, dtype=torch.int64, device=DEV)
+    N.class_stats_update_(want, s.argmax(dim=1), t, C, ignore_index)
+    assert torch.equal(got, 2 * want)
+    assert N.read_status_words(torch.device(DEV)) == (0, 0)
+
+
 # =========================================================================== K4b fused exact AUROC / AP
 def _auroc_ap_from_curve(N, p, t):
     """The same two scalars from the materialised curve, in float64 (what the fused kernel must reproduce)."""

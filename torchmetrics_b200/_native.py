@@ -59,6 +59,9 @@ _SIGNATURES = {
     "tmb_class_stats_topk_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                                _c.c_int64, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_size_t,
                                                _c.c_void_p, _c.c_void_p]),
+    "tmb_class_stats_argmax_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
+                                                 _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_size_t,
+                                                 _c.c_void_p, _c.c_void_p]),
     "tmb_binned_curve_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int64]),
     "tmb_binned_curve_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                            _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int64, _c.c_int,
@@ -324,6 +327,26 @@ def class_stats_topk_update_(out: Tensor, topk: Tensor, target: Tensor, num_clas
                                              0 if ignore_index is None else int(ignore_index), out.data_ptr(),
                                              ws.data_ptr(), ws.numel(), sc.status.data_ptr(), _stream_ptr(dev))
     _check(rc, "tmb_class_stats_topk_update")
+
+
+def class_stats_argmax_update_(out: Tensor, scores: Tensor, target: Tensor, num_classes: int,
+                               ignore_index: Optional[int] = None) -> None:
+    """out (4, C) int64 [tp|fp|tn|fn] += per-class statistics of (n, C) scores: argmax fused into the count (K1c)."""
+    dev = require_cuda(out, scores, target)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == 4 * num_classes
+    assert scores.ndim == 2 and scores.shape[1] == num_classes
+    scores, target = as_kernel_scores(scores), as_kernel_labels(target.reshape(-1))
+    assert scores.shape[0] == target.numel()
+    lib = load()
+    sc = scratch(dev)
+    ws = sc.workspace("class_stats", lib.tmb_class_stats_workspace_bytes(num_classes), dev)
+    with torch.cuda.device(dev):
+        rc = lib.tmb_class_stats_argmax_update(scores.data_ptr(), dtype_code(scores), target.data_ptr(),
+                                               dtype_code(target), target.numel(), num_classes,
+                                               ignore_index is not None,
+                                               0 if ignore_index is None else int(ignore_index), out.data_ptr(),
+                                               ws.data_ptr(), ws.numel(), sc.status.data_ptr(), _stream_ptr(dev))
+    _check(rc, "tmb_class_stats_argmax_update")
 
 
 def binned_curve_update_(confmat: Tensor, preds: Tensor, target: Tensor, thresholds: Tensor, num_columns: int = 1,

@@ -195,6 +195,93 @@ __global__ void __launch_bounds__(kClassThreads) class_stats_topk_kernel(const C
   finish<SMEM>(P, s_bins, &s_valid, &s_last, valid, bad);
 }
 
+// Score inputs with top_k == 1 (the usual "logits in, accuracy out" call): the reference's `_format` runs
+// `preds.argmax(dim=1)` (stat_scores.py:333-334) and the update re-reads the labels.  Here one warp takes one row of C
+// scores, finds the first maximum (torch.argmax's rule: the lowest index among equal maxima, NaN counts as the
+// maximum) and lane 0 bumps the three histograms — the (N,) label tensor is never written.
+template <typename CT>
+__device__ __forceinline__ bool beats(CT v, u32 i, CT bv, u32 bi) {
+  const bool vn = v != v, bn = bv != bv;
+  if (bn) return vn && i < bi;
+  if (vn) return true;
+  return v > bv || (v == bv && i < bi);
+}
+
+template <typename ST, typename TT, bool HAS_IGNORE, bool SMEM>
+__global__ void __launch_bounds__(kClassThreads) class_stats_argmax_kernel(const ClassParams P) {
+  using CT = typename CmpType<ST>::type;
+  extern __shared__ u32 s_bins[];
+  __shared__ int s_last;
+  __shared__ u32 s_valid;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const u32 C = (u32)P.C;
+  u64* const hist = reinterpret_cast<u64*>(P.ws + 1);
+  if constexpr (SMEM)
+    for (u32 i = tid; i < (u32)P.copies * 3u * C; i += kClassThreads) s_bins[i] = 0;
+  if (tid == 0) s_valid = 0;
+  __syncthreads();
+  u32* const my = SMEM ? s_bins + (u32)(warp % P.copies) * 3u * C : nullptr;
+  const ST* __restrict__ scores = static_cast<const ST*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  u32 valid = 0;
+  int bad = 0;
+  auto bump = [&](u32 idx) {
+    if constexpr (SMEM) atomicAdd(my + idx, 1u); else atomicAdd(hist + idx, 1ULL);
+  };
+  const bool vec = (C & 3u) == 0;  // rows start on a 4-element boundary: vector loads
+  const long long wstride = (long long)gridDim.x * (kClassThreads / 32);
+  for (long long row = (long long)blockIdx.x * (kClassThreads / 32) + warp; row < P.n; row += wstride) {
+    const long long tl = as_i64(target[row]);
+    if constexpr (HAS_IGNORE)
+      if (tl == P.ignore) continue;  // warp-uniform
+    const ST* r = scores + row * (long long)C;
+    CT bv = to_cmp(r[0]);
+    u32 bi = 0;  // every lane starts from element 0, so a lane without elements of its own still holds a valid pair
+    if (vec) {
+      for (u32 j = (u32)lane * 4; j < C; j += 128) {
+        const Vec4<ST> v = load4(r + j);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const CT x = to_cmp(v.v[q]);
+          if (beats(x, j + q, bv, bi)) { bv = x; bi = j + q; }
+        }
+      }
+    } else {
+      for (u32 j = lane; j < C; j += 32) {
+        const CT x = to_cmp(r[j]);
+        if (beats(x, j, bv, bi)) { bv = x; bi = j; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      const CT ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const u32 oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (beats(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) {
+      if ((u64)tl >= (u64)P.C) {  // pred is in range by construction: the key arithmetic of the label kernel
+        const long long k = tl * P.C + (long long)bi;
+        bad |= TMB_STATUS_TARGET_VALUES;
+        if ((u64)k >= (u64)P.CC) {
+          bad |= TMB_STATUS_LABEL_RANGE;
+        } else {
+          const u32 rr = (u32)(k / P.C), cc = (u32)(k - (long long)rr * P.C);
+          ++valid;
+          bump(C + cc);
+          bump(2 * C + rr);
+          if (rr == cc) bump(cc);
+        }
+      } else {
+        ++valid;
+        bump(C + bi);
+        bump(2 * C + (u32)tl);
+        if ((u32)tl == bi) bump(bi);
+      }
+    }
+  }
+  finish<SMEM>(P, s_bins, &s_valid, &s_last, valid, bad);
+}
+
 }  // namespace tmb
 
 using namespace tmb;
@@ -273,4 +360,52 @@ extern "C" int tmb_class_stats_topk_update(const void* topk, int topk_dtype, con
                                            int32_t* status, void* stream) {
   return class_stats_launch(topk, topk_dtype, target, target_dtype, n, num_classes, top_k, has_ignore, ignore_index,
                             out, workspace, workspace_bytes, status, stream);
+}
+
+
+extern "C" int tmb_class_stats_argmax_update(const void* scores, int scores_dtype, const void* target, int target_dtype,
+                                             int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index,
+                                             int64_t* out, void* workspace, size_t workspace_bytes, int32_t* status,
+                                             void* stream) {
+  if (n < 0 || num_classes < 1 || num_classes > (1LL << 31) - 1 || !out || !workspace || !status) return TMB_ERR_ARG;
+  if (workspace_bytes < tmb_class_stats_workspace_bytes(num_classes)) return TMB_ERR_ARG;
+  if (n == 0) return TMB_OK;
+  if (!scores || !target) return TMB_ERR_ARG;
+  if (n >= (1LL << 32)) return TMB_ERR_TOO_LARGE;
+  if (!aligned32(scores) || !aligned32(target) || !aligned32(workspace)) return TMB_ERR_ALIGN;
+  ClassParams P{};
+  P.preds = scores;
+  P.target = target;
+  P.n = n;
+  P.C = num_classes;
+  P.CC = (long long)num_classes * num_classes;
+  P.has_ignore = has_ignore ? 1 : 0;
+  P.ignore = ignore_index;
+  P.out = (u64*)out;
+  P.ws = (ClassStatsWs*)workspace;
+  P.status = status;
+  P.top_k = 1;
+  const size_t per_copy = (size_t)num_classes * 3 * 4;
+  size_t copies = per_copy <= kClassSmemBudget ? kClassSmemBudget / per_copy : 0;
+  if (copies > kClassThreads / 32) copies = kClassThreads / 32;
+  P.copies = (int)copies;
+  const size_t smem = copies * per_copy;
+  const long long want = (n + kClassThreads / 32 - 1) / (kClassThreads / 32);  // one warp per row
+  const long long cap = (long long)sm_count() * 4;
+  const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  TMB_DISPATCH_FLOAT(scores_dtype, ST, {
+    TMB_DISPATCH_INT(target_dtype, TT, {
+      if (copies) {
+        if (P.has_ignore) class_stats_argmax_kernel<ST, TT, true, true><<<grid, kClassThreads, smem, st>>>(P);
+        else class_stats_argmax_kernel<ST, TT, false, true><<<grid, kClassThreads, smem, st>>>(P);
+      } else {
+        if (P.has_ignore) class_stats_argmax_kernel<ST, TT, true, false><<<grid, kClassThreads, 0, st>>>(P);
+        else class_stats_argmax_kernel<ST, TT, false, false><<<grid, kClassThreads, 0, st>>>(P);
+      }
+      TMB_CUDA_CHECK(cudaGetLastError());
+      return TMB_OK;
+    })
+  })
+  return TMB_ERR_ARG;
 }

@@ -205,6 +205,12 @@ def _multiclass_stat_scores_reports_values(top_k: int, average: Optional[str], m
 def _multiclass_stat_scores_update_fused(preds: Tensor, target: Tensor, num_classes: int, top_k: int = 1,
                                          average: Optional[str] = "macro", multidim_average: str = "global",
                                          ignore_index: Optional[int] = None):
+    if (top_k == 1 and multidim_average == "global" and average != "micro" and preds.ndim == 2 and target.ndim == 1
+            and preds.is_cuda and preds.is_floating_point() and preds.shape[1] == num_classes):
+        # (N, C) scores: the argmax of `_format` rides on the counting kernel, one warp per row (K1c, argmax form)
+        stats = torch.zeros(4, num_classes, dtype=torch.int64, device=preds.device)
+        _native.class_stats_argmax_update_(stats, preds, target, num_classes, ignore_index)
+        return stats[0], stats[1], stats[2], stats[3]
     preds, target = _multiclass_stat_scores_format(preds, target, top_k)
     return _multiclass_stat_scores_update(preds, target, num_classes, top_k, average, multidim_average, ignore_index)
 
