@@ -167,3 +167,21 @@ def bench_class_stats():
 
 if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "class_stats"):
     bench_class_stats()
+
+
+def bench_class_stats_argmax():
+    for C, n, dt in [(1000, 8192, torch.float32), (1000, 1 << 17, torch.float32), (1000, 1 << 17, torch.bfloat16),
+                     (100, 1 << 20, torch.float32), (10, 1 << 22, torch.float32)]:
+        g = torch.Generator(device=DEV).manual_seed(1)
+        s = torch.randn(n, C, device=DEV, generator=g).to(dt)
+        t = torch.randint(0, C, (n,), device=DEV, generator=g)
+        out = torch.zeros(4, C, dtype=torch.int64, device=DEV)
+        med, best = timeit(lambda: N.class_stats_argmax_update_(out, s, t, C))
+        report(f"class_stats_argmax C={C} n={n} {str(dt)[6:]}", n * (C * s.element_size() + 8), med, best, n)
+        med, best = timeit(lambda: s.argmax(dim=1))
+        report("   torch.argmax(dim=1) alone", n * C * s.element_size(), med, best, n)
+        del s, t
+
+
+if __name__ == "__main__" and (len(sys.argv) > 1 and sys.argv[1] == "class_stats_argmax"):
+    bench_class_stats_argmax()

@@ -33,6 +33,7 @@ struct ClassParams {
   long long ignore;
   int copies;  // shared-memory copies of the bins per CTA (0: straight to the global scratch)
   int top_k;   // predicted classes per sample (preds is (n, top_k)); 1 for plain label predictions
+  int group;   // argmax form: lanes that share a row (power of two)
   u64* out;    // [4][C] tp | fp | tn | fn, accumulated
   ClassStatsWs* ws;
   int* status;
@@ -207,6 +208,12 @@ __device__ __forceinline__ bool beats(CT v, u32 i, CT bv, u32 bi) {
   return v > bv || (v == bv && i < bi);
 }
 
+// lane-local scan visits increasing indices, so "strictly better" is enough there
+template <typename CT>
+__device__ __forceinline__ bool beats_later(CT v, CT bv) {
+  return v > bv || (v != v && bv == bv);
+}
+
 template <typename ST, typename TT, bool HAS_IGNORE, bool SMEM>
 __global__ void __launch_bounds__(kClassThreads) class_stats_argmax_kernel(const ClassParams P) {
   using CT = typename CmpType<ST>::type;
@@ -228,37 +235,46 @@ __global__ void __launch_bounds__(kClassThreads) class_stats_argmax_kernel(const
   auto bump = [&](u32 idx) {
     if constexpr (SMEM) atomicAdd(my + idx, 1u); else atomicAdd(hist + idx, 1ULL);
   };
+  // g lanes share a row (a power of two, ~8 elements per lane), so a
+  // warp works on 32 / g rows at once: short rows do not leave lanes idle
+  const u32 g = (u32)P.group, sub = (u32)lane & (g - 1u), rpw = 32u / g;
   const bool vec = (C & 3u) == 0;  // rows start on a 4-element boundary: vector loads
-  const long long wstride = (long long)gridDim.x * (kClassThreads / 32);
-  for (long long row = (long long)blockIdx.x * (kClassThreads / 32) + warp; row < P.n; row += wstride) {
-    const long long tl = as_i64(target[row]);
-    if constexpr (HAS_IGNORE)
-      if (tl == P.ignore) continue;  // warp-uniform
-    const ST* r = scores + row * (long long)C;
-    CT bv = to_cmp(r[0]);
-    u32 bi = 0;  // every lane starts from element 0, so a lane without elements of its own still holds a valid pair
-    if (vec) {
-      for (u32 j = (u32)lane * 4; j < C; j += 128) {
-        const Vec4<ST> v = load4(r + j);
+  const long long wstride = (long long)gridDim.x * (kClassThreads / 32) * rpw;
+  for (long long rbase = ((long long)blockIdx.x * (kClassThreads / 32) + warp) * rpw; rbase < P.n; rbase += wstride) {
+    const long long row = rbase + (u32)lane / g;
+    bool active = row < P.n;
+    long long tl = 0;
+    if (active) {
+      tl = as_i64(target[row]);
+      if constexpr (HAS_IGNORE) active = tl != P.ignore;
+    }
+    CT bv = (CT)0;
+    u32 bi = 0;
+    if (active) {
+      const ST* r = scores + row * (long long)C;
+      bv = to_cmp(r[0]);  // every lane starts from element 0: a lane without elements of its own holds a valid pair
+      if (vec) {
+        for (u32 j = sub * 4; j < C; j += g * 4) {
+          const Vec4<ST> v = load4(r + j);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const CT x = to_cmp(v.v[q]);
-          if (beats(x, j + q, bv, bi)) { bv = x; bi = j + q; }
+          for (int q = 0; q < 4; ++q) {
+            const CT x = to_cmp(v.v[q]);
+            if (beats_later(x, bv)) { bv = x; bi = j + q; }
+          }
+        }
+      } else {
+        for (u32 j = sub; j < C; j += g) {
+          const CT x = to_cmp(r[j]);
+          if (beats_later(x, bv)) { bv = x; bi = j; }
         }
       }
-    } else {
-      for (u32 j = lane; j < C; j += 32) {
-        const CT x = to_cmp(r[j]);
-        if (beats(x, j, bv, bi)) { bv = x; bi = j; }
-      }
     }
-#pragma unroll
-    for (int o = 16; o; o >>= 1) {
+    for (u32 o = g >> 1; o; o >>= 1) {  // stays inside the aligned group of g lanes
       const CT ov = __shfl_xor_sync(0xffffffffu, bv, o);
       const u32 oi = __shfl_xor_sync(0xffffffffu, bi, o);
       if (beats(ov, oi, bv, bi)) { bv = ov; bi = oi; }
     }
-    if (lane == 0) {
+    if (active && sub == 0) {
       if ((u64)tl >= (u64)P.C) {  // pred is in range by construction: the key arithmetic of the label kernel
         const long long k = tl * P.C + (long long)bi;
         bad |= TMB_STATUS_TARGET_VALUES;
@@ -390,7 +406,11 @@ extern "C" int tmb_class_stats_argmax_update(const void* scores, int scores_dtyp
   if (copies > kClassThreads / 32) copies = kClassThreads / 32;
   P.copies = (int)copies;
   const size_t smem = copies * per_copy;
-  const long long want = (n + kClassThreads / 32 - 1) / (kClassThreads / 32);  // one warp per row
+  int group = 1;
+  while (group < 32 && (long long)group * 8 < num_classes) group <<= 1;
+  P.group = group;
+  const long long rows_per_cta = (long long)(kClassThreads / 32) * (32 / group);
+  const long long want = (n + rows_per_cta - 1) / rows_per_cta;
   const long long cap = (long long)sm_count() * 4;
   const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
   cudaStream_t st = (cudaStream_t)stream;
