@@ -235,6 +235,13 @@ TMB_API int tmb_class_stats_argmax_update(const void* scores_dev, int scores_dty
                                           int64_t ignore_index, int64_t* out_dev, void* workspace_dev,
                                           size_t workspace_bytes, int32_t* status_dev, void* stream);
 
+/* Row argmax with the class ids written out.  Replaces `preds.argmax(dim=1)` in `_multiclass_confusion_matrix_format`
+ * (confusion_matrix.py:318-319) / `_multiclass_stat_scores_format` (stat_scores.py:333-334) for (n, C) row-major
+ * scores: index of the first maximum per row, NaN counting as the maximum (torch.argmax's rule).
+ * out_dev: int32[n] — one of the label dtypes the K1 entry points read. */
+TMB_API int tmb_rows_argmax(const void* scores_dev, int scores_dtype, int64_t n, int64_t num_classes, int32_t* out_dev,
+                            void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * K2  tp / fp / tn / fn per label.
  * Replaces: functional/classification/stat_scores.py:120-131 `_binary_stat_scores_update` and :672-681

@@ -681,6 +681,26 @@ def test_class_stats_argmax_matches_argmax_then_count(C, n, dt, ignore_index):
     assert N.read_status_words(torch.device(DEV)) == (0, 0)
 
 
+@pytest.mark.parametrize("C,n", [(1, 9), (3, 1000), (10, 4099), (64, 513), (1000, 3001), (1003, 64)])
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16, torch.bfloat16, torch.float64])
+def test_rows_argmax_is_torch_argmax(C, n, dt):
+    N = _native()
+    g = torch.Generator().manual_seed(C * 7 + n)
+    s = torch.randn(n, C, generator=g)
+    s[::2] = s[::2].round()
+    if C > 1:
+        s[1::17, C // 2] = float("nan")
+        s[3::17, 0] = float("nan")
+    s[2::19, C - 1] = float("inf")
+    s[4::23] = float("-inf")
+    s[5::29] = 0.0
+    s[5::29, ::2] = -0.0  # +0.0 and -0.0 compare equal: the first index wins
+    s = s.to(dt).to(DEV)
+    got = N.rows_argmax(s)
+    assert got.dtype == torch.int32
+    assert torch.equal(got.long(), s.argmax(dim=1))
+
+
 # =========================================================================== K4b fused exact AUROC / AP
 def _auroc_ap_from_curve(N, p, t):
     """The same two scalars from the materialised curve, in float64 (what the fused kernel must reproduce)."""

@@ -62,6 +62,7 @@ _SIGNATURES = {
     "tmb_class_stats_argmax_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                                  _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_size_t,
                                                  _c.c_void_p, _c.c_void_p]),
+    "tmb_rows_argmax": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_void_p]),
     "tmb_binned_curve_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int64]),
     "tmb_binned_curve_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                            _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int64, _c.c_int,
@@ -347,6 +348,19 @@ def class_stats_argmax_update_(out: Tensor, scores: Tensor, target: Tensor, num_
                                                0 if ignore_index is None else int(ignore_index), out.data_ptr(),
                                                ws.data_ptr(), ws.numel(), sc.status.data_ptr(), _stream_ptr(dev))
     _check(rc, "tmb_class_stats_argmax_update")
+
+
+def rows_argmax(scores: Tensor) -> Tensor:
+    """int32 class id of the first maximum of every row of (n, C) scores (torch.argmax(dim=1) semantics)."""
+    dev = require_cuda(scores)
+    assert scores.ndim == 2
+    scores = as_kernel_scores(scores)
+    n, C = scores.shape
+    out = torch.empty(n, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = load().tmb_rows_argmax(scores.data_ptr(), dtype_code(scores), n, C, out.data_ptr(), _stream_ptr(dev))
+    _check(rc, "tmb_rows_argmax")
+    return out
 
 
 def binned_curve_update_(confmat: Tensor, preds: Tensor, target: Tensor, thresholds: Tensor, num_columns: int = 1,

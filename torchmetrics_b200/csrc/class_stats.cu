@@ -298,6 +298,49 @@ __global__ void __launch_bounds__(kClassThreads) class_stats_argmax_kernel(const
   finish<SMEM>(P, s_bins, &s_valid, &s_last, valid, bad);
 }
 
+// The same row scan with the class ids written out (int32): the argmax of `_multiclass_confusion_matrix_format`
+// (confusion_matrix.py:318-319) for the callers that need the labels themselves (K1's C x C matrix).
+template <typename ST>
+__global__ void __launch_bounds__(kClassThreads) rows_argmax_kernel(const ST* __restrict__ scores, long long n, u32 C,
+                                                                    u32 g, int* __restrict__ out) {
+  using CT = typename CmpType<ST>::type;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const u32 sub = (u32)lane & (g - 1u), rpw = 32u / g;
+  const bool vec = (C & 3u) == 0;
+  const long long wstride = (long long)gridDim.x * (kClassThreads / 32) * rpw;
+  for (long long rbase = ((long long)blockIdx.x * (kClassThreads / 32) + warp) * rpw; rbase < n; rbase += wstride) {
+    const long long row = rbase + (u32)lane / g;
+    const bool active = row < n;
+    CT bv = (CT)0;
+    u32 bi = 0;
+    if (active) {
+      const ST* r = scores + row * (long long)C;
+      bv = to_cmp(r[0]);
+      if (vec) {
+        for (u32 j = sub * 4; j < C; j += g * 4) {
+          const Vec4<ST> v = load4(r + j);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const CT x = to_cmp(v.v[q]);
+            if (beats_later(x, bv)) { bv = x; bi = j + q; }
+          }
+        }
+      } else {
+        for (u32 j = sub; j < C; j += g) {
+          const CT x = to_cmp(r[j]);
+          if (beats_later(x, bv)) { bv = x; bi = j; }
+        }
+      }
+    }
+    for (u32 o = g >> 1; o; o >>= 1) {
+      const CT ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const u32 oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (beats(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+    }
+    if (active && sub == 0) out[row] = (int)bi;
+  }
+}
+
 }  // namespace tmb
 
 using namespace tmb;
@@ -426,6 +469,28 @@ extern "C" int tmb_class_stats_argmax_update(const void* scores, int scores_dtyp
       TMB_CUDA_CHECK(cudaGetLastError());
       return TMB_OK;
     })
+  })
+  return TMB_ERR_ARG;
+}
+
+
+extern "C" int tmb_rows_argmax(const void* scores, int scores_dtype, int64_t n, int64_t num_classes, int32_t* out,
+                               void* stream) {
+  if (n < 0 || num_classes < 1 || num_classes > (1LL << 31) - 1 || !out) return TMB_ERR_ARG;
+  if (n == 0) return TMB_OK;
+  if (!scores) return TMB_ERR_ARG;
+  if (!aligned32(scores)) return TMB_ERR_ALIGN;
+  int group = 1;
+  while (group < 32 && (long long)group * 8 < num_classes) group <<= 1;
+  const long long rows_per_cta = (long long)(kClassThreads / 32) * (32 / group);
+  const long long want = (n + rows_per_cta - 1) / rows_per_cta;
+  const long long cap = (long long)sm_count() * 4;
+  const int grid = (int)(want < cap ? want : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  TMB_DISPATCH_FLOAT(scores_dtype, ST, {
+    rows_argmax_kernel<ST><<<grid, kClassThreads, 0, st>>>((const ST*)scores, n, (u32)num_classes, (u32)group, out);
+    TMB_CUDA_CHECK(cudaGetLastError());
+    return TMB_OK;
   })
   return TMB_ERR_ARG;
 }

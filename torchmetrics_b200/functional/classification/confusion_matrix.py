@@ -157,7 +157,10 @@ def _multiclass_confusion_matrix_update_fused(preds: Tensor, target: Tensor, num
                                               ignore_index: Optional[int] = None, out: Optional[Tensor] = None) -> Tensor:
     """argmax (when preds are scores) + ignore filter + histogram; accumulates into `out` when given."""
     if preds.ndim == target.ndim + 1:
-        preds = preds.argmax(dim=1)
+        if preds.ndim == 2 and preds.is_cuda and preds.is_floating_point():
+            preds = _native.rows_argmax(preds)  # int32 ids, same first-maximum / NaN rule as torch.argmax
+        else:
+            preds = preds.argmax(dim=1)
     cm = out if out is not None else torch.zeros(num_classes, num_classes, dtype=torch.int64, device=preds.device)
     _native.confmat_update_(cm, preds, target, num_classes, ignore_index)
     return cm
