@@ -113,8 +113,11 @@ template <typename CT>
 __device__ __forceinline__ bool out_of_unit(CT p) { return !(p >= (CT)0 && p <= (CT)1); }
 
 // last CTA: hist -> suffix sums -> confmat += ; leaves the workspace zeroed.  s_scan: 2*(T+1) u64 of smem.
+// Warps 0 and 1 scan the negative / positive histogram of a column, 32 bins per step from the top bin down (a single
+// thread walking the 201 bins of T = 200 cost ~3 us of every update).
 __device__ void finalize_columns(const BinnedParams& P, u64* hist, u64* s_scan, bool discard) {
   const int NB = P.T + 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long c = 0; c < P.num_columns; ++c) {
     u64* h = hist + c * 2 * NB;
     __syncthreads();
@@ -124,13 +127,20 @@ __device__ void finalize_columns(const BinnedParams& P, u64* hist, u64* s_scan, 
     }
     __syncthreads();
     if (!discard) {
-      // one lane per class: serial suffix sum (NB is at most a few thousand)
-      if (threadIdx.x == 0 || threadIdx.x == 32) {
-        u64* s = s_scan + (threadIdx.x ? NB : 0);
-        u64 run = 0;
-        for (int b = NB - 1; b >= 0; --b) {
-          run += s[b];
-          s[b] = run;
+      if (warp < 2) {
+        u64* s = s_scan + (warp ? NB : 0);
+        u64 carry = 0;
+        for (int top = NB - 1; top >= 0; top -= 32) {
+          const int b = top - lane;  // lane 0 holds the highest bin of the step
+          u64 v = b >= 0 ? s[b] : 0;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const u64 y = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += y;
+          }
+          v += carry;
+          carry = __shfl_sync(0xffffffffu, v, 31);
+          if (b >= 0) s[b] = v;
         }
       }
       __syncthreads();
