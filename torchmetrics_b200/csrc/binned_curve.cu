@@ -81,9 +81,8 @@ __device__ __forceinline__ int bin_of(CT p, const BinMap& m, const float* __rest
   return b;
 }
 
-// builds s_thr (T+1 floats, NaN sentinel) and s_lut for the calling CTA; returns false if unsorted
-__device__ __forceinline__ bool build_binning(const float* __restrict__ thr, int T, float* s_thr,
-                                              unsigned short* s_lut, BinMap& m) {
+// copies the thresholds into s_thr (T+1 floats, NaN sentinel) for the calling CTA; returns false if unsorted
+__device__ __forceinline__ bool load_thresholds(const float* __restrict__ thr, int T, float* s_thr, BinMap& m) {
   int unsorted = 0;
   for (int i = threadIdx.x; i <= T; i += blockDim.x) {
     float v = i < T ? thr[i] : __int_as_float(0x7fc00000);
@@ -96,6 +95,11 @@ __device__ __forceinline__ bool build_binning(const float* __restrict__ thr, int
   m.lo = lo;
   m.scale = (range > 0.f && range < 3.0e38f) ? (float)kLutCells / range : 0.f;
   if (!(m.scale < 3.0e38f)) m.scale = 0.f;
+  return !unsorted;
+}
+
+// the cell -> first-candidate table of bin_of(); only needed when the thresholds are not evenly spaced
+__device__ __forceinline__ void build_lut(int T, const float* s_thr, unsigned short* s_lut, const BinMap& m) {
   for (int c = threadIdx.x; c < kLutCells; c += blockDim.x) {
     // lower_bound over the non-decreasing sequence cell_of(thr[i]) for value c
     int l = 0, r = T;
@@ -106,7 +110,13 @@ __device__ __forceinline__ bool build_binning(const float* __restrict__ thr, int
     s_lut[c] = (unsigned short)l;
   }
   __syncthreads();
-  return !unsorted;
+}
+
+__device__ __forceinline__ bool build_binning(const float* __restrict__ thr, int T, float* s_thr,
+                                              unsigned short* s_lut, BinMap& m) {
+  const bool sorted = load_thresholds(thr, T, s_thr, m);
+  build_lut(T, s_thr, s_lut, m);
+  return sorted;
 }
 
 template <typename CT>
@@ -234,12 +244,13 @@ __global__ void __launch_bounds__(kWarpHistThreads, 2) binned_warphist_kernel(co
 
   for (int i = tid; i < copies * NB2; i += NT) s_hist[i] = 0;
   BinMap m;
-  const bool sorted = build_binning(P.thr, T, s_thr, s_lut, m);
+  const bool sorted = load_thresholds(P.thr, T, s_thr, m);
   if (!sorted) {
     if (blockIdx.x == 0 && tid == 0) atomicOr(P.status, TMB_STATUS_THRESHOLD_ORDER);
     return;
   }
   const UniformMap um = detect_uniform(s_thr, T);
+  if (!um.ok) build_lut(T, s_thr, s_lut, m);  // evenly spaced thresholds never consult the table
 
   const float* __restrict__ preds = static_cast<const float*>(P.preds);
   const TT* __restrict__ target = static_cast<const TT*>(P.target);
@@ -361,12 +372,13 @@ __global__ void __launch_bounds__(kMultiThreads, 2) binned_multicol_kernel(const
 
   for (u32 i = tid; i < (u32)copies * nbins; i += NT) s_hist[i] = 0;
   BinMap m;
-  const bool sorted = build_binning(P.thr, T, s_thr, s_lut, m);
+  const bool sorted = load_thresholds(P.thr, T, s_thr, m);
   if (!sorted) {
     if (blockIdx.x == 0 && tid == 0) atomicOr(P.status, TMB_STATUS_THRESHOLD_ORDER);
     return;
   }
   const UniformMap um = detect_uniform(s_thr, T);
+  if (!um.ok) build_lut(T, s_thr, s_lut, m);  // evenly spaced thresholds never consult the table
 
   const float* __restrict__ preds = static_cast<const float*>(P.preds);
   const TT* __restrict__ target = static_cast<const TT*>(P.target);
