@@ -7,15 +7,15 @@
 // atomics run >1500 G/s chip-wide, so the increments are moved there:
 //
 //   phase A  stream the batch once; key = target*C + pred; groups of 16 neighbouring cells (128 B of the int64
-//            state) are dealt round-robin over NB buckets (NB a power of two, >= 256):
-//                group = key >> 4,  bucket = group & (NB-1),  local bin = ((group >> log2 NB) << 4) | (key & 15) < 4096
+//            state) are dealt round-robin over NB buckets (NB a power of two, >= 128):
+//                group = key >> 4,  bucket = group & (NB-1),  local bin = ((group >> log2 NB) << 4) | (key & 15) < 8192
 //            Every bucket has a FIFO in shared memory.  A sample reserves a FIFO slot with one shared-memory atomic
-//            on the bucket's counter and stores its 12-bit local bin there (u16); nothing is kept in registers
+//            on the bucket's counter and stores its 13-bit local bin there (u16); nothing is kept in registers
 //            across a barrier.  After every 8192-sample tile the full 8-entry chunks of each FIFO are appended
 //            (16-byte vector stores, L2 "evict last") to a queue segment that belongs to this CTA and bucket alone
 //            — no global atomics, a shared cursor per bucket serialises thousands of reservations on one L2
 //            address — and the < 8 leftovers move to the front of the FIFO.  2 B/sample written.
-//   phase B  a few CTAs per bucket: histogram the bucket's segments into 4096 shared-memory bins, then add the
+//   phase B  one to four CTAs per bucket: histogram the bucket's segments into 8192 shared-memory bins, then add the
 //            non-zero bins to the int64 state (128-byte runs of REDs).
 //
 // A heavy class (a whole row or column of the matrix) spreads evenly over the buckets because neighbouring groups
