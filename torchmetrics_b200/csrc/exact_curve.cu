@@ -62,10 +62,25 @@ __global__ void __launch_bounds__(kSortThreads) k4_tile_hist(const u32* __restri
   h[threadIdx.x] = 0;
   __syncthreads();
   const long long base = (long long)blockIdx.x * kSortTile;
-#pragma unroll 4
-  for (int r = 0; r < kSortItems; ++r) {
-    long long i = base + r * kSortThreads + threadIdx.x;
-    if (i < n) atomicAdd(&h[(keys[i] >> shift) & 0xff], 1u);
+  const long long left = n - base;
+  const int valid = left < kSortTile ? (int)left : kSortTile;
+  // the key buffers are padded to whole tiles, so 16-byte loads never leave them; validity is decided per key
+  const uint4* kv = reinterpret_cast<const uint4*>(keys + base);
+#pragma unroll
+  for (int r = 0; r < kSortItems / 4; ++r) {
+    const int v = r * kSortThreads + threadIdx.x;
+    const uint4 k = kv[v];
+    const int j = v * 4;
+    if (j + 3 < valid) {
+      atomicAdd(&h[(k.x >> shift) & 0xff], 1u);
+      atomicAdd(&h[(k.y >> shift) & 0xff], 1u);
+      atomicAdd(&h[(k.z >> shift) & 0xff], 1u);
+      atomicAdd(&h[(k.w >> shift) & 0xff], 1u);
+    } else {
+      if (j < valid) atomicAdd(&h[(k.x >> shift) & 0xff], 1u);
+      if (j + 1 < valid) atomicAdd(&h[(k.y >> shift) & 0xff], 1u);
+      if (j + 2 < valid) atomicAdd(&h[(k.z >> shift) & 0xff], 1u);
+    }
   }
   __syncthreads();
   table[(long long)threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
@@ -136,27 +151,45 @@ __global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restr
                                                            int shift, const u32* __restrict__ table, int ntiles,
                                                            const u64* __restrict__ bases, u32* __restrict__ keys_out,
                                                            unsigned char* __restrict__ labs_out) {
-  __shared__ u32 s_keys[kSortTile];
-  __shared__ unsigned char s_labs[kSortTile];
+  __shared__ __align__(16) u32 s_keys[kSortTile];
+  __shared__ __align__(16) unsigned char s_labs[kSortTile];
+  __shared__ __align__(16) unsigned char s_labs_in[kSortTile];
   __shared__ u32 warp_cnt[kSortWarps][kRadix];  // per-warp digit counts, then exclusive offsets in the tile
   __shared__ u32 digit_start[kRadix];           // first position of each digit in the digit-ordered tile
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long long base = (long long)blockIdx.x * kSortTile;
+  const long long left = n - base;
+  const int valid = left < kSortTile ? (int)left : kSortTile;
   for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&warp_cnt[0][0])[i] = 0;
+  // the whole tile comes in with 16-byte loads issued back to back (the buffers are padded to whole tiles); the
+  // (warp, round, lane) order of the ranking below is then read from shared memory
+  {
+    const uint4* kv = reinterpret_cast<const uint4*>(keys_in + base);
+    uint4 k[kSortItems / 4];
+#pragma unroll
+    for (int r = 0; r < kSortItems / 4; ++r) k[r] = kv[r * kSortThreads + tid];
+    const u32 l = reinterpret_cast<const u32*>(labs_in + base)[tid];  // 4096 labels = 1024 words, 4 per thread below
+    u32 lrest[3];
+#pragma unroll
+    for (int r = 1; r < 4; ++r) lrest[r - 1] = reinterpret_cast<const u32*>(labs_in + base)[r * kSortThreads + tid];
+#pragma unroll
+    for (int r = 0; r < kSortItems / 4; ++r) reinterpret_cast<uint4*>(s_keys)[r * kSortThreads + tid] = k[r];
+    reinterpret_cast<u32*>(s_labs_in)[tid] = l;
+#pragma unroll
+    for (int r = 1; r < 4; ++r) reinterpret_cast<u32*>(s_labs_in)[r * kSortThreads + tid] = lrest[r - 1];
+  }
   __syncthreads();
 
   // warp w owns the contiguous slice [w*512, (w+1)*512) of the tile, taken 32 keys per round: input order is
   // (warp, round, lane), and ranks are handed out in exactly that order => stable
   u32 key[kSortItems];
-  unsigned char lab[kSortItems];
   unsigned short rank[kSortItems];
-  const long long wbase = base + (long long)warp * (32 * kSortItems);
+  const int wofs = warp * (32 * kSortItems) + lane;
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) key[r] = s_keys[wofs + r * 32];  // s_keys is rewritten after the next barrier
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
-    long long i = wbase + r * 32 + lane;
-    const bool in = i < n;
-    key[r] = in ? keys_in[i] : 0u;
-    lab[r] = in ? labs_in[i] : 0;
+    const bool in = wofs + r * 32 < valid;
     const u32 d = (key[r] >> shift) & 0xff;
     // lanes holding the same digit: eight ballots (one per digit bit) instead of match.any, whose cost grows with
     // the number of distinct values in the warp (~30 of 256 here) and measured 10x slower than shared-memory atomics.
@@ -207,12 +240,12 @@ __global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restr
   // stage the tile in digit order
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
-    long long i = wbase + r * 32 + lane;
-    if (i < n) {
+    const int j = wofs + r * 32;
+    if (j < valid) {
       const u32 d = (key[r] >> shift) & 0xff;
       const u32 pos = digit_start[d] + warp_cnt[warp][d] + rank[r];
       s_keys[pos] = key[r];
-      s_labs[pos] = lab[r];
+      s_labs[pos] = s_labs_in[j];
     }
   }
   __syncthreads();
@@ -222,8 +255,6 @@ __global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restr
   __shared__ long long s_dst[kRadix];
   s_dst[tid] = (long long)bases[tid] + table[(long long)tid * ntiles + blockIdx.x] - (long long)digit_start[tid];
   __syncthreads();
-  const long long remaining = n - base;
-  const int valid = remaining < kSortTile ? (int)remaining : kSortTile;
 #pragma unroll 4
   for (int pos = tid; pos < valid; pos += kSortThreads) {
     const u32 k = s_keys[pos];
