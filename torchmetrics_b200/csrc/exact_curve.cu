@@ -127,40 +127,27 @@ __global__ void __launch_bounds__(1024) k4_scan_rows(u32* __restrict__ table, in
   if (threadIdx.x == 0) totals[blockIdx.x] = carry_s;
 }
 
-// exclusive scan of the 256 digit totals -> digit bases
-__global__ void __launch_bounds__(kRadix) k4_scan_totals(const u64* __restrict__ totals, u64* __restrict__ bases) {
-  __shared__ u64 s[kRadix];
-  s[threadIdx.x] = totals[threadIdx.x];
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    u64 run = 0;
-    for (int d = 0; d < kRadix; ++d) {
-      u64 v = s[d];
-      s[d] = run;
-      run += v;
-    }
-  }
-  __syncthreads();
-  bases[threadIdx.x] = s[threadIdx.x];
-}
-
 // stable scatter of one tile
 // four CTAs per SM (64 registers): 24 % -> 48 % occupancy, 171 -> 115 us per pass at 2^24 (3, 5, 6 CTAs: slower)
 __global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restrict__ keys_in,
                                                            const unsigned char* __restrict__ labs_in, long long n,
                                                            int shift, const u32* __restrict__ table, int ntiles,
-                                                           const u64* __restrict__ bases, u32* __restrict__ keys_out,
+                                                           const u64* __restrict__ totals, u32* __restrict__ keys_out,
                                                            unsigned char* __restrict__ labs_out) {
   __shared__ __align__(16) u32 s_keys[kSortTile];
   __shared__ __align__(16) unsigned char s_labs[kSortTile];
   __shared__ __align__(16) unsigned char s_labs_in[kSortTile];
   __shared__ u32 warp_cnt[kSortWarps][kRadix];  // per-warp digit counts, then exclusive offsets in the tile
   __shared__ u32 digit_start[kRadix];           // first position of each digit in the digit-ordered tile
+  __shared__ u32 s_dst[kRadix];                 // where position 0 of the staged tile would go for each digit's run
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long long base = (long long)blockIdx.x * kSortTile;
   const long long left = n - base;
   const int valid = left < kSortTile ? (int)left : kSortTile;
   for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&warp_cnt[0][0])[i] = 0;
+  // thread d owns digit d: its global total and this tile's offset inside the digit are needed only at the end
+  const u64 my_total = totals[tid];
+  const u32 my_tile_off = table[(long long)tid * ntiles + blockIdx.x];
   // the whole tile comes in with 16-byte loads issued back to back (the buffers are padded to whole tiles); the
   // (warp, round, lane) order of the ranking below is then read from shared memory
   {
@@ -229,12 +216,30 @@ __global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restr
       u32 y = __shfl_up_sync(0xffffffffu, x, o);
       if (lane >= o) x += y;
     }
+    // ... and of the global digit totals: base of digit d in the output (replaces a separate 1-CTA scan kernel)
+    u64 gx = my_total;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const u64 gy = __shfl_up_sync(0xffffffffu, gx, o);
+      if (lane >= o) gx += gy;
+    }
     __shared__ u32 wsum[kSortWarps];
-    if (lane == 31) wsum[warp] = x;
+    __shared__ u64 gsum[kSortWarps];
+    if (lane == 31) {
+      wsum[warp] = x;
+      gsum[warp] = gx;
+    }
     __syncthreads();
     u32 add = 0;
-    for (int w = 0; w < warp; ++w) add += wsum[w];
+    u64 gadd = 0;
+    for (int w = 0; w < warp; ++w) {
+      add += wsum[w];
+      gadd += gsum[w];
+    }
     digit_start[d] = add + x - run;
+    // destination of digit d's run: global digit base + this tile's offset inside the digit - the run's start in the
+    // staged tile; < 2^32 once a position is added, so 32-bit wrap-around arithmetic is exact
+    s_dst[d] = (u32)(gadd + gx - my_total) + my_tile_off - (add + x - run);
   }
   __syncthreads();
   // stage the tile in digit order
@@ -249,16 +254,11 @@ __global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restr
     }
   }
   __syncthreads();
-  // coalesced write-out: consecutive threads hold consecutive positions of the same digit run.  The destination of
-  // digit d's run (global digit base + this tile's offset inside the digit - its start in the staged tile) is
-  // fetched once per digit, not once per key.
-  __shared__ long long s_dst[kRadix];
-  s_dst[tid] = (long long)bases[tid] + table[(long long)tid * ntiles + blockIdx.x] - (long long)digit_start[tid];
-  __syncthreads();
+  // coalesced write-out: consecutive threads hold consecutive positions of the same digit run
 #pragma unroll 4
   for (int pos = tid; pos < valid; pos += kSortThreads) {
     const u32 k = s_keys[pos];
-    const long long dst = s_dst[(k >> shift) & 0xff] + pos;
+    const u32 dst = s_dst[(k >> shift) & 0xff] + (u32)pos;
     keys_out[dst] = k;
     labs_out[dst] = s_labs[pos];
   }
@@ -771,8 +771,7 @@ static int k4_sort(const float* preds, const void* target, int target_dtype, lon
     const int shift = 8 * pass;
     k4_tile_hist<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], n, shift, ws.table, ntiles);
     k4_scan_rows<<<kRadix, 1024, 0, st>>>(ws.table, ntiles, ws.totals);
-    k4_scan_totals<<<1, kRadix, 0, st>>>(ws.totals, ws.bases);
-    k4_scatter<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], ws.labs[cur], n, shift, ws.table, ntiles, ws.bases,
+    k4_scatter<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], ws.labs[cur], n, shift, ws.table, ntiles, ws.totals,
                                                 ws.keys[cur ^ 1], ws.labs[cur ^ 1]);
     cur ^= 1;
   }
