@@ -265,26 +265,47 @@ __global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restr
 }
 
 // ---- scan over the sorted sequence ------------------------------------------------------------------
-// run end at i  <=>  i == n-1 or score[i] != score[i+1] (float compare: -0.0 and 0.0 are one run, as in the
-// reference's `preds[1:] - preds[:-1]`)
-__device__ __forceinline__ bool run_end(const u32* __restrict__ keys, long long i, long long n) {
-  if (i == n - 1) return true;
-  float a = key_to_float(keys[i]), b = key_to_float(keys[i + 1]);
-  return (a - b) != 0.0f;  // NaN - x is NaN != 0 -> true, exactly what torch.where(diff) sees
+// run end at i  <=>  i == n-1 or score[i] != score[i+1] (float compare: -0.0 and 0.0 are one run, NaN - x != 0 is
+// true: exactly what the reference's `torch.where(preds[1:] - preds[:-1])` sees)
+
+// A thread's 16 consecutive items of a tile, loaded with 16-byte loads (the buffers are padded to whole tiles and the
+// element after the tile is readable: it lies in the workspace and only matters when it belongs to the input).
+struct Items16 {
+  u32 labels;  // bit r: item r is a positive
+  u32 ends;    // bit r: item r is a run end
+};
+__device__ __forceinline__ Items16 load_items16(const u32* __restrict__ keys, const unsigned char* __restrict__ labs,
+                                                long long first, long long n) {
+  u32 k[kSortItems + 1];
+  const uint4* kv = reinterpret_cast<const uint4*>(keys + first);
+#pragma unroll
+  for (int q = 0; q < kSortItems / 4; ++q) {
+    const uint4 v = kv[q];
+    k[4 * q] = v.x; k[4 * q + 1] = v.y; k[4 * q + 2] = v.z; k[4 * q + 3] = v.w;
+  }
+  k[kSortItems] = keys[first + kSortItems];
+  const uint4 lv = *reinterpret_cast<const uint4*>(labs + first);
+  const u32 lw[4] = {lv.x, lv.y, lv.z, lv.w};
+  Items16 it{0u, 0u};
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) {
+    const long long i = first + r;
+    const bool in = i < n;
+    const u32 lab = (lw[r >> 2] >> (8 * (r & 3))) & 0xffu;
+    // run end  <=>  last element, or score differs from the next one (float compare: -0.0 == 0.0, NaN != x)
+    const bool end = in && (i == n - 1 || (key_to_float(k[r]) - key_to_float(k[r + 1])) != 0.0f);
+    it.labels |= (u32)(in && lab) << r;
+    it.ends |= (u32)end << r;
+  }
+  return it;
 }
 
 __global__ void __launch_bounds__(kSortThreads) k4_tile_sums(const u32* __restrict__ keys,
                                                              const unsigned char* __restrict__ labs, long long n,
                                                              u64* __restrict__ tile_pos, u64* __restrict__ tile_ends) {
-  const long long base = (long long)blockIdx.x * kSortTile;
-  u32 pos = 0, ends = 0;
-  for (int r = 0; r < kSortItems; ++r) {
-    long long i = base + r * kSortThreads + threadIdx.x;
-    if (i < n) {
-      pos += labs[i];
-      ends += run_end(keys, i, n);
-    }
-  }
+  const long long first = (long long)blockIdx.x * kSortTile + (long long)threadIdx.x * kSortItems;
+  const Items16 it = load_items16(keys, labs, first, n);
+  u32 pos = __popc(it.labels), ends = __popc(it.ends);
   pos = __reduce_add_sync(0xffffffffu, pos);
   ends = __reduce_add_sync(0xffffffffu, ends);
   __shared__ u32 sp[kSortWarps], se[kSortWarps];
@@ -440,18 +461,10 @@ __global__ void __launch_bounds__(kSortThreads) k4_tile_sums_last(const u32* __r
                                                                   u64* __restrict__ tile_last_idx1,
                                                                   u64* __restrict__ tile_last_tp) {
   const long long base = (long long)blockIdx.x * kSortTile;
-  u32 pos = 0, ends = 0, last1 = 0;  // last1: (local index of the last run end seen by this thread) + 1
-  for (int r = 0; r < kSortItems; ++r) {
-    const int j = r * kSortThreads + threadIdx.x;
-    const long long i = base + j;
-    if (i < n) {
-      pos += labs[i];
-      if (run_end(keys, i, n)) {
-        ++ends;
-        last1 = (u32)j + 1;  // j grows with r
-      }
-    }
-  }
+  const int j0 = threadIdx.x * kSortItems;  // local index of this thread's first item
+  const Items16 it = load_items16(keys, labs, base + j0, n);
+  u32 pos = __popc(it.labels), ends = __popc(it.ends);
+  u32 last1 = it.ends ? (u32)j0 + (32u - __clz(it.ends)) : 0u;  // (local index of this thread's last run end) + 1
   pos = __reduce_add_sync(0xffffffffu, pos);
   ends = __reduce_add_sync(0xffffffffu, ends);
   last1 = __reduce_max_sync(0xffffffffu, last1);
@@ -470,11 +483,10 @@ __global__ void __launch_bounds__(kSortThreads) k4_tile_sums_last(const u32* __r
   }
   __syncthreads();
   const u32 lastidx1 = s_last1;
-  u32 upto = 0;  // positives of the tile at local indices < lastidx1
-  for (int r = 0; r < kSortItems; ++r) {
-    const int j = r * kSortThreads + threadIdx.x;
-    if ((u32)j < lastidx1) upto += labs[base + j];  // in range: lastidx1 <= number of valid items
-  }
+  // positives of the tile at local indices < lastidx1: this thread's items r with j0 + r < lastidx1
+  const int keep = (int)lastidx1 - j0;
+  const u32 mask = keep <= 0 ? 0u : keep >= kSortItems ? 0xffffu : ((1u << keep) - 1u);
+  u32 upto = __popc(it.labels & mask);
   upto = __reduce_add_sync(0xffffffffu, upto);
   if ((threadIdx.x & 31) == 0) sq[threadIdx.x >> 5] = upto;
   __syncthreads();
