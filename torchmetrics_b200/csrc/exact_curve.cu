@@ -588,7 +588,10 @@ __global__ void __launch_bounds__(1024) k4_scan_tiles_last(u64* __restrict__ til
   }
 }
 
-// per tile: the two sums over the tile's run ends, written to tile_auc / tile_ap (deterministic: no float atomics)
+// per tile: the two sums over the tile's run ends, written to tile_auc / tile_ap (deterministic: no float atomics).
+// A thread walks the run ends among its 16 consecutive items with the running (TP, FP) in registers; what it needs
+// from the threads before it — positives so far and the previous run end — comes from two block scans (a sum and a
+// "latest" = max, cumulative counts being monotone).
 __global__ void __launch_bounds__(kSortThreads) k4_reduce_tiles(const u32* __restrict__ keys,
                                                                 const unsigned char* __restrict__ labs, long long n,
                                                                 const u64* __restrict__ tile_pos,
@@ -596,78 +599,77 @@ __global__ void __launch_bounds__(kSortThreads) k4_reduce_tiles(const u32* __res
                                                                 const u64* __restrict__ tile_last_tp,
                                                                 double* __restrict__ tile_auc,
                                                                 double* __restrict__ tile_ap) {
-  __shared__ u32 s_key[kSortThreads * (kSortItems + 1) + 1];
-  __shared__ unsigned char s_lab[kSortTile];
-  __shared__ u32 wp[kSortWarps], we[kSortWarps];
+  __shared__ u32 wp[kSortWarps], wl[kSortWarps], wt[kSortWarps];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long long tbase = (long long)blockIdx.x * kSortTile;
-  for (int j = tid; j <= kSortTile; j += kSortThreads) {
-    const long long i = tbase + j;
-    const u32 k = i < n ? keys[i] : 0u;
-    s_key[(j / kSortItems) * (kSortItems + 1) + (j % kSortItems)] = k;
-    if (j < kSortTile) s_lab[j] = i < n ? labs[i] : 0;
-  }
-  __syncthreads();
-  const u32* mk = s_key + tid * (kSortItems + 1);
-  const u32 next_first = s_key[(tid + 1) * (kSortItems + 1)];  // item 0 of thread t+1
-  const long long base = tbase + (long long)tid * kSortItems;
-  u32 lp[kSortItems];
-  bool le[kSortItems];
-  u32 tp = 0, te = 0;
-#pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    const long long i = base + r;
-    const bool in = i < n;
-    lp[r] = in ? s_lab[tid * kSortItems + r] : 0;
-    const u32 nxt = r + 1 < kSortItems ? mk[r + 1] : next_first;
-    le[r] = in && (i == n - 1 || (key_to_float(mk[r]) - key_to_float(nxt)) != 0.0f);
-    tp += lp[r];
-    te += le[r];
-  }
-  u32 xp = tp, xe = te;
+  const int j0 = tid * kSortItems;
+  const Items16 it = load_items16(keys, labs, tbase + j0, n);
+  const u32 npos = __popc(it.labels);
+  // this thread's last run end: (local index + 1, positives of the thread up to and including it); 0 = none
+  const u32 hi = it.ends ? 32u - __clz(it.ends) : 0u;  // 1-based position of the highest set bit
+  const u32 my_last1 = it.ends ? (u32)j0 + hi : 0u;
+  const u32 my_last_pos = it.ends ? __popc(it.labels & (0xffffffffu >> (32u - hi))) : 0u;
+  // inclusive scans over the warp: positives (sum); last run end and the tile-local TP there (max)
+  u32 xp = npos, xl = my_last1;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const u32 yp = __shfl_up_sync(0xffffffffu, xp, o), ye = __shfl_up_sync(0xffffffffu, xe, o);
-    if (lane >= o) { xp += yp; xe += ye; }
+    const u32 yp = __shfl_up_sync(0xffffffffu, xp, o), yl = __shfl_up_sync(0xffffffffu, xl, o);
+    if (lane >= o) {
+      xp += yp;
+      xl = yl > xl ? yl : xl;
+    }
   }
-  if (lane == 31) { wp[warp] = xp; we[warp] = xe; }
+  if (lane == 31) {
+    wp[warp] = xp;
+    wl[warp] = xl;
+  }
   __syncthreads();
-  u32 addp = 0, adde = 0;
-  for (int w = 0; w < warp; ++w) { addp += wp[w]; adde += we[w]; }
-  __shared__ unsigned short s_idx[kSortTile];
-  __shared__ unsigned short s_cum[kSortTile];
-  u32 local_pos = addp + xp - tp;
-  u32 slot = adde + xe - te;
+  u32 addp = 0, prevl_w = 0;
+  for (int w = 0; w < warp; ++w) {
+    addp += wp[w];
+    prevl_w = wl[w] > prevl_w ? wl[w] : prevl_w;
+  }
+  const u32 tp_before = addp + xp - npos;            // positives of the tile before this thread's first item
+  const u32 my_last_tp = tp_before + my_last_pos;    // tile-local TP at this thread's last run end (if any)
+  u32 xt = it.ends ? my_last_tp : 0u;                // max-scan: TP is monotone, so the latest is the largest
 #pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    local_pos += lp[r];
-    if (le[r]) {
-      s_idx[slot] = (unsigned short)(tid * kSortItems + r);
-      s_cum[slot] = (unsigned short)local_pos;
-      ++slot;
-    }
+  for (int o = 1; o < 32; o <<= 1) {
+    const u32 yt = __shfl_up_sync(0xffffffffu, xt, o);
+    if (lane >= o) xt = yt > xt ? yt : xt;
   }
-  __shared__ u32 s_nend;
-  if (tid == kSortThreads - 1) s_nend = slot;
+  if (lane == 31) wt[warp] = xt;
   __syncthreads();
-  const u32 nend = s_nend;
+  u32 prevt_w = 0;
+  for (int w = 0; w < warp; ++w) prevt_w = wt[w] > prevt_w ? wt[w] : prevt_w;
+  // exclusive: the lanes before this one
+  u32 pl = __shfl_up_sync(0xffffffffu, xl, 1), pt = __shfl_up_sync(0xffffffffu, xt, 1);
+  if (lane == 0) {
+    pl = 0;
+    pt = 0;
+  }
+  const u32 prev_l = pl > prevl_w ? pl : prevl_w;  // local (index + 1) of the previous run end in this tile, 0 = none
+  const u32 prev_t = pt > prevt_w ? pt : prevt_w;
   const u64 pos0 = tile_pos[blockIdx.x];
-  const u64 prev_idx1 = tile_last_idx1[blockIdx.x], prev_tp0 = tile_last_tp[blockIdx.x];
+  u64 tpp, fpp;  // cumulative counts at the previous run end
+  if (prev_l) {
+    tpp = pos0 + prev_t;
+    fpp = (u64)tbase + prev_l - tpp;
+  } else {
+    tpp = tile_last_tp[blockIdx.x];
+    fpp = tile_last_idx1[blockIdx.x] - tpp;
+  }
   double auc = 0.0, ap = 0.0;
-  for (u32 e = tid; e < nend; e += kSortThreads) {
-    const u64 tpk = pos0 + s_cum[e];
-    const u64 idx1 = (u64)tbase + s_idx[e] + 1;  // TP_k + FP_k
+  u32 e = it.ends;
+  while (e) {
+    const u32 r = __ffs(e) - 1;
+    e &= e - 1;
+    const u64 tpk = pos0 + tp_before + __popc(it.labels & (0xffffffffu >> (31u - r)));
+    const u64 idx1 = (u64)tbase + j0 + r + 1;  // TP_k + FP_k
     const u64 fpk = idx1 - tpk;
-    u64 tpp, fpp;
-    if (e) {
-      tpp = pos0 + s_cum[e - 1];
-      fpp = (u64)tbase + s_idx[e - 1] + 1 - tpp;
-    } else {
-      tpp = prev_tp0;
-      fpp = prev_idx1 - prev_tp0;
-    }
     auc += (double)(fpk - fpp) * (double)(tpk + tpp);
-    ap += (double)(tpk - tpp) * ((double)tpk / (double)idx1);
+    if (tpk != tpp) ap += (double)(tpk - tpp) * ((double)tpk / (double)idx1);
+    tpp = tpk;
+    fpp = fpk;
   }
   // fixed-order block reduction
 #pragma unroll
@@ -676,13 +678,19 @@ __global__ void __launch_bounds__(kSortThreads) k4_reduce_tiles(const u32* __res
     ap += __shfl_xor_sync(0xffffffffu, ap, o);
   }
   __shared__ double ra[kSortWarps], rb[kSortWarps];
-  if (lane == 0) { ra[warp] = auc; rb[warp] = ap; }
+  if (lane == 0) {
+    ra[warp] = auc;
+    rb[warp] = ap;
+  }
   __syncthreads();
   if (tid == 0) {
-    double a = 0.0, b = 0.0;
-    for (int w = 0; w < kSortWarps; ++w) { a += ra[w]; b += rb[w]; }
-    tile_auc[blockIdx.x] = a;
-    tile_ap[blockIdx.x] = b;
+    double x = 0.0, y = 0.0;
+    for (int w = 0; w < kSortWarps; ++w) {
+      x += ra[w];
+      y += rb[w];
+    }
+    tile_auc[blockIdx.x] = x;
+    tile_ap[blockIdx.x] = y;
   }
 }
 

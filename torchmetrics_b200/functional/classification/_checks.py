@@ -241,3 +241,13 @@ def check_float_preds(preds: Tensor) -> None:
             "Expected argument `preds` to be an floating tensor with probability/logit scores,"
             f" but got tensor with dtype {preds.dtype}"
         )
+
+
+def in_unit_interval(preds: Tensor) -> bool:
+    """`torch.all((preds >= 0) * (preds <= 1))` of the reference's `_format` steps (e.g. precision_recall_curve.py:183)
+    in one pass: min >= 0 and max <= 1.  NaN propagates through aminmax and fails both comparisons, like the
+    elementwise form; an empty tensor passes, like `torch.all` of nothing."""
+    if preds.numel() == 0:
+        return True
+    lo, hi = torch.aminmax(preds)
+    return bool((lo >= 0) & (hi <= 1))

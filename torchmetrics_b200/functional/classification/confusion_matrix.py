@@ -64,7 +64,7 @@ def _binary_confusion_matrix_format(preds: Tensor, target: Tensor, threshold: fl
         keep = target != ignore_index
         preds, target = preds[keep], target[keep]
     if preds.is_floating_point():
-        if not torch.all((preds >= 0) * (preds <= 1)):
+        if not C.in_unit_interval(preds):
             preds = preds.sigmoid()
         if convert_to_labels:
             preds = preds > threshold
@@ -207,7 +207,7 @@ def _multilabel_confusion_matrix_format(preds: Tensor, target: Tensor, num_label
                                         ) -> Tuple[Tensor, Tensor]:
     """Reference-contract formatting (confusion_matrix.py:486-518): ignored entries become -4*L."""
     if preds.is_floating_point():
-        if not torch.all((preds >= 0) * (preds <= 1)):
+        if not C.in_unit_interval(preds):
             preds = preds.sigmoid()
         if should_threshold:
             preds = preds > threshold

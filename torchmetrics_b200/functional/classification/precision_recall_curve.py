@@ -112,7 +112,7 @@ def _binary_precision_recall_curve_format(preds: Tensor, target: Tensor,
     if ignore_index is not None:
         keep = target != ignore_index
         preds, target = preds[keep], target[keep]
-    if not torch.all((preds >= 0) * (preds <= 1)):
+    if not C.in_unit_interval(preds):
         preds = preds.sigmoid()
     return preds, target, _adjust_threshold_arg(thresholds, preds.device)
 
@@ -236,7 +236,7 @@ def _multiclass_precision_recall_curve_format(preds: Tensor, target: Tensor, num
     if ignore_index is not None:
         keep = target != ignore_index
         preds, target = preds[keep], target[keep]
-    if not torch.all((preds >= 0) * (preds <= 1)):
+    if not C.in_unit_interval(preds):
         preds = preds.softmax(1)
     if average == "micro":
         preds = preds.flatten()
@@ -381,7 +381,7 @@ def _multilabel_precision_recall_curve_format(preds: Tensor, target: Tensor, num
     """Reference-contract formatting (precision_recall_curve.py:739-766)."""
     preds = preds.transpose(0, 1).reshape(num_labels, -1).T
     target = target.transpose(0, 1).reshape(num_labels, -1).T
-    if not torch.all((preds >= 0) * (preds <= 1)):
+    if not C.in_unit_interval(preds):
         preds = preds.sigmoid()
     thresholds = _adjust_threshold_arg(thresholds, preds.device)
     if ignore_index is not None and thresholds is not None:

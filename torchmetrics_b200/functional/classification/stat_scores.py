@@ -56,7 +56,7 @@ def _binary_stat_scores_format(preds: Tensor, target: Tensor, threshold: float =
                                ignore_index: Optional[int] = None) -> Tuple[Tensor, Tensor]:
     """Reference-contract formatting (stat_scores.py:90-117): ignored targets become -1."""
     if preds.is_floating_point():
-        if not torch.all((preds >= 0) * (preds <= 1)):
+        if not C.in_unit_interval(preds):
             preds = preds.sigmoid()
         preds = preds > threshold
     preds = preds.reshape(preds.shape[0], -1)
@@ -274,7 +274,7 @@ def _multilabel_stat_scores_format(preds: Tensor, target: Tensor, num_labels: in
                                    ignore_index: Optional[int] = None) -> Tuple[Tensor, Tensor]:
     """Reference-contract formatting (stat_scores.py:647-669): (N, L, X) label tensors, ignored targets -1."""
     if preds.is_floating_point():
-        if not torch.all((preds >= 0) * (preds <= 1)):
+        if not C.in_unit_interval(preds):
             preds = preds.sigmoid()
         preds = preds > threshold
     preds = preds.reshape(*preds.shape[:2], -1)
