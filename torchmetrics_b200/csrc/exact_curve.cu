@@ -275,7 +275,7 @@ struct Items16 {
   u32 ends;    // bit r: item r is a run end
 };
 __device__ __forceinline__ Items16 load_items16(const u32* __restrict__ keys, const unsigned char* __restrict__ labs,
-                                                long long first, long long n) {
+                                                long long first, long long n, u32* keys_out = nullptr) {
   u32 k[kSortItems + 1];
   const uint4* kv = reinterpret_cast<const uint4*>(keys + first);
 #pragma unroll
@@ -296,6 +296,10 @@ __device__ __forceinline__ Items16 load_items16(const u32* __restrict__ keys, co
     const bool end = in && (i == n - 1 || (key_to_float(k[r]) - key_to_float(k[r + 1])) != 0.0f);
     it.labels |= (u32)(in && lab) << r;
     it.ends |= (u32)end << r;
+  }
+  if (keys_out) {
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) keys_out[r] = k[r];
   }
   return it;
 }
@@ -370,80 +374,55 @@ __global__ void __launch_bounds__(1024) k4_scan_tiles(u64* __restrict__ tile_pos
   }
 }
 
-// per tile: inclusive scans with the tile's base, emit at run ends
+// per tile: inclusive scans with the tile's base, emit at run ends.  A thread owns 16 consecutive items (16-byte
+// loads); the tile's run ends are compacted in shared memory (local position, positives so far, score) so that the
+// three output arrays are written with consecutive threads on consecutive rows.
 __global__ void __launch_bounds__(kSortThreads) k4_emit(const u32* __restrict__ keys,
                                                         const unsigned char* __restrict__ labs, long long n,
                                                         const u64* __restrict__ tile_pos, const u64* __restrict__ tile_ends,
                                                         long long* __restrict__ fps, long long* __restrict__ tps,
                                                         float* __restrict__ thr) {
-  // The tile (+ the first key of the next tile) is staged in shared memory with coalesced loads; thread t then owns
-  // items [t*16, t*16+16) so its running sums are sequential.  Row stride 17 words keeps the blocked reads
-  // conflict-free (bank = (17*t + r) % 32).
-  __shared__ u32 s_key[kSortThreads * (kSortItems + 1) + 1];
-  __shared__ unsigned char s_lab[kSortTile];
   __shared__ u32 wp[kSortWarps], we[kSortWarps];
+  __shared__ unsigned short s_idx[kSortTile];
+  __shared__ unsigned short s_cum[kSortTile];
+  __shared__ float s_thr[kSortTile];
+  __shared__ u32 s_nend;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long long tbase = (long long)blockIdx.x * kSortTile;
-  for (int j = tid; j <= kSortTile; j += kSortThreads) {
-    const long long i = tbase + j;
-    const u32 k = i < n ? keys[i] : 0u;
-    s_key[(j / kSortItems) * (kSortItems + 1) + (j % kSortItems)] = k;
-    if (j < kSortTile) s_lab[j] = i < n ? labs[i] : 0;
-  }
-  __syncthreads();
-  const u32* mk = s_key + tid * (kSortItems + 1);
-  const u32 next_first = s_key[((tid + 1) * kSortItems / kSortItems) * (kSortItems + 1)];  // item 0 of thread t+1
-  const long long base = tbase + (long long)tid * kSortItems;
-  u32 lp[kSortItems];
-  bool le[kSortItems];
-  u32 tp = 0, te = 0;
-#pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    const long long i = base + r;
-    const bool in = i < n;
-    lp[r] = in ? s_lab[tid * kSortItems + r] : 0;
-    const u32 nxt = r + 1 < kSortItems ? mk[r + 1] : next_first;
-    // run end  <=>  last element, or score differs from the next one (float compare: -0.0 == 0.0, NaN != x)
-    le[r] = in && (i == n - 1 || (key_to_float(mk[r]) - key_to_float(nxt)) != 0.0f);
-    tp += lp[r];
-    te += le[r];
-  }
+  const int j0 = tid * kSortItems;
+  u32 k[kSortItems];
+  const Items16 it = load_items16(keys, labs, tbase + j0, n, k);
+  const u32 tp = __popc(it.labels), te = __popc(it.ends);
   u32 xp = tp, xe = te;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    u32 yp = __shfl_up_sync(0xffffffffu, xp, o), ye = __shfl_up_sync(0xffffffffu, xe, o);
+    const u32 yp = __shfl_up_sync(0xffffffffu, xp, o), ye = __shfl_up_sync(0xffffffffu, xe, o);
     if (lane >= o) { xp += yp; xe += ye; }
   }
   if (lane == 31) { wp[warp] = xp; we[warp] = xe; }
   __syncthreads();
   u32 addp = 0, adde = 0;
   for (int w = 0; w < warp; ++w) { addp += wp[w]; adde += we[w]; }
-  // compact this tile's run ends in shared memory (position in tile + positives so far in tile), then write the
-  // three output arrays with consecutive threads on consecutive rows
-  __shared__ unsigned short s_idx[kSortTile];
-  __shared__ unsigned short s_cum[kSortTile];
-  u32 local_pos = addp + xp - tp;   // positives of this tile strictly before this thread's first item
-  u32 slot = adde + xe - te;        // run ends of this tile before this thread
+  const u32 pos_before = addp + xp - tp;  // positives of this tile strictly before this thread's first item
+  u32 slot = adde + xe - te;              // run ends of this tile before this thread
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
-    local_pos += lp[r];
-    if (le[r]) {
-      s_idx[slot] = (unsigned short)(tid * kSortItems + r);
-      s_cum[slot] = (unsigned short)local_pos;  // <= 4096 fits
+    if ((it.ends >> r) & 1u) {
+      s_idx[slot] = (unsigned short)(j0 + r);
+      s_cum[slot] = (unsigned short)(pos_before + __popc(it.labels & (0xffffffffu >> (31 - r))));  // <= 4096 fits
+      s_thr[slot] = key_to_float(k[r]);
       ++slot;
     }
   }
-  __shared__ u32 s_nend;
   if (tid == kSortThreads - 1) s_nend = slot;
   __syncthreads();
   const u32 nend = s_nend;
   const u64 pos0 = tile_pos[blockIdx.x], out0 = tile_ends[blockIdx.x];
   for (u32 e = tid; e < nend; e += kSortThreads) {
-    const u32 j = s_idx[e];
     const long long tpv = (long long)(pos0 + s_cum[e]);
     tps[out0 + e] = tpv;
-    fps[out0 + e] = tbase + j + 1 - tpv;
-    thr[out0 + e] = key_to_float(s_key[(j / kSortItems) * (kSortItems + 1) + (j % kSortItems)]);
+    fps[out0 + e] = tbase + s_idx[e] + 1 - tpv;
+    thr[out0 + e] = s_thr[e];
   }
 }
 
