@@ -168,6 +168,45 @@ def _body_custom_sync_fn_protocol(rank):
     assert len(calls) == 5  # once per state tensor, as the reference does
 
 
+class _Narrow(Metric):
+    full_state_update = False
+
+    def __init__(self, **kwargs):
+        super().__init__(**kwargs)
+        self.add_state("flag", torch.zeros(3, dtype=torch.bool), dist_reduce_fx="sum")
+        self.add_state("small", torch.zeros(2, dtype=torch.int32), dist_reduce_fx="sum")
+        self.add_state("byte", torch.zeros(1, dtype=torch.uint8), dist_reduce_fx="sum")
+        self.add_state("half", torch.zeros(2, dtype=torch.float16), dist_reduce_fx="mean")
+        self.add_state("seen", torch.zeros(2, dtype=torch.bool), dist_reduce_fx="max")
+
+    def update(self, rank):
+        self.flag = torch.tensor([True, rank == 1, False])
+        self.small = torch.tensor([2**31 - 1, rank], dtype=torch.int32)
+        self.byte = torch.tensor([200], dtype=torch.uint8)
+        self.half = torch.tensor([60000.0, 1.0 + rank], dtype=torch.float16)
+        self.seen = torch.tensor([rank == 0, False])
+
+    def compute(self):
+        return self.flag
+
+
+def _body_narrow_dtypes_follow_the_reference(rank):
+    """Sums of bool / narrow integer states are int64 counts (torch.sum of the stacked gather, metric.py:449-456),
+    half-precision means do not overflow on the way; the per-state protocol gives the same dtypes and values."""
+    m = _Narrow()
+    m.update(rank)
+    m.sync()
+    ref = _Narrow(dist_sync_fn=gather_all_tensors)
+    ref.update(rank)
+    ref.sync()
+    for name in ("flag", "small", "byte", "half", "seen"):
+        a, b = getattr(m, name), getattr(ref, name)
+        assert a.dtype == b.dtype, (name, a.dtype, b.dtype)
+        assert torch.equal(a, b), (name, a, b)
+    assert m.flag.tolist() == [2, 1, 0] and m.small.tolist() == [2 * (2**31 - 1), 1] and m.byte.tolist() == [400]
+    assert m.half.tolist() == [60000.0, 1.5] and m.seen.tolist() == [True, False]
+
+
 class _SS(DummyCounts):
     def compute(self):
         return self.tp

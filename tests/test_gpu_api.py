@@ -508,6 +508,43 @@ def test_fused_validation_raises_like_the_reference_and_restores_state(monkeypat
     F.binary_stat_scores(ps, tb)
 
 
+def test_multiclass_binned_curve_rejects_targets_outside_the_classes():
+    """The multiclass binned family reads the error word in the middle of its update (softmax decision); the
+    fused-validation finding next to it must survive until `finish` (reference: the `torch.unique` check in
+    precision_recall_curve.py:382-420 raises before any state is touched)."""
+    tm = _tm()
+    F = tm.functional
+    g = torch.Generator().manual_seed(8)
+    n, C = 4096, 5
+    p = torch.rand(n, C, generator=g).softmax(1).to(DEV)
+    logits = (torch.randn(n, C, generator=g) * 3).to(DEV)
+    t = torch.randint(0, C, (n,), generator=g).to(DEV)
+    bad = t.clone()
+    bad[::7] = 7
+    msg = "Detected more unique values in `target` than `num_classes`"
+    for scores in (p, logits):
+        with pytest.raises(RuntimeError, match=msg):
+            F.multiclass_auroc(scores, bad, C, thresholds=50)
+        with pytest.raises(RuntimeError, match=msg):
+            F.multiclass_precision_recall_curve(scores, bad, C, thresholds=50)
+        with pytest.raises(RuntimeError, match=msg):
+            F.multiclass_average_precision(scores, bad, C, thresholds=50)
+        for cls in (tm.classification.MulticlassPrecisionRecallCurve, tm.classification.MulticlassAUROC,
+                    tm.classification.MulticlassROC, tm.classification.MulticlassAveragePrecision):
+            m = cls(num_classes=C, thresholds=50).to(DEV)
+            m.update(scores, t)
+            before = m.confmat.clone()
+            with pytest.raises(RuntimeError, match=msg):
+                m.update(scores, bad)
+            assert torch.equal(m.confmat, before)
+            m.update(scores, t)
+            assert torch.equal(m.confmat, 2 * before)
+    # the same value is legal as ignore_index
+    a = F.multiclass_auroc(p, bad, C, thresholds=50, ignore_index=7)
+    b = F.multiclass_auroc(p, bad, C, thresholds=50, ignore_index=7, validate_args=False)
+    assert torch.equal(a, b)
+
+
 # ------------------------------------------------------------------ N2: consumers of the same update kernels
 _AVGS = ("micro", "macro", "weighted", "none")
 

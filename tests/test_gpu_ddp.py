@@ -1,5 +1,6 @@
-"""Cross-GPU synchronisation over NCCL (one process per GPU). Needs >= 2 GPUs; skipped otherwise.
-Run on a 2-GPU box with: gpurun --gpus 2 -- python -m pytest tests/test_gpu_ddp.py -m gpu -q"""
+"""Cross-GPU synchronisation over NCCL (one process per GPU), at every world size in {2, 4, 8} the box has GPUs
+for; skipped on a single-GPU box.  Shards are uneven, and from 4 ranks on one rank holds nothing at all.
+Run with: gpurun --gpus 2 -- python -m pytest tests/test_gpu_ddp.py -m gpu -q   (logs: profiles/r2_nccl_parity_*.log)"""
 import os
 import socket
 import sys
@@ -13,7 +14,7 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 pytestmark = pytest.mark.gpu
-WORLD = 2
+WORLDS = [2, 4, 8]
 
 
 def _free_port():
@@ -22,24 +23,26 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, port, body):
+def _worker(rank, world, port, body):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", rank=rank, world_size=WORLD, device_id=torch.device("cuda", rank))
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        globals()[body](rank)
+        globals()[body](rank, world)
         torch.cuda.synchronize()
     finally:
         dist.destroy_process_group()
 
 
-def _data(rank_or_all, n_per_rank):
+def _data(rank_or_all, n_per_rank, world):
     """Deterministic per-rank shards; rank None -> everything, in rank order."""
     out = []
-    for r in range(WORLD):
+    for r in range(world):
         g = torch.Generator().manual_seed(100 + r)
         n = n_per_rank + 17 * r  # uneven shards
+        if world > 2 and r == 1:
+            n = 0  # a rank that saw no data still takes part in every collective
         p = torch.rand(n, generator=g)
         t = (torch.rand(n, generator=g) < 0.3 + 0.4 * p).long()
         lp = torch.randint(0, 1000, (n,), generator=g)
@@ -50,15 +53,15 @@ def _data(rank_or_all, n_per_rank):
     return out[rank_or_all]
 
 
-def _body_sum_and_cat_states(rank):
+def _body_sum_and_cat_states(rank, world):
     import numpy as np
 
     import torchmetrics_b200 as tm
     from oracle import oracle_np as O
 
     dev = torch.device("cuda", rank)
-    p, t, lp, lt = (x.to(dev) for x in _data(rank, 50_000))
-    ap, at, alp, alt = _data(None, 50_000)
+    p, t, lp, lt = (x.to(dev) for x in _data(rank, 50_000, world))
+    ap, at, alp, alt = _data(None, 50_000, world)
 
     cm = tm.MulticlassConfusionMatrix(1000, validate_args=False).to(dev)
     cm.update(lp, lt)
@@ -81,15 +84,27 @@ def _body_sum_and_cat_states(rank):
     assert abs(val - float(O.binary_auroc_exact(ap.numpy(), at.numpy(), np.float64))) < 1e-6
     assert isinstance(exact.preds, list) and exact.preds[0].numel() == p.numel()  # un-synced again
 
+    # the exact curve itself after the gather: counts bit-exact against the oracle on the concatenated shards
+    prc = tm.BinaryPrecisionRecallCurve(thresholds=None).to(dev)
+    prc.update(p, t)
+    with prc.sync_context():
+        from torchmetrics_b200.functional.classification.precision_recall_curve import _binary_clf_curve
+        from torchmetrics_b200.utilities.data import dim_zero_cat
 
-def _body_multilabel_collection(rank):
+        fps, tps, thr = _binary_clf_curve(dim_zero_cat(prc.preds), dim_zero_cat(prc.target))
+    wf, wt, wthr = O.binary_clf_curve_exact(ap.numpy(), at.numpy())
+    assert np.array_equal(fps.cpu().numpy(), wf) and np.array_equal(tps.cpu().numpy(), wt)
+    assert np.array_equal(thr.cpu().numpy(), wthr)
+
+
+def _body_multilabel_collection(rank, world):
     import torchmetrics_b200 as tm
 
     dev = torch.device("cuda", rank)
     L = 100
     g = torch.Generator().manual_seed(5)
-    allp = torch.rand(2 * 4096, L, generator=g)
-    allt = torch.randint(0, 2, (2 * 4096, L), generator=g)
+    allp = torch.rand(world * 4096, L, generator=g)
+    allt = torch.randint(0, 2, (world * 4096, L), generator=g)
     mine = slice(rank * 4096, (rank + 1) * 4096)
     mc = tm.MetricCollection([tm.MultilabelStatScores(num_labels=L), tm.MultilabelPrecision(num_labels=L),
                               tm.MultilabelRecall(num_labels=L), tm.MultilabelF1Score(num_labels=L)]).to(dev)
@@ -102,8 +117,9 @@ def _body_multilabel_collection(rank):
     assert torch.allclose(out["MultilabelF1Score"], F.multilabel_f1_score(both_p, both_t, L), atol=1e-6)
 
 
+@pytest.mark.parametrize("world", WORLDS)
 @pytest.mark.parametrize("body", ["_body_sum_and_cat_states", "_body_multilabel_collection"])
-def test_nccl_sync(body):
-    if torch.cuda.device_count() < WORLD:
-        pytest.skip("needs 2 GPUs")
-    mp.spawn(_worker, args=(_free_port(), body), nprocs=WORLD, join=True)
+def test_nccl_sync(body, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    mp.spawn(_worker, args=(world, _free_port(), body), nprocs=world, join=True)

@@ -1,4 +1,4 @@
-"""Run one kernel a few times (for ncu). Usage: python tools/prof_one.py binned|confmat|stat [log2n]"""
+"""Run one kernel a few times (for ncu). Usage: python tools/prof_one.py binned|binned_multi|confmat|class_stats|stat|exact|exact_auroc [log2n]"""
 import os
 import sys
 
@@ -32,6 +32,27 @@ elif what == "stat":
     out = torch.zeros(4, L, dtype=torch.int64, device=DEV)
     for _ in range(4):
         N.stat_scores_update_(out, p, t, L, 0.5, None, N.PROB_AS_IS)
+elif what == "binned_multi":
+    L = 100
+    rows = n // 64
+    thr = torch.linspace(0, 1, 200, device=DEV)
+    preds = torch.rand(rows, L, device=DEV, generator=g)
+    tl = torch.randint(0, 2, (rows, L), device=DEV, generator=g)
+    st = torch.zeros(200, L, 2, 2, dtype=torch.int64, device=DEV)
+    for _ in range(4):
+        N.binned_curve_update_(st, preds, tl, thr, num_columns=L, prob_mode=N.PROB_AS_IS)
+elif what == "class_stats":
+    C = 1000
+    t = torch.randint(0, C, (n,), device=DEV, generator=g)
+    p = torch.randint(0, C, (n,), device=DEV, generator=g)
+    out = torch.zeros(4, C, dtype=torch.int64, device=DEV)
+    for _ in range(4):
+        N.class_stats_update_(out, p, t, C)
+elif what == "exact_auroc":
+    preds = torch.rand(n, device=DEV, generator=g)
+    target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
+    for _ in range(2):
+        N.exact_auroc_ap(preds, target, 1)
 elif what == "exact":
     preds = torch.rand(n, device=DEV, generator=g)
     target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()

@@ -218,8 +218,13 @@ def read_status_words(dev: torch.device) -> Tuple[int, int]:
 
 
 def read_status(dev: torch.device) -> int:
-    """Synchronising read-and-clear of the device status words; returns the error bits."""
-    return read_status_words(dev)[0]
+    """Synchronising read of the status words that returns and clears the error bits only: fused-validation
+    findings (word 1) stay where they are for the `FusedValidation.finish` that follows."""
+    s = scratch(dev)
+    err = int(s.status[:2].tolist()[0])
+    if err:
+        s.status[0].zero_()
+    return err
 
 
 def raise_on_status(dev: torch.device, num_classes: Optional[int] = None) -> None:
@@ -460,6 +465,11 @@ def binned_curve_update_static_(confmat: Tensor, preds: Tensor, target: Tensor, 
     The inputs must already be contiguous, aligned tensors of a kernel dtype, because this wrapper does not copy or
     cast (that would allocate); problems whose counters do not fit the array raise.  Calls on one device share the
     array, so do not let two of them overlap on the GPU.
+
+    One allocation remains on the Python side: the 32-byte status tensor this binding keeps per (device, stream) is
+    created by torch the first time ANY kernel wrapper runs on that stream.  Make one warm-up call (this function or
+    any other update) on the stream before entering the region that must not allocate; a C caller passes its own
+    `status` pointer and has no such step.
     """
     dev = require_cuda(confmat, preds, target, thresholds)
     T = thresholds.numel()

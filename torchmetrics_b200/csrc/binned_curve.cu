@@ -775,20 +775,35 @@ extern "C" size_t tmb_binned_curve_workspace_bytes(int num_thresholds, int64_t n
   return sizeof(BinnedWs) + (size_t)num_columns * 2 * ((size_t)num_thresholds + 1) * sizeof(u64);
 }
 
+// argument checks shared by the two entry points (nothing is enqueued before they pass)
+static int binned_check_args(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n_rows,
+                             int64_t num_columns, int target_is_class_index, const float* thresholds,
+                             int num_thresholds, int prob_mode, const int64_t* confmat, const int32_t* status) {
+  if (n_rows < 0 || num_columns < 1 || num_thresholds < 1 || num_thresholds > 65000 || !thresholds || !confmat ||
+      !status)
+    return TMB_ERR_ARG;
+  if (!is_float_dtype(preds_dtype) || !is_int_dtype(target_dtype)) return TMB_ERR_ARG;
+  if (prob_mode < TMB_PROB_AS_IS || prob_mode > TMB_PROB_CHECK) return TMB_ERR_ARG;
+  // multiclass scores are normalised by a row softmax, not a sigmoid: only AS_IS / CHECK make sense there
+  if (target_is_class_index && (prob_mode == TMB_PROB_AUTO || prob_mode == TMB_PROB_SIGMOID)) return TMB_ERR_ARG;
+  if (n_rows == 0) return TMB_OK;
+  if (!preds || !target) return TMB_ERR_ARG;
+  if (!aligned32(preds) || !aligned32(target)) return TMB_ERR_ALIGN;
+  return TMB_OK;
+}
+
 extern "C" int tmb_binned_curve_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
                                        int64_t n_rows, int64_t num_columns, int target_is_class_index,
                                        const float* thresholds, int num_thresholds, int has_ignore,
                                        int64_t ignore_index, int prob_mode, int64_t* confmat, void* workspace,
                                        size_t workspace_bytes, int32_t* status, void* stream) {
-  if (n_rows < 0 || num_columns < 1 || num_thresholds < 1 || num_thresholds > 65000 || !thresholds || !confmat ||
-      !workspace || !status)
+  if (!workspace || workspace_bytes < tmb_binned_curve_workspace_bytes(num_thresholds, num_columns))
     return TMB_ERR_ARG;
-  if (workspace_bytes < tmb_binned_curve_workspace_bytes(num_thresholds, num_columns)) return TMB_ERR_ARG;
+  const int rc = binned_check_args(preds, preds_dtype, target, target_dtype, n_rows, num_columns,
+                                   target_is_class_index, thresholds, num_thresholds, prob_mode, confmat, status);
+  if (rc != TMB_OK) return rc;
   if (n_rows == 0) return TMB_OK;
-  if (!preds || !target) return TMB_ERR_ARG;
-  if (!aligned32(preds) || !aligned32(target) || !aligned32(workspace)) return TMB_ERR_ALIGN;
-  // multiclass scores are normalised by a row softmax, not a sigmoid: only AS_IS / CHECK make sense there
-  if (target_is_class_index && (prob_mode == TMB_PROB_AUTO || prob_mode == TMB_PROB_SIGMOID)) return TMB_ERR_ARG;
+  if (!aligned32(workspace)) return TMB_ERR_ALIGN;
   BinnedParams P{};
   P.preds = preds;
   P.target = target;
@@ -845,9 +860,18 @@ extern "C" int tmb_binned_curve_update_static(const void* preds, int preds_dtype
     set_error_text(msg.c_str());
     return TMB_ERR_TOO_LARGE;
   }
+  // every check that can fail comes before the first thing put on the stream: a rejected call leaves the shared
+  // array as the previous call left it
+  const int rc = binned_check_args(preds, preds_dtype, target, target_dtype, n_rows, num_columns,
+                                   target_is_class_index, thresholds, num_thresholds, prob_mode, confmat, status);
+  if (rc != TMB_OK) return rc;
+  if (n_rows == 0) return TMB_OK;
   int dev = 0;
   TMB_CUDA_CHECK(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 64) return TMB_ERR_ARG;
+  if (dev < 0 || dev >= 64) {
+    set_error_text("tmb_binned_curve_update_static: only device ordinals 0..63 are supported");
+    return TMB_ERR_ARG;
+  }
   void* scratch = nullptr;
   {
     std::lock_guard<std::mutex> lk(g_static_mu);

@@ -99,15 +99,18 @@ class FusedValidation:
                 _native.raise_on_status(dev, num_classes)
             return
         err, val = _native.read_status_words(dev)
-        if val:
-            try:
+        if not (err or val):
+            return
+        try:
+            if val:
                 for chk in self.pending:
                     chk()
-            except Exception:
-                if undo is not None:
-                    undo()
-                raise
-        _native.raise_for_bits(err, num_classes)
+            _native.raise_for_bits(err, num_classes)
+        except Exception:
+            # the reference raises before it touches the state: take the batch out of the accumulator again
+            if undo is not None:
+                undo()
+            raise
 
 
 def _deferred(fn: Callable, t: Tensor, *args) -> bool:

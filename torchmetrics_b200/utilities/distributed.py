@@ -64,12 +64,30 @@ _DTYPE_CODES = [torch.float32, torch.float64, torch.float16, torch.bfloat16, tor
                 torch.int8, torch.uint8, torch.bool]
 
 
+_NARROW_INTS = (torch.bool, torch.uint8, torch.int8, torch.int16, torch.int32)
+_HALF_FLOATS = (torch.float16, torch.bfloat16)
+
+
+def _wire_dtype(op: str, dtype: torch.dtype) -> torch.dtype:
+    """dtype a state travels and is reduced in.  The reference stacks the gathered copies and calls torch.sum /
+    torch.mean on them (metric.py:449-456): sums of bool and narrow integer states come back as int64, and
+    half-precision means are accumulated in float32 before they are rounded back."""
+    if op == "sum" and dtype in _NARROW_INTS:
+        return torch.int64
+    if op == "mean" and dtype in _HALF_FLOATS:
+        return torch.float32
+    if dtype == torch.bool:
+        return torch.uint8  # max / min of flags
+    return dtype
+
+
 def fused_reduce(tensors: Sequence[Tuple[str, Tensor]], group: Optional[Any] = None) -> List[Tensor]:
     """All-reduce several tensors with as few collectives as possible.
 
-    `tensors` is a list of (op, tensor) with op in sum/mean/max/min. Tensors sharing (op class, dtype, device) are
-    packed into one flat arena, reduced in one all_reduce and returned as views of that arena (fresh memory: the
-    inputs are left untouched so `unsync` can restore them).
+    `tensors` is a list of (op, tensor) with op in sum/mean/max/min. Tensors sharing (op class, wire dtype, device)
+    are packed into one flat arena, reduced in one all_reduce and returned as views of that arena (fresh memory: the
+    inputs are left untouched so `unsync` can restore them).  Result dtypes are the reference's: int64 for sums of
+    bool / narrow integer states, the state's own dtype otherwise.
     """
     if group is None:
         group = dist.group.WORLD
@@ -77,13 +95,13 @@ def fused_reduce(tensors: Sequence[Tuple[str, Tensor]], group: Optional[Any] = N
     out: List[Optional[Tensor]] = [None] * len(tensors)
     buckets: Dict[Tuple[Any, torch.dtype, torch.device], List[int]] = {}
     for i, (op, t) in enumerate(tensors):
-        buckets.setdefault((_REDUCE_OPS[op], t.dtype, t.device), []).append(i)
-    for (rop, dtype, device), idxs in buckets.items():
-        flat = [tensors[i][1].detach().reshape(-1) for i in idxs]
-        arena = torch.cat(flat) if len(flat) > 1 else flat[0].clone()
-        as_bool = dtype == torch.bool
-        if as_bool:
-            arena = arena.to(torch.uint8)
+        buckets.setdefault((_REDUCE_OPS[op], _wire_dtype(op, t.dtype), t.device), []).append(i)
+    for (rop, wire, device), idxs in buckets.items():
+        if len(idxs) == 1:
+            t = tensors[idxs[0]][1].detach()
+            arena = t.reshape(-1).to(wire, copy=True)
+        else:
+            arena = torch.cat([tensors[i][1].detach().reshape(-1).to(wire) for i in idxs])
         dist.all_reduce(arena, op=rop, group=group)
         off = 0
         for i in idxs:
@@ -91,9 +109,9 @@ def fused_reduce(tensors: Sequence[Tuple[str, Tensor]], group: Optional[Any] = N
             piece = arena[off:off + t.numel()].view(t.shape)
             off += t.numel()
             if op == "mean":
-                piece = piece / world
-            if as_bool:
-                piece = piece.to(torch.bool)
+                piece = (piece / world).to(t.dtype)
+            elif op != "sum" and piece.dtype != t.dtype:
+                piece = piece.to(t.dtype)
             out[i] = piece
     return out  # type: ignore[return-value]
 
