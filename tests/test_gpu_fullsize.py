@@ -137,7 +137,9 @@ def _sorted_curve_restatement(preds, target):
     n = preds.numel()
     sp, order = torch.sort(preds, descending=True, stable=True)
     st = target[order]
-    ends = torch.cat([torch.nonzero(sp[1:] != sp[:-1]).flatten(), torch.tensor([n - 1], device=preds.device)])
+    # run boundaries as the reference finds them: `torch.where(preds[1:] - preds[:-1])` (inf - inf is NaN, i.e.
+    # non-zero, so equal infinities do NOT merge; -0.0 and 0.0 do)
+    ends = torch.cat([torch.nonzero((sp[1:] - sp[:-1]) != 0).flatten(), torch.tensor([n - 1], device=preds.device)])
     tps = torch.cumsum(st, 0)[ends]
     return ends + 1 - tps, tps, sp[ends]
 

@@ -14,7 +14,9 @@ from typing import Dict, Optional, Tuple
 import torch
 from torch import Tensor
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libtm_b200.so")
+# TMB_B200_LIB: development hook, load an alternative build of the same library (kernel tuning experiments)
+_LIB_PATH = os.environ.get("TMB_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc",
+                                                          "libtm_b200.so")
 
 TMB_OK = 0
 ERR_NAMES = {-1: "TMB_ERR_ARG", -2: "TMB_ERR_ALIGN", -3: "TMB_ERR_CUDA", -4: "TMB_ERR_TOO_LARGE"}

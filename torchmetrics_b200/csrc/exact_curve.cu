@@ -2,13 +2,15 @@
 // emits cumulative true / false positives at the last element of every run of equal scores
 // (contract in include/tm_b200.h; reference: functional/classification/precision_recall_curve.py:28-80).
 //
-// Sort: least-significant-digit radix sort, 4 passes of 8 bits over order-preserving 32-bit keys.  Each pass is
-//   tile histogram -> per-digit exclusive scan over tiles -> stable scatter.
-// The scatter ranks keys inside a 4096-key tile with warp match.any (no per-key shared-memory atomics), stages the
-// tile in shared memory in digit order and writes it out in coalesced runs.  Ties keep their input order, which the
+// Sort: least-significant-digit radix sort, 4 passes of 8 bits over order-preserving 32-bit keys, "onesweep" style:
+// the digit histograms of all four passes are counted once up front, and every pass is ONE kernel whose tiles
+// chain their digit counts through status words (decoupled look-back) instead of a histogram + scan + scatter
+// triple.  The first pass reads the caller's scores and targets directly.  Ties keep their input order, which the
 // curve does not depend on (counts are read only at run boundaries).
 // Scan: tile sums of (positives, run ends) -> exclusive scan of tile sums -> per-tile rescan that writes
 // (fps, tps, threshold) at the compacted position of every run end.  Counts are exact int64.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace tmb {
@@ -32,233 +34,225 @@ __device__ __forceinline__ float key_to_float(u32 k) {
   return __uint_as_float(b);
 }
 
-template <typename TT>
-__global__ void __launch_bounds__(256) k4_prepare(const float* __restrict__ preds, const TT* __restrict__ target,
-                                                  long long n, long long pos_label, u32* __restrict__ keys,
-                                                  unsigned char* __restrict__ labs) {
+// ---- sort ---------------------------------------------------------------------------------------------------
+// k4_digit_hist: one read of the scores -> the four 256-bin digit histograms of the whole input (the digit bases of
+// every pass are known before the first pass starts).
+__global__ void __launch_bounds__(512) k4_digit_hist(const float* __restrict__ preds, long long n,
+                                                     u32* __restrict__ ghist) {
+  __shared__ u32 h[4 * kRadix];
+  for (int i = threadIdx.x; i < 4 * kRadix; i += blockDim.x) h[i] = 0;
+  __syncthreads();
   const long long nvec = n >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nvec; g += stride) {
-    Vec4<float> p = load4(preds + 4 * g);
-    Vec4<TT> t = load4(target + 4 * g);
-    uint4 k;
-    k.x = desc_key(p.v[0]); k.y = desc_key(p.v[1]); k.z = desc_key(p.v[2]); k.w = desc_key(p.v[3]);
-    u32 l = (u32)(as_i64(t.v[0]) == pos_label) | ((u32)(as_i64(t.v[1]) == pos_label) << 8) |
-            ((u32)(as_i64(t.v[2]) == pos_label) << 16) | ((u32)(as_i64(t.v[3]) == pos_label) << 24);
-    reinterpret_cast<uint4*>(keys)[g] = k;
-    reinterpret_cast<u32*>(labs)[g] = l;
+    const Vec4<float> p = load4(preds + 4 * g);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const u32 k = desc_key(p.v[q]);
+      atomicAdd(&h[k & 0xff], 1u);
+      atomicAdd(&h[kRadix + ((k >> 8) & 0xff)], 1u);
+      atomicAdd(&h[2 * kRadix + ((k >> 16) & 0xff)], 1u);
+      atomicAdd(&h[3 * kRadix + (k >> 24)], 1u);
+    }
   }
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
-    long long i = (nvec << 2) + threadIdx.x;
-    keys[i] = desc_key(preds[i]);
-    labs[i] = (unsigned char)(as_i64(target[i]) == pos_label);
+    const u32 k = desc_key(preds[(nvec << 2) + threadIdx.x]);
+    atomicAdd(&h[k & 0xff], 1u);
+    atomicAdd(&h[kRadix + ((k >> 8) & 0xff)], 1u);
+    atomicAdd(&h[2 * kRadix + ((k >> 16) & 0xff)], 1u);
+    atomicAdd(&h[3 * kRadix + (k >> 24)], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4 * kRadix; i += blockDim.x) {
+    const u32 c = h[i];
+    if (c) atomicAdd(ghist + i, c);
   }
 }
 
-// table layout: [digit][tile], so the scan over tiles of one digit is contiguous
-__global__ void __launch_bounds__(kSortThreads) k4_tile_hist(const u32* __restrict__ keys, long long n, int shift,
-                                                             u32* __restrict__ table, int ntiles) {
-  __shared__ u32 h[kRadix];
-  h[threadIdx.x] = 0;
-  __syncthreads();
-  const long long base = (long long)blockIdx.x * kSortTile;
-  const long long left = n - base;
-  const int valid = left < kSortTile ? (int)left : kSortTile;
-  // the key buffers are padded to whole tiles, so 16-byte loads never leave them; validity is decided per key
-  const uint4* kv = reinterpret_cast<const uint4*>(keys + base);
-#pragma unroll
-  for (int r = 0; r < kSortItems / 4; ++r) {
-    const int v = r * kSortThreads + threadIdx.x;
-    const uint4 k = kv[v];
-    const int j = v * 4;
-    if (j + 3 < valid) {
-      atomicAdd(&h[(k.x >> shift) & 0xff], 1u);
-      atomicAdd(&h[(k.y >> shift) & 0xff], 1u);
-      atomicAdd(&h[(k.z >> shift) & 0xff], 1u);
-      atomicAdd(&h[(k.w >> shift) & 0xff], 1u);
-    } else {
-      if (j < valid) atomicAdd(&h[(k.x >> shift) & 0xff], 1u);
-      if (j + 1 < valid) atomicAdd(&h[(k.y >> shift) & 0xff], 1u);
-      if (j + 2 < valid) atomicAdd(&h[(k.z >> shift) & 0xff], 1u);
-    }
-  }
-  __syncthreads();
-  table[(long long)threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
-}
+// Tile status words of the decoupled look-back: {flag : 2 | count}.  flag 0 = nothing yet, 1 = the tile's own count
+// of the digit, 2 = the count summed over this and all earlier tiles.  32-bit words hold inputs below 2^30 keys,
+// 64-bit words the rest.
+template <typename ST>
+struct StatusWord;
+template <>
+struct StatusWord<u32> {
+  static constexpr int kFlagShift = 30;
+};
+template <>
+struct StatusWord<u64> {
+  static constexpr int kFlagShift = 62;
+};
 
-// one CTA per digit: exclusive scan of its row in place, row total to totals[digit]
-__global__ void __launch_bounds__(1024) k4_scan_rows(u32* __restrict__ table, int ntiles, u64* __restrict__ totals) {
-  __shared__ u64 warp_sums[32];
-  __shared__ u64 carry_s;
-  u32* row = table + (long long)blockIdx.x * ntiles;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry_s = 0;
-  __syncthreads();
-  for (int start = 0; start < ntiles; start += 1024) {
-    int i = start + threadIdx.x;
-    u64 v = i < ntiles ? row[i] : 0;
-    u64 x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      u64 y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) warp_sums[warp] = x;
-    __syncthreads();
-    if (warp == 0) {
-      u64 w = warp_sums[lane];
-      u64 ws = w;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        u64 y = __shfl_up_sync(0xffffffffu, ws, o);
-        if (lane >= o) ws += y;
-      }
-      warp_sums[lane] = ws - w;  // exclusive over warps
-    }
-    __syncthreads();
-    const u64 carry = carry_s;
-    u64 excl = carry + warp_sums[warp] + x - v;
-    // offsets inside one digit are < n < 2^32 (checked by the entry point); digit bases are 64-bit in `totals`
-    if (i < ntiles) row[i] = (u32)excl;
-    __syncthreads();
-    if (threadIdx.x == 1023) carry_s = carry + warp_sums[warp] + x;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) totals[blockIdx.x] = carry_s;
-}
-
-// stable scatter of one tile
-// four CTAs per SM (64 registers): 24 % -> 48 % occupancy, 171 -> 115 us per pass at 2^24 (3, 5, 6 CTAs: slower)
-__global__ void __launch_bounds__(kSortThreads, 4) k4_scatter(const u32* __restrict__ keys_in,
-                                                           const unsigned char* __restrict__ labs_in, long long n,
-                                                           int shift, const u32* __restrict__ table, int ntiles,
-                                                           const u64* __restrict__ totals, u32* __restrict__ keys_out,
-                                                           unsigned char* __restrict__ labs_out) {
+// One radix pass in ONE kernel ("onesweep"): a CTA takes the next tile of 4096 keys, ranks them by the pass's 8-bit
+// digit, publishes its 256 digit counts, adds up the counts of the tiles before it by walking their status words
+// backwards until it meets an inclusive one, and writes its keys to their final places of this pass.  Tile ids come
+// from a counter, so a tile only ever waits for tiles that are already running.
+//
+// Ranking is stable (least-significant-digit passes depend on it): warp w owns keys [512 w, 512 w + 512) of the tile
+// and takes them 32 per round.  In a round every lane ORs its lane bit into the warp's mask word of its digit
+// (one shared-memory atomic), reads the word back - that is the set of lanes holding the same digit - and ranks itself
+// by the lower lanes in it plus the digit's running count, which lives in the upper half of the same 64-bit entry;
+// the highest lane of each set stores the new count and clears the mask.
+// SHIFT == 0: the pass reads the caller's scores and targets and makes keys / labels on the fly.
+template <int SHIFT, typename TT, typename ST>
+#ifndef TMB_K4_MIN_CTAS
+#define TMB_K4_MIN_CTAS 4
+#endif
+__global__ void __launch_bounds__(kSortThreads, TMB_K4_MIN_CTAS)
+k4_onesweep(const u32* __restrict__ keys_in, const unsigned char* __restrict__ labs_in,
+            const float* __restrict__ preds, const TT* __restrict__ target, long long pos_label, long long n,
+            const u32* __restrict__ ghist, ST* __restrict__ status, u32* __restrict__ tile_counter,
+            u32* __restrict__ keys_out, unsigned char* __restrict__ labs_out) {
+  constexpr bool FIRST = SHIFT == 0;  // the pass over the lowest digit reads the caller's scores and targets
+  constexpr int shift = SHIFT;
+  constexpr int SH = StatusWord<ST>::kFlagShift;
+  constexpr ST kValMask = (ST(1) << SH) - 1;
   __shared__ __align__(16) u32 s_keys[kSortTile];
   __shared__ __align__(16) unsigned char s_labs[kSortTile];
-  __shared__ __align__(16) unsigned char s_labs_in[kSortTile];
-  __shared__ u32 warp_cnt[kSortWarps][kRadix];  // per-warp digit counts, then exclusive offsets in the tile
-  __shared__ u32 digit_start[kRadix];           // first position of each digit in the digit-ordered tile
-  __shared__ u32 s_dst[kRadix];                 // where position 0 of the staged tile would go for each digit's run
+  __shared__ u64 s_wtab[kSortWarps][kRadix];  // ranking: {count : 32 | lane mask : 32}; then low word = staging base
+  __shared__ u32 s_dst[kRadix];               // destination of position 0 of the staged tile, per digit run
+  __shared__ u32 s_wsum[kSortWarps], s_gsum[kSortWarps];
+  __shared__ u32 s_tile;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const long long base = (long long)blockIdx.x * kSortTile;
+  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&s_wtab[0][0])[i] = 0;
+  if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
+  __syncthreads();
+  const u32 tile = s_tile;
+  const long long base = (long long)tile * kSortTile;
   const long long left = n - base;
   const int valid = left < kSortTile ? (int)left : kSortTile;
-  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&warp_cnt[0][0])[i] = 0;
-  // thread d owns digit d: its global total and this tile's offset inside the digit are needed only at the end
-  const u64 my_total = totals[tid];
-  const u32 my_tile_off = table[(long long)tid * ntiles + blockIdx.x];
-  // the whole tile comes in with 16-byte loads issued back to back (the buffers are padded to whole tiles); the
-  // (warp, round, lane) order of the ranking below is then read from shared memory
+  const int wofs = warp * (32 * kSortItems) + lane;
+
+  u32 key[kSortItems];
+  u32 labbits = 0;
+  if constexpr (FIRST) {
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) {
+      const int j = wofs + r * 32;
+      float p = 0.f;
+      long long t = 0;
+      if (j < valid) {
+        p = __ldg(preds + base + j);
+        t = as_i64(__ldg(target + base + j));
+      }
+      key[r] = desc_key(p);
+      labbits |= (u32)(t == pos_label) << r;
+    }
+  } else {
+    // the key / label buffers are padded to whole tiles: loads past the end are harmless and never used
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) key[r] = keys_in[base + wofs + r * 32];
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) labbits |= (u32)(labs_in[base + wofs + r * 32] & 1u) << r;
+  }
+
+  u32 rank2[kSortItems / 2];  // two 16-bit ranks per register
   {
-    const uint4* kv = reinterpret_cast<const uint4*>(keys_in + base);
-    uint4 k[kSortItems / 4];
+    u64* wt = s_wtab[warp];
+    const u32 lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int r = 0; r < kSortItems / 4; ++r) k[r] = kv[r * kSortThreads + tid];
-    const u32 l = reinterpret_cast<const u32*>(labs_in + base)[tid];  // 4096 labels = 1024 words, 4 per thread below
-    u32 lrest[3];
-#pragma unroll
-    for (int r = 1; r < 4; ++r) lrest[r - 1] = reinterpret_cast<const u32*>(labs_in + base)[r * kSortThreads + tid];
-#pragma unroll
-    for (int r = 0; r < kSortItems / 4; ++r) reinterpret_cast<uint4*>(s_keys)[r * kSortThreads + tid] = k[r];
-    reinterpret_cast<u32*>(s_labs_in)[tid] = l;
-#pragma unroll
-    for (int r = 1; r < 4; ++r) reinterpret_cast<u32*>(s_labs_in)[r * kSortThreads + tid] = lrest[r - 1];
+    for (int r = 0; r < kSortItems; ++r) {
+      const bool in = wofs + r * 32 < valid;
+      const u32 d = (key[r] >> shift) & 0xffu;
+      if (in) atomicOr(reinterpret_cast<u32*>(wt + d), 1u << lane);
+      __syncwarp();
+      const u64 e = wt[d];
+      const u32 peers = (u32)e, before = (u32)(e >> 32);
+      const u32 rk = before + __popc(peers & lt);
+      if (r & 1) rank2[r >> 1] |= rk << 16;
+      else rank2[r >> 1] = rk;
+      __syncwarp();
+      if (in && (peers >> lane) == 1u) wt[d] = (u64)(before + __popc(peers)) << 32;  // highest lane of the set
+      __syncwarp();
+    }
   }
   __syncthreads();
 
-  // warp w owns the contiguous slice [w*512, (w+1)*512) of the tile, taken 32 keys per round: input order is
-  // (warp, round, lane), and ranks are handed out in exactly that order => stable
-  u32 key[kSortItems];
-  unsigned short rank[kSortItems];
-  const int wofs = warp * (32 * kSortItems) + lane;
-#pragma unroll
-  for (int r = 0; r < kSortItems; ++r) key[r] = s_keys[wofs + r * 32];  // s_keys is rewritten after the next barrier
-#pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    const bool in = wofs + r * 32 < valid;
-    const u32 d = (key[r] >> shift) & 0xff;
-    // lanes holding the same digit: eight ballots (one per digit bit) instead of match.any, whose cost grows with
-    // the number of distinct values in the warp (~30 of 256 here) and measured 10x slower than shared-memory atomics.
-    // Slots past the end of the input (last tile only) match nobody and take no rank.
-    unsigned peers = __ballot_sync(0xffffffffu, in);
-#pragma unroll
-    for (int bit = 0; bit < 8; ++bit) {
-      const bool one = (d >> bit) & 1u;
-      const unsigned vote = __ballot_sync(0xffffffffu, one);
-      peers &= one ? vote : ~vote;
-    }
-    if (!in) peers = 1u << lane;
-    u32 before = 0;
-    if (in) {
-      before = warp_cnt[warp][d];
-      rank[r] = (unsigned short)(before + __popc(peers & ((1u << lane) - 1)));
-    }
-    __syncwarp();
-    if (in && lane == __ffs(peers) - 1) warp_cnt[warp][d] = before + __popc(peers);
-    __syncwarp();
-  }
-  __syncthreads();
-  // per digit: exclusive prefix over warps, and the digit's total in this tile
+  // thread d <-> digit d
+  u32 my_cnt, my_start, my_gbase;
   {
-    const int d = tid;  // 256 threads <-> 256 digits
+    const int d = tid;
     u32 run = 0;
 #pragma unroll
-    for (int w = 0; w < kSortWarps; ++w) {
-      u32 c = warp_cnt[w][d];
-      warp_cnt[w][d] = run;
-      run += c;
-    }
-    // exclusive scan of the digit totals across the CTA
-    u32 x = run;
+    for (int w = 0; w < kSortWarps; ++w) run += (u32)(s_wtab[w][d] >> 32);
+    my_cnt = run;
+    // the first tile has nothing before it: its own counts are inclusive already
+    *reinterpret_cast<volatile ST*>(status + (size_t)tile * kRadix + d) = (ST(tile == 0 ? 2 : 1) << SH) | (ST)run;
+    // exclusive scans over the digits: this tile's counts (start of the digit's run in the staged tile) and the
+    // whole input's counts (start of the digit's region in the output)
+    const u32 g = ghist[d];
+    u32 x = run, gx = g;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      u32 y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
+      const u32 y = __shfl_up_sync(0xffffffffu, x, o), gy = __shfl_up_sync(0xffffffffu, gx, o);
+      if (lane >= o) {
+        x += y;
+        gx += gy;
+      }
     }
-    // ... and of the global digit totals: base of digit d in the output (replaces a separate 1-CTA scan kernel)
-    u64 gx = my_total;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const u64 gy = __shfl_up_sync(0xffffffffu, gx, o);
-      if (lane >= o) gx += gy;
-    }
-    __shared__ u32 wsum[kSortWarps];
-    __shared__ u64 gsum[kSortWarps];
     if (lane == 31) {
-      wsum[warp] = x;
-      gsum[warp] = gx;
+      s_wsum[warp] = x;
+      s_gsum[warp] = gx;
     }
     __syncthreads();
-    u32 add = 0;
-    u64 gadd = 0;
+    u32 add = 0, gadd = 0;
     for (int w = 0; w < warp; ++w) {
-      add += wsum[w];
-      gadd += gsum[w];
+      add += s_wsum[w];
+      gadd += s_gsum[w];
     }
-    digit_start[d] = add + x - run;
-    // destination of digit d's run: global digit base + this tile's offset inside the digit - the run's start in the
-    // staged tile; < 2^32 once a position is added, so 32-bit wrap-around arithmetic is exact
-    s_dst[d] = (u32)(gadd + gx - my_total) + my_tile_off - (add + x - run);
-  }
-  __syncthreads();
-  // stage the tile in digit order
+    my_start = add + x - run;
+    my_gbase = gadd + gx - g;
+    u32 at = my_start;  // staging base of (warp, digit): the digit's run start + the counts of the warps before
 #pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    const int j = wofs + r * 32;
-    if (j < valid) {
-      const u32 d = (key[r] >> shift) & 0xff;
-      const u32 pos = digit_start[d] + warp_cnt[warp][d] + rank[r];
-      s_keys[pos] = key[r];
-      s_labs[pos] = s_labs_in[j];
+    for (int w = 0; w < kSortWarps; ++w) {
+      const u32 c = (u32)(s_wtab[w][d] >> 32);
+      *reinterpret_cast<u32*>(&s_wtab[w][d]) = at;
+      at += c;
     }
   }
   __syncthreads();
-  // coalesced write-out: consecutive threads hold consecutive positions of the same digit run
+
+  // stage the tile in digit order
+  {
+    const u64* wt = s_wtab[warp];
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) {
+      if (wofs + r * 32 < valid) {
+        const u32 d = (key[r] >> shift) & 0xffu;
+        const u32 rk = (r & 1) ? (rank2[r >> 1] >> 16) : (rank2[r >> 1] & 0xffffu);
+        const u32 pos = *reinterpret_cast<const u32*>(wt + d) + rk;
+        s_keys[pos] = key[r];
+        s_labs[pos] = (unsigned char)((labbits >> r) & 1u);
+      }
+    }
+  }
+
+  // look back over the earlier tiles' counts of digit d
+  {
+    const int d = tid;
+    ST excl = 0;
+    if (tile > 0) {
+      long long j = (long long)tile - 1;
+      while (true) {
+        const volatile ST* w = reinterpret_cast<const volatile ST*>(status + (size_t)j * kRadix + d);
+        ST sw = *w;
+        while ((sw >> SH) == 0) sw = *w;
+        excl += sw & kValMask;
+        if ((sw >> SH) == 2) break;
+        --j;
+      }
+      *reinterpret_cast<volatile ST*>(status + (size_t)tile * kRadix + d) = (ST(2) << SH) | (excl + (ST)my_cnt);
+    }
+    // destinations stay below 2^32 (checked by the entry point), so 32-bit wrap-around arithmetic is exact
+    s_dst[d] = my_gbase + (u32)excl - my_start;
+  }
+  __syncthreads();
+
+  // coalesced write-out: consecutive threads hold consecutive positions of one digit run
 #pragma unroll 4
   for (int pos = tid; pos < valid; pos += kSortThreads) {
     const u32 k = s_keys[pos];
-    const u32 dst = s_dst[(k >> shift) & 0xff] + (u32)pos;
+    const u32 dst = s_dst[(k >> shift) & 0xffu] + (u32)pos;
     keys_out[dst] = k;
     labs_out[dst] = s_labs[pos];
   }
@@ -701,9 +695,11 @@ __global__ void __launch_bounds__(1024) k4_sum_tiles(const double* __restrict__ 
 struct K4Ws {
   u32* keys[2];
   unsigned char* labs[2];
-  u32* table;
-  u64* totals;
-  u64* bases;
+  unsigned char* zeroed;   // status words of the four passes, digit histograms, tile counters: cleared per call
+  size_t zeroed_bytes;
+  void* status;            // [4][ntiles][256] status words (u32 or u64)
+  u32* ghist;              // [4][256]
+  u32* counters;           // [4] + padding
   u64* tile_pos;
   u64* tile_ends;
   u64* tile_last_idx1;
@@ -713,6 +709,15 @@ struct K4Ws {
 };
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// inputs of 2^30 keys and more need 64-bit status words; TMB_K4_WIDE_STATUS=1 forces them (tests)
+static bool k4_wide_status(long long n) {
+  static const bool forced = [] {
+    const char* e = getenv("TMB_K4_WIDE_STATUS");
+    return e && e[0] == '1';
+  }();
+  return forced || n >= (1LL << 30);
+}
 
 static size_t k4_layout(long long n, unsigned char* base, K4Ws* ws) {
   const long long ntiles = (n + kSortTile - 1) / kSortTile;
@@ -724,12 +729,14 @@ static size_t k4_layout(long long n, unsigned char* base, K4Ws* ws) {
     return p;
   };
   u32* k0 = (u32*)take(npad * 4);
-  u32* k1 = (u32*)take(npad * 4);
+  u32* k1 = (u32*)take(npad * 4 + 256);  // + the one key the scan kernels read past the last tile
   unsigned char* l0 = take(npad);
   unsigned char* l1 = take(npad);
-  u32* table = (u32*)take((size_t)kRadix * ntiles * 4);
-  u64* totals = (u64*)take(kRadix * 8);
-  u64* bases = (u64*)take(kRadix * 8);
+  const size_t zero_begin = off;
+  void* status = take((size_t)4 * ntiles * kRadix * (k4_wide_status(n) ? 8 : 4));
+  u32* ghist = (u32*)take(4 * kRadix * 4);
+  u32* counters = (u32*)take(256);
+  const size_t zero_end = off;
   u64* tp = (u64*)take((size_t)ntiles * 8);
   u64* te = (u64*)take((size_t)ntiles * 8);
   u64* tli = (u64*)take((size_t)ntiles * 8);
@@ -739,7 +746,8 @@ static size_t k4_layout(long long n, unsigned char* base, K4Ws* ws) {
   if (ws) {
     ws->tile_last_idx1 = tli; ws->tile_last_tp = tlt; ws->tile_auc = tau; ws->tile_ap = tap;
     ws->keys[0] = k0; ws->keys[1] = k1; ws->labs[0] = l0; ws->labs[1] = l1;
-    ws->table = table; ws->totals = totals; ws->bases = bases; ws->tile_pos = tp; ws->tile_ends = te;
+    ws->zeroed = base + zero_begin; ws->zeroed_bytes = zero_end - zero_begin;
+    ws->status = status; ws->ghist = ghist; ws->counters = counters; ws->tile_pos = tp; ws->tile_ends = te;
   }
   return off;
 }
@@ -753,28 +761,41 @@ extern "C" size_t tmb_exact_curve_workspace_bytes(int64_t n) {
   return k4_layout(n, nullptr, nullptr);
 }
 
-// prepare + 4 radix passes; returns the index of the buffer pair that holds the sorted keys / labels
+template <typename TT, typename ST>
+static void k4_launch_passes(const float* preds, const TT* target, long long n, long long pos_label, const K4Ws& ws,
+                             int ntiles, cudaStream_t st) {
+  ST* status = (ST*)ws.status;
+  const size_t per_pass = (size_t)ntiles * kRadix;
+  using U8 = unsigned char;
+  k4_onesweep<0, TT, ST><<<ntiles, kSortThreads, 0, st>>>(nullptr, nullptr, preds, target, pos_label, n, ws.ghist,
+                                                          status, ws.counters, ws.keys[0], ws.labs[0]);
+  k4_onesweep<8, U8, ST><<<ntiles, kSortThreads, 0, st>>>(ws.keys[0], ws.labs[0], nullptr, nullptr, 0, n,
+                                                          ws.ghist + kRadix, status + per_pass, ws.counters + 1,
+                                                          ws.keys[1], ws.labs[1]);
+  k4_onesweep<16, U8, ST><<<ntiles, kSortThreads, 0, st>>>(ws.keys[1], ws.labs[1], nullptr, nullptr, 0, n,
+                                                           ws.ghist + 2 * kRadix, status + 2 * per_pass,
+                                                           ws.counters + 2, ws.keys[0], ws.labs[0]);
+  k4_onesweep<24, U8, ST><<<ntiles, kSortThreads, 0, st>>>(ws.keys[0], ws.labs[0], nullptr, nullptr, 0, n,
+                                                           ws.ghist + 3 * kRadix, status + 3 * per_pass,
+                                                           ws.counters + 3, ws.keys[1], ws.labs[1]);
+}
+
+// digit histograms + 4 onesweep passes; the sorted keys / labels end up in buffer pair 1
 static int k4_sort(const float* preds, const void* target, int target_dtype, long long n, long long pos_label,
                    const K4Ws& ws, int ntiles, cudaStream_t st, int* cur_out) {
+  TMB_CUDA_CHECK(cudaMemsetAsync(ws.zeroed, 0, ws.zeroed_bytes, st));
   {
-    long long nvec = n >> 2;
-    long long want = (nvec + 255) / 256;
-    long long cap = (long long)sm_count() * 8;
-    int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
-    TMB_DISPATCH_INT(target_dtype, TT, {
-      k4_prepare<TT><<<grid, 256, 0, st>>>(preds, (const TT*)target, n, pos_label, ws.keys[0], ws.labs[0]);
-    })
+    const long long want = ((n >> 2) + 511) / 512;
+    const long long cap = (long long)sm_count() * 4;
+    const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
+    k4_digit_hist<<<grid, 512, 0, st>>>(preds, n, ws.ghist);
   }
-  int cur = 0;
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 8 * pass;
-    k4_tile_hist<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], n, shift, ws.table, ntiles);
-    k4_scan_rows<<<kRadix, 1024, 0, st>>>(ws.table, ntiles, ws.totals);
-    k4_scatter<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], ws.labs[cur], n, shift, ws.table, ntiles, ws.totals,
-                                                ws.keys[cur ^ 1], ws.labs[cur ^ 1]);
-    cur ^= 1;
-  }
-  *cur_out = cur;
+  const bool wide = k4_wide_status(n);
+  TMB_DISPATCH_INT(target_dtype, TT, {
+    if (wide) k4_launch_passes<TT, u64>(preds, (const TT*)target, n, pos_label, ws, ntiles, st);
+    else k4_launch_passes<TT, u32>(preds, (const TT*)target, n, pos_label, ws, ntiles, st);
+  })
+  *cur_out = 1;
   return TMB_OK;
 }
 
