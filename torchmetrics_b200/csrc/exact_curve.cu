@@ -83,51 +83,92 @@ struct StatusWord<u64> {
   static constexpr int kFlagShift = 62;
 };
 
+// status words travel through the L2 with GPU-scope relaxed accesses (a word carries its own flag, so no fence)
+#ifdef TMB_K4_VOLATILE_STATUS
+__device__ __forceinline__ u32 ld_status(const u32* p) { return *reinterpret_cast<const volatile u32*>(p); }
+__device__ __forceinline__ u64 ld_status(const u64* p) { return *reinterpret_cast<const volatile u64*>(p); }
+#else
+__device__ __forceinline__ u32 ld_status(const u32* p) {
+  u32 v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ u64 ld_status(const u64* p) {
+  u64 v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+#endif
+__device__ __forceinline__ void st_status(u32* p, u32 v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_status(u64* p, u64 v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+#ifndef TMB_K4_WINDOW
+#define TMB_K4_WINDOW 1  // status words of this many earlier tiles are fetched per look-back step
+#endif
+
 // One radix pass in ONE kernel ("onesweep"): a CTA takes the next tile of 4096 keys, ranks them by the pass's 8-bit
 // digit, publishes its 256 digit counts, adds up the counts of the tiles before it by walking their status words
 // backwards until it meets an inclusive one, and writes its keys to their final places of this pass.  Tile ids come
 // from a counter, so a tile only ever waits for tiles that are already running.
 //
-// Ranking is stable (least-significant-digit passes depend on it): warp w owns keys [512 w, 512 w + 512) of the tile
-// and takes them 32 per round.  In a round every lane ORs its lane bit into the warp's mask word of its digit
-// (one shared-memory atomic), reads the word back - that is the set of lanes holding the same digit - and ranks itself
-// by the lower lanes in it plus the digit's running count, which lives in the upper half of the same 64-bit entry;
-// the highest lane of each set stores the new count and clears the mask.
+// The kernel is bound by the shared-memory / load-store pipe (one wavefront per clock and SM), not by HBM, so the
+// design spends ALU instructions to save shared-memory traffic:
+//  * Ranking is stable (least-significant-digit passes depend on it): warp w owns keys [512 w, 512 w + 512) of the
+//    tile and takes them 32 per round.  The lanes holding the same digit are found with eight ballots (one per
+//    digit bit, no memory traffic); a key's rank is the warp's running count of its digit plus the lower lanes of
+//    its set, and the highest lane of the set stores the new count.  (A shared-memory formulation - OR the lane
+//    bit into a mask word per digit, read it back - measured 15 wavefronts per round against 6 for this one.)
+//  * The tile is staged in digit order with the label riding in the key: inside a digit run the lowest digit bit
+//    is known from the position, so that bit carries the label while the key sits in shared memory.
 // SHIFT == 0: the pass reads the caller's scores and targets and makes keys / labels on the fly.
-template <int SHIFT, typename TT, typename ST>
+#ifndef TMB_K4_OS_THREADS
+#define TMB_K4_OS_THREADS 256
+#endif
 #ifndef TMB_K4_MIN_CTAS
 #define TMB_K4_MIN_CTAS 4
 #endif
-__global__ void __launch_bounds__(kSortThreads, TMB_K4_MIN_CTAS)
+constexpr int kOsThreads = TMB_K4_OS_THREADS;       // threads of a onesweep CTA (at least one per digit)
+constexpr int kOsWarps = kOsThreads / 32;
+constexpr int kOsItems = kSortTile / kOsThreads;    // keys per thread
+static_assert(kOsThreads >= kRadix && kOsItems % 2 == 0 && (kOsWarps * kRadix / 4) % kOsThreads == 0, "geometry");
+template <int SHIFT, typename TT, typename ST>
+__global__ void __launch_bounds__(kOsThreads, TMB_K4_MIN_CTAS)
 k4_onesweep(const u32* __restrict__ keys_in, const unsigned char* __restrict__ labs_in,
             const float* __restrict__ preds, const TT* __restrict__ target, long long pos_label, long long n,
             const u32* __restrict__ ghist, ST* __restrict__ status, u32* __restrict__ tile_counter,
             u32* __restrict__ keys_out, unsigned char* __restrict__ labs_out) {
   constexpr bool FIRST = SHIFT == 0;  // the pass over the lowest digit reads the caller's scores and targets
-  constexpr int shift = SHIFT;
   constexpr int SH = StatusWord<ST>::kFlagShift;
   constexpr ST kValMask = (ST(1) << SH) - 1;
   __shared__ __align__(16) u32 s_keys[kSortTile];
-  __shared__ __align__(16) unsigned char s_labs[kSortTile];
-  __shared__ u64 s_wtab[kSortWarps][kRadix];  // ranking: {count : 32 | lane mask : 32}; then low word = staging base
-  __shared__ u32 s_dst[kRadix];               // destination of position 0 of the staged tile, per digit run
-  __shared__ u32 s_wsum[kSortWarps], s_gsum[kSortWarps];
+  __shared__ __align__(16) u32 s_cnt[kOsWarps][kRadix];  // per-warp digit counts, then staging bases
+  __shared__ u32 s_start[kRadix];                          // first position of each digit run in the staged tile
+  __shared__ u32 s_dst[kRadix];                            // destination of staged position 0, per digit run
+  __shared__ u32 s_wsum[kRadix / 32], s_gsum[kRadix / 32];
   __shared__ u32 s_tile;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&s_wtab[0][0])[i] = 0;
+  {
+    uint4* z = reinterpret_cast<uint4*>(&s_cnt[0][0]);
+#pragma unroll
+    for (int i = 0; i < kOsWarps * kRadix / 4 / kOsThreads; ++i) z[i * kOsThreads + tid] = make_uint4(0, 0, 0, 0);
+  }
   if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
   __syncthreads();
   const u32 tile = s_tile;
   const long long base = (long long)tile * kSortTile;
   const long long left = n - base;
   const int valid = left < kSortTile ? (int)left : kSortTile;
-  const int wofs = warp * (32 * kSortItems) + lane;
+  const int wofs = warp * (32 * kOsItems) + lane;
 
-  u32 key[kSortItems];
+  u32 key[kOsItems];
   u32 labbits = 0;
   if constexpr (FIRST) {
 #pragma unroll
-    for (int r = 0; r < kSortItems; ++r) {
+    for (int r = 0; r < kOsItems; ++r) {
       const int j = wofs + r * 32;
       float p = 0.f;
       long long t = 0;
@@ -141,47 +182,54 @@ k4_onesweep(const u32* __restrict__ keys_in, const unsigned char* __restrict__ l
   } else {
     // the key / label buffers are padded to whole tiles: loads past the end are harmless and never used
 #pragma unroll
-    for (int r = 0; r < kSortItems; ++r) key[r] = keys_in[base + wofs + r * 32];
+    for (int r = 0; r < kOsItems; ++r) key[r] = keys_in[base + wofs + r * 32];
 #pragma unroll
-    for (int r = 0; r < kSortItems; ++r) labbits |= (u32)(labs_in[base + wofs + r * 32] & 1u) << r;
+    for (int r = 0; r < kOsItems; ++r) labbits |= (u32)(labs_in[base + wofs + r * 32] & 1u) << r;
   }
 
-  u32 rank2[kSortItems / 2];  // two 16-bit ranks per register
+  u32 rank2[kOsItems / 2];  // two 16-bit ranks per register
   {
-    u64* wt = s_wtab[warp];
+    u32* cnt = s_cnt[warp];
     const u32 lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int r = 0; r < kSortItems; ++r) {
+    for (int r = 0; r < kOsItems; ++r) {
       const bool in = wofs + r * 32 < valid;
-      const u32 d = (key[r] >> shift) & 0xffu;
-      if (in) atomicOr(reinterpret_cast<u32*>(wt + d), 1u << lane);
-      __syncwarp();
-      const u64 e = wt[d];
-      const u32 peers = (u32)e, before = (u32)(e >> 32);
+      const u32 d = (key[r] >> SHIFT) & 0xffu;
+      u32 peers = __ballot_sync(0xffffffffu, in);
+#pragma unroll
+      for (int bit = 0; bit < 8; ++bit) {
+        const bool one = (d >> bit) & 1u;
+        const u32 vote = __ballot_sync(0xffffffffu, one);
+        peers &= one ? vote : ~vote;
+      }
+      const u32 before = cnt[d];
       const u32 rk = before + __popc(peers & lt);
       if (r & 1) rank2[r >> 1] |= rk << 16;
       else rank2[r >> 1] = rk;
       __syncwarp();
-      if (in && (peers >> lane) == 1u) wt[d] = (u64)(before + __popc(peers)) << 32;  // highest lane of the set
+      if (in && (peers >> lane) == 1u) cnt[d] = before + __popc(peers);  // highest lane of the set
       __syncwarp();
     }
   }
   __syncthreads();
 
-  // thread d <-> digit d
-  u32 my_cnt, my_start, my_gbase;
-  {
+  // thread d <-> digit d (the first 256 threads)
+  const bool digit_thread = tid < kRadix;
+  u32 my_cnt = 0, my_start = 0, my_gbase = 0;
+  u32 x = 0, gx = 0, g = 0;
+  if (digit_thread) {
     const int d = tid;
     u32 run = 0;
 #pragma unroll
-    for (int w = 0; w < kSortWarps; ++w) run += (u32)(s_wtab[w][d] >> 32);
+    for (int w = 0; w < kOsWarps; ++w) run += s_cnt[w][d];
     my_cnt = run;
     // the first tile has nothing before it: its own counts are inclusive already
-    *reinterpret_cast<volatile ST*>(status + (size_t)tile * kRadix + d) = (ST(tile == 0 ? 2 : 1) << SH) | (ST)run;
+    st_status(status + (size_t)tile * kRadix + d, (ST(tile == 0 ? 2 : 1) << SH) | (ST)run);
     // exclusive scans over the digits: this tile's counts (start of the digit's run in the staged tile) and the
     // whole input's counts (start of the digit's region in the output)
-    const u32 g = ghist[d];
-    u32 x = run, gx = g;
+    g = ghist[d];
+    x = run;
+    gx = g;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const u32 y = __shfl_up_sync(0xffffffffu, x, o), gy = __shfl_up_sync(0xffffffffu, gx, o);
@@ -194,67 +242,91 @@ k4_onesweep(const u32* __restrict__ keys_in, const unsigned char* __restrict__ l
       s_wsum[warp] = x;
       s_gsum[warp] = gx;
     }
-    __syncthreads();
+  }
+  __syncthreads();
+  if (digit_thread) {
+    const int d = tid;
     u32 add = 0, gadd = 0;
     for (int w = 0; w < warp; ++w) {
       add += s_wsum[w];
       gadd += s_gsum[w];
     }
-    my_start = add + x - run;
+    my_start = add + x - my_cnt;
     my_gbase = gadd + gx - g;
+    s_start[d] = my_start;
     u32 at = my_start;  // staging base of (warp, digit): the digit's run start + the counts of the warps before
 #pragma unroll
-    for (int w = 0; w < kSortWarps; ++w) {
-      const u32 c = (u32)(s_wtab[w][d] >> 32);
-      *reinterpret_cast<u32*>(&s_wtab[w][d]) = at;
+    for (int w = 0; w < kOsWarps; ++w) {
+      const u32 c = s_cnt[w][d];
+      s_cnt[w][d] = at;
       at += c;
     }
   }
   __syncthreads();
 
-  // stage the tile in digit order
+  // stage the tile in digit order; the lowest digit bit of the staged word is the label
   {
-    const u64* wt = s_wtab[warp];
+    const u32* bases = s_cnt[warp];
 #pragma unroll
-    for (int r = 0; r < kSortItems; ++r) {
+    for (int r = 0; r < kOsItems; ++r) {
       if (wofs + r * 32 < valid) {
-        const u32 d = (key[r] >> shift) & 0xffu;
+        const u32 d = (key[r] >> SHIFT) & 0xffu;
         const u32 rk = (r & 1) ? (rank2[r >> 1] >> 16) : (rank2[r >> 1] & 0xffffu);
-        const u32 pos = *reinterpret_cast<const u32*>(wt + d) + rk;
-        s_keys[pos] = key[r];
-        s_labs[pos] = (unsigned char)((labbits >> r) & 1u);
+        s_keys[bases[d] + rk] = (key[r] & ~(1u << SHIFT)) | (((labbits >> r) & 1u) << SHIFT);
       }
     }
   }
 
   // look back over the earlier tiles' counts of digit d
-  {
+  if (digit_thread) {
     const int d = tid;
     ST excl = 0;
+#ifdef TMB_K4_EXPERIMENT_NO_LOOKBACK
+    if (false) {
+#else
     if (tile > 0) {
-      long long j = (long long)tile - 1;
-      while (true) {
-        const volatile ST* w = reinterpret_cast<const volatile ST*>(status + (size_t)j * kRadix + d);
-        ST sw = *w;
-        while ((sw >> SH) == 0) sw = *w;
-        excl += sw & kValMask;
-        if ((sw >> SH) == 2) break;
-        --j;
+#endif
+      // The tiles of a wave reach this point together, so the nearest inclusive word is often several tiles back:
+      // fetch a window of words per step (independent loads, one L2 round trip) and consume the ready prefix.
+      long long j = (long long)tile - 1;  // nearest tile not yet added
+      bool done = false;
+      while (!done) {
+        ST sw[TMB_K4_WINDOW];
+#pragma unroll
+        for (int q = 0; q < TMB_K4_WINDOW; ++q)
+          sw[q] = j - q >= 0 ? ld_status(status + (size_t)(j - q) * kRadix + d) : (ST(2) << SH);
+        int used = 0;
+#pragma unroll
+        for (int q = 0; q < TMB_K4_WINDOW; ++q) {
+          const ST f = sw[q] >> SH;
+          if (!done && used == q && f != 0) {
+            excl += sw[q] & kValMask;
+            used = q + 1;
+            done = f == 2;
+          }
+        }
+        j -= used;
+#ifdef TMB_K4_BACKOFF_NS
+        if (used == 0) __nanosleep(TMB_K4_BACKOFF_NS);
+#endif
       }
-      *reinterpret_cast<volatile ST*>(status + (size_t)tile * kRadix + d) = (ST(2) << SH) | (excl + (ST)my_cnt);
+      st_status(status + (size_t)tile * kRadix + d, (ST(2) << SH) | (excl + (ST)my_cnt));
     }
     // destinations stay below 2^32 (checked by the entry point), so 32-bit wrap-around arithmetic is exact
     s_dst[d] = my_gbase + (u32)excl - my_start;
   }
   __syncthreads();
 
-  // coalesced write-out: consecutive threads hold consecutive positions of one digit run
+  // coalesced write-out: consecutive threads hold consecutive positions of one digit run.  The digit of a staged
+  // word: its upper seven digit bits, and the lowest from which of the two candidate runs the position lies in.
 #pragma unroll 4
-  for (int pos = tid; pos < valid; pos += kSortThreads) {
-    const u32 k = s_keys[pos];
-    const u32 dst = s_dst[(k >> shift) & 0xffu] + (u32)pos;
-    keys_out[dst] = k;
-    labs_out[dst] = s_labs[pos];
+  for (int pos = tid; pos < valid; pos += kOsThreads) {
+    const u32 w = s_keys[pos];
+    const u32 dodd = ((w >> SHIFT) & 0xfeu) | 1u;
+    const u32 low = (u32)pos >= s_start[dodd] ? 1u : 0u;
+    const u32 dst = s_dst[dodd - 1u + low] + (u32)pos;
+    keys_out[dst] = (w & ~(1u << SHIFT)) | (low << SHIFT);
+    labs_out[dst] = (unsigned char)((w >> SHIFT) & 1u);
   }
 }
 
@@ -767,15 +839,15 @@ static void k4_launch_passes(const float* preds, const TT* target, long long n, 
   ST* status = (ST*)ws.status;
   const size_t per_pass = (size_t)ntiles * kRadix;
   using U8 = unsigned char;
-  k4_onesweep<0, TT, ST><<<ntiles, kSortThreads, 0, st>>>(nullptr, nullptr, preds, target, pos_label, n, ws.ghist,
+  k4_onesweep<0, TT, ST><<<ntiles, kOsThreads, 0, st>>>(nullptr, nullptr, preds, target, pos_label, n, ws.ghist,
                                                           status, ws.counters, ws.keys[0], ws.labs[0]);
-  k4_onesweep<8, U8, ST><<<ntiles, kSortThreads, 0, st>>>(ws.keys[0], ws.labs[0], nullptr, nullptr, 0, n,
+  k4_onesweep<8, U8, ST><<<ntiles, kOsThreads, 0, st>>>(ws.keys[0], ws.labs[0], nullptr, nullptr, 0, n,
                                                           ws.ghist + kRadix, status + per_pass, ws.counters + 1,
                                                           ws.keys[1], ws.labs[1]);
-  k4_onesweep<16, U8, ST><<<ntiles, kSortThreads, 0, st>>>(ws.keys[1], ws.labs[1], nullptr, nullptr, 0, n,
+  k4_onesweep<16, U8, ST><<<ntiles, kOsThreads, 0, st>>>(ws.keys[1], ws.labs[1], nullptr, nullptr, 0, n,
                                                            ws.ghist + 2 * kRadix, status + 2 * per_pass,
                                                            ws.counters + 2, ws.keys[0], ws.labs[0]);
-  k4_onesweep<24, U8, ST><<<ntiles, kSortThreads, 0, st>>>(ws.keys[0], ws.labs[0], nullptr, nullptr, 0, n,
+  k4_onesweep<24, U8, ST><<<ntiles, kOsThreads, 0, st>>>(ws.keys[0], ws.labs[0], nullptr, nullptr, 0, n,
                                                            ws.ghist + 3 * kRadix, status + 3 * per_pass,
                                                            ws.counters + 3, ws.keys[1], ws.labs[1]);
 }
