@@ -107,7 +107,7 @@ __device__ __forceinline__ void st_status(u64* p, u64 v) {
 }
 
 #ifndef TMB_K4_WINDOW
-#define TMB_K4_WINDOW 1  // status words of this many earlier tiles are fetched per look-back step
+#define TMB_K4_WINDOW 2  // status words of this many earlier tiles are fetched per look-back step
 #endif
 
 // One radix pass in ONE kernel ("onesweep"): a CTA takes the next tile of 4096 keys, ranks them by the pass's 8-bit
