@@ -50,6 +50,7 @@ def test_confmat_c1000_2p24_full_matrix(kind, dt):
     g = torch.Generator(device=DEV).manual_seed(11)
     p, t = _confmat_inputs(kind, n, C, g)
     cm = torch.zeros(C, C, dtype=torch.int64, device=DEV)
+    N.read_status_words(torch.device(DEV))  # findings left behind by earlier tests are not this call's
     N.confmat_update_(cm, p.to(dt), t.to(dt), C)
     assert torch.equal(cm, _bincount_matrix(p, t, C))
     assert N.read_status_words(torch.device(DEV)) == (0, 0)
@@ -113,6 +114,7 @@ def test_binned_t200_2p28_all_thresholds():
     target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
     thr = torch.linspace(0, 1, 200, device=DEV)
     st = torch.zeros(200, 2, 2, dtype=torch.int64, device=DEV)
+    N.read_status_words(torch.device(DEV))
     N.binned_curve_update_(st, preds, target, thr)
     assert torch.equal(st, _binned_restatement(preds, target, thr))
     assert N.read_status_words(torch.device(DEV)) == (0, 0)
@@ -216,6 +218,7 @@ def test_bincount_update_vs_oracle(dt, n, m):
     g = torch.Generator().manual_seed(n + m)
     x = torch.randint(0, m, (n,), generator=g).to(dt)
     out = torch.zeros(m, dtype=torch.int64, device=DEV)
+    N.read_status_words(torch.device(DEV))
     N.bincount_update_(out, x.to(DEV))
     N.bincount_update_(out, x.to(DEV))  # accumulates
     assert np.array_equal(out.cpu().numpy(), 2 * O.bincount(x.numpy().astype(np.int64), m))

@@ -106,6 +106,26 @@ __device__ __forceinline__ void st_status(u64* p, u64 v) {
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// peers &= lanes whose key agrees with mine in the bit(s) of `bitmask`: test, ballot, complement the ballot on the
+// lanes where the bit is clear, and - four instructions per digit bit, written out because the compiler's version of
+// the same expression takes six
+__device__ __forceinline__ u32 match_bit(u32 peers, u32 key, u32 bitmask) {
+  u32 out;
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " .reg .b32 v, t;\n"
+      " and.b32 t, %2, %3;\n"
+      " setp.ne.u32 p, t, 0;\n"
+      " vote.sync.ballot.b32 v, p, 0xffffffff;\n"
+      " @!p not.b32 v, v;\n"
+      " and.b32 %0, %1, v;\n"
+      "}"
+      : "=r"(out)
+      : "r"(peers), "r"(key), "r"(bitmask));
+  return out;
+}
+
 #ifndef TMB_K4_WINDOW
 #define TMB_K4_WINDOW 2  // status words of this many earlier tiles are fetched per look-back step
 #endif
@@ -198,9 +218,7 @@ k4_onesweep(const u32* __restrict__ keys_in, const unsigned char* __restrict__ l
       u32 peers = __ballot_sync(0xffffffffu, in);
 #pragma unroll
       for (int bit = 0; bit < 8; ++bit) {
-        const bool one = (d >> bit) & 1u;
-        const u32 vote = __ballot_sync(0xffffffffu, one);
-        peers &= one ? vote : ~vote;
+        peers = match_bit(peers, key[r], 1u << (SHIFT + bit));
       }
       const u32 before = cnt[d];
       const u32 rk = before + __popc(peers & lt);
