@@ -261,6 +261,28 @@ TMB_API int tmb_stat_scores_update(const void* preds_dev, int preds_dtype, const
                            int64_t ignore_index, int range_check_ignored, int64_t* out_dev, void* workspace_dev,
                            size_t workspace_bytes, int32_t* status_dev /* may be NULL */, void* stream);
 
+/* K2, row-wise form: the four counts of every ROW of (n_rows, width) row-major tensors.
+ * Replaces: the `multidim_average="samplewise"` branches of `_binary_stat_scores_update`
+ *           (stat_scores.py:127-130; rows = samples, width = the flattened extra dimensions) and
+ *           `_multilabel_stat_scores_update` (:677-680; rows = (sample, label) pairs, width = extra dimensions), and
+ *           the legacy `_stat_scores` (:861-906) with reduce="samples" / the per-sample forms of (N, C, X) inputs.
+ * Float preds are thresholded (strict >) after an optional sigmoid (prob_mode: TMB_PROB_AS_IS or TMB_PROB_SIGMOID —
+ * the all-or-nothing range decision is the caller's, it spans the whole batch); integer preds are labels.
+ * out_dev: int64[4 * n_rows] laid out [tp | fp | tn | fn], WRITTEN (per-sample rows are cat states, not sums). */
+TMB_API int tmb_stat_scores_rows(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
+                                 int64_t n_rows, int64_t width, double threshold, int prob_mode, int has_ignore,
+                                 int64_t ignore_index, int64_t* out_dev, void* stream);
+
+/* K1c, row-wise form: per sample and class tp / fp / tn / fn of (n_rows, width) label tensors.
+ * Replaces: the samplewise one-hot branch of `_multiclass_stat_scores_update` (stat_scores.py:363-393, top_k = 1):
+ *           no (N, X, C) one-hot tensors, three length-C shared-memory histograms per sample instead.
+ * Targets equal to ignore_index are skipped; a label outside [0, num_classes) raises TMB_STATUS_LABEL_RANGE (the
+ * reference's one_hot raises).  out_dev: int64[4 * n_rows * num_classes] laid out [tp | fp | tn | fn][row][class],
+ * WRITTEN.  TMB_ERR_TOO_LARGE when 3 * num_classes counters exceed one CTA's shared memory. */
+TMB_API int tmb_class_stats_rows(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
+                                 int64_t n_rows, int64_t width, int64_t num_classes, int has_ignore,
+                                 int64_t ignore_index, int64_t* out_dev, int32_t* status_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

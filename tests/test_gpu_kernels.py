@@ -775,3 +775,84 @@ def test_exact_auroc_ap_functional_agrees_with_curve_path_and_sklearn():
     # degenerate targets fall back to the reference behaviour
     with pytest.warns(UserWarning):
         assert float(F.binary_auroc(p.to(DEV), torch.zeros(n, dtype=torch.long, device=DEV), thresholds=None)) == 0.0
+
+
+# =========================================================================== row-wise (samplewise) forms
+@pytest.mark.parametrize("width", [1, 2, 3, 4, 7, 8, 31, 32, 33, 100, 128, 1000, 4096 + 4])
+@pytest.mark.parametrize("pdt", [torch.float32, torch.float16, torch.int64, torch.uint8])
+def test_stat_scores_rows_vs_masked_sums(width, pdt):
+    """K2 row-wise form against the reference's four masked sums over dim 1 (stat_scores.py:120-131)."""
+    N = _native()
+    n_rows = 257 if width < 1000 else 19
+    g = torch.Generator().manual_seed(width * 7 + 1)
+    if pdt.is_floating_point:
+        preds = torch.rand(n_rows, width, generator=g).to(pdt)
+        hard = preds > torch.tensor(0.5, dtype=pdt)  # the comparison happens in the preds dtype
+    else:
+        preds = torch.randint(0, 2, (n_rows, width), generator=g).to(pdt)
+        hard = preds.bool()
+    target = torch.randint(0, 2, (n_rows, width), generator=g)
+    for ignore_index in (None, -1):
+        t = target.clone()
+        if ignore_index is not None:
+            t[torch.rand(n_rows, width, generator=g) < 0.2] = ignore_index
+        got = N.stat_scores_rows(preds.to(DEV), t.to(DEV), width, 0.5, ignore_index).cpu()
+        valid = t != ignore_index if ignore_index is not None else torch.ones_like(t, dtype=torch.bool)
+        want = torch.stack([(hard & (t == 1) & valid).sum(1), (hard & (t == 0) & valid).sum(1),
+                            (~hard & (t == 0) & valid).sum(1), (~hard & (t == 1) & valid).sum(1)])
+        assert torch.equal(got, want)
+    if pdt.is_floating_point:  # logits through the kernel's sigmoid
+        logits = (torch.randn(n_rows, width, generator=g) * 3).to(pdt)
+        got = N.stat_scores_rows(logits.to(DEV), target.to(DEV), width, 0.5, None, sigmoid=True).cpu()
+        hard = logits.to(DEV).sigmoid().cpu() > torch.tensor(0.5, dtype=pdt)
+        want = torch.stack([(hard & (target == 1)).sum(1), (hard & (target == 0)).sum(1),
+                            (~hard & (target == 0)).sum(1), (~hard & (target == 1)).sum(1)])
+        assert torch.equal(got, want)
+
+
+@pytest.mark.parametrize("C", [2, 5, 100, 1000, 5000])
+@pytest.mark.parametrize("width", [1, 17, 64, 1000])
+@pytest.mark.parametrize("ignore_index", [None, -1, 1])
+def test_class_stats_rows_vs_onehot(C, width, ignore_index):
+    """K1c row-wise form against the one-hot formulation (stat_scores.py:363-393) evaluated with torch ops."""
+    N = _native()
+    n_rows = 64 if C <= 1000 else 5
+    g = torch.Generator().manual_seed(C + width)
+    p = torch.randint(0, C, (n_rows, width), generator=g)
+    t = torch.randint(0, C, (n_rows, width), generator=g)
+    p = torch.where(torch.rand(n_rows, width, generator=g) < 0.5, t, p)
+    if ignore_index == -1:
+        t[torch.rand(n_rows, width, generator=g) < 0.2] = -1
+    got = N.class_stats_rows(p.to(DEV), t.to(DEV), C, ignore_index).cpu()
+    valid = t != ignore_index if ignore_index is not None else torch.ones_like(t, dtype=torch.bool)
+    poh = torch.nn.functional.one_hot(p, C).bool()
+    toh = torch.nn.functional.one_hot(t.clamp(min=0), C).bool()
+    v = valid[..., None]
+    want = torch.stack([(poh & toh & v).sum(1), (poh & ~toh & v).sum(1), (~poh & ~toh & v).sum(1),
+                        (~poh & toh & v).sum(1)])
+    assert torch.equal(got, want)
+    assert N.read_status(torch.device(DEV)) == 0
+
+
+def test_samplewise_paths_are_native(monkeypatch):
+    """The samplewise branches must go through the row-wise kernels, not through eager one-hot sums."""
+    import torchmetrics_b200 as tm
+    from torchmetrics_b200.functional.classification import stat_scores as S
+
+    def boom(*a, **k):
+        raise AssertionError("eager masked sums used")
+
+    monkeypatch.setattr(S, "_four_masked_sums", boom)
+    g = torch.Generator().manual_seed(2)
+    F = tm.functional
+    pb = torch.rand(6, 50, generator=g).to(DEV)
+    tb = torch.randint(0, 2, (6, 50), generator=g).to(DEV)
+    assert F.binary_stat_scores(pb, tb, multidim_average="samplewise").shape == (6, 5)
+    pl = torch.rand(6, 4, 50, generator=g).to(DEV)
+    tl = torch.randint(0, 2, (6, 4, 50), generator=g).to(DEV)
+    assert F.multilabel_stat_scores(pl, tl, 4, multidim_average="samplewise", average=None).shape == (6, 4, 5)
+    pc = torch.randn(6, 7, 50, generator=g).to(DEV)
+    tc = torch.randint(0, 7, (6, 50), generator=g).to(DEV)
+    assert F.multiclass_stat_scores(pc, tc, 7, multidim_average="samplewise", average=None).shape == (6, 7, 5)
+    with pytest.raises(RuntimeError, match="CUDA tensors only"):
+        F.binary_stat_scores(pb.cpu(), tb.cpu(), multidim_average="samplewise")

@@ -81,6 +81,10 @@ _SIGNATURES = {
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                           _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,
                                           _c.c_void_p, _c.c_size_t, _c.c_void_p, _c.c_void_p]),
+    "tmb_stat_scores_rows": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
+                                        _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p]),
+    "tmb_class_stats_rows": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
+                                        _c.c_int64, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_void_p]),
 }
 
 _lib = None
@@ -415,6 +419,42 @@ def stat_scores_update_(out: Tensor, preds: Tensor, target: Tensor, num_labels: 
                                         out.data_ptr(), ws.data_ptr(), ws.numel(),
                                         sc.status.data_ptr() if report_values else None, _stream_ptr(dev))
     _check(rc, "tmb_stat_scores_update")
+
+
+def stat_scores_rows(preds: Tensor, target: Tensor, width: int, threshold: float = 0.5,
+                     ignore_index: Optional[int] = None, sigmoid: bool = False) -> Tensor:
+    """(4, n_rows) int64 [tp|fp|tn|fn] of every row of (n_rows, width) preds / target (K2, row-wise form)."""
+    dev = require_cuda(preds, target)
+    preds = as_kernel_scores(preds.reshape(-1)) if preds.is_floating_point() else as_kernel_labels(preds.reshape(-1))
+    target = as_kernel_labels(target.reshape(-1))
+    assert preds.numel() == target.numel()
+    n_rows = preds.numel() // width if width else 0
+    out = torch.empty(4, n_rows, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = load().tmb_stat_scores_rows(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                         n_rows, width, float(threshold), PROB_SIGMOID if sigmoid else PROB_AS_IS,
+                                         ignore_index is not None, 0 if ignore_index is None else int(ignore_index),
+                                         out.data_ptr(), _stream_ptr(dev))
+    _check(rc, "tmb_stat_scores_rows")
+    return out
+
+
+def class_stats_rows(preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int] = None) -> Tensor:
+    """(4, n_rows, C) int64 [tp|fp|tn|fn] per sample and class of (n_rows, width) label tensors (K1c, row-wise)."""
+    dev = require_cuda(preds, target)
+    assert preds.shape == target.shape and preds.ndim == 2
+    n_rows, width = preds.shape
+    preds, target = as_kernel_labels(preds), as_kernel_labels(target)
+    out = torch.empty(4, n_rows, num_classes, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = load().tmb_class_stats_rows(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
+                                         n_rows, width, num_classes, ignore_index is not None,
+                                         0 if ignore_index is None else int(ignore_index), out.data_ptr(),
+                                         scratch(dev).status.data_ptr(), _stream_ptr(dev))
+    if rc == -4:
+        raise RuntimeError("tmb_class_stats_rows failed with TMB_ERR_TOO_LARGE: " + load().tmb_last_cuda_error().decode())
+    _check(rc, "tmb_class_stats_rows")
+    return out
 
 
 def exact_curve(preds: Tensor, target: Tensor, pos_label: int = 1):

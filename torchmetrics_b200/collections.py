@@ -232,65 +232,67 @@ class MetricCollection(ModuleDict):
     # ------------------------------------------------------------------ construction
     def add_metrics(self, metrics: Union[Metric, Sequence[Metric], Dict[str, Metric]],
                     *additional_metrics: Metric) -> None:
-        if isinstance(metrics, Metric):
-            metrics = [metrics]
-        if isinstance(metrics, Sequence):
-            metrics = list(metrics)
-            extra = []
-            for m in additional_metrics:
-                (metrics if isinstance(m, Metric) else extra).append(m)
-            if extra:
-                rank_zero_warn(f"You have passes extra arguments {extra} which are not `Metric` so they will be ignored.")
-        elif additional_metrics:
-            raise ValueError(
-                f"You have passes extra arguments {additional_metrics} which are not compatible"
-                f" with first passed dictionary {metrics} so they will be ignored."
-            )
+        """Register metrics under their names (reference behaviour: collections.py:408-462).
 
-        if isinstance(metrics, dict):
-            for name in sorted(metrics.keys()):
-                metric = metrics[name]
-                if not isinstance(metric, (Metric, MetricCollection)):
-                    raise ValueError(
-                        f"Value {metric} belonging to key {name} is not an instance of"
-                        " `torchmetrics.Metric` or `torchmetrics.MetricCollection`"
-                    )
-                if isinstance(metric, Metric):
-                    self[name] = metric
-                else:
-                    for k, v in metric.items(keep_base=False):
-                        v.postfix = metric.postfix
-                        v.prefix = metric.prefix
-                        v._from_collection = True
-                        self[f"{name}_{k}"] = v
-        elif isinstance(metrics, Sequence):
-            for metric in metrics:
-                if not isinstance(metric, (Metric, MetricCollection)):
-                    raise ValueError(
-                        f"Input {metric} to `MetricCollection` is not a instance of"
-                        " `torchmetrics.Metric` or `torchmetrics.MetricCollection`"
-                    )
-                if isinstance(metric, Metric):
-                    name = metric.__class__.__name__
-                    if name in self:
-                        raise ValueError(f"Encountered two metrics both named {name}")
-                    self[name] = metric
-                else:
-                    for k, v in metric.items(keep_base=False):
-                        v.postfix = metric.postfix
-                        v.prefix = metric.prefix
-                        v._from_collection = True
-                        self[k] = v
-        else:
-            raise ValueError(
-                "Unknown input to MetricCollection. Expected, `Metric`, `MetricCollection` or `dict`/`sequence` of the"
-                f" previous, but got {metrics}"
-            )
+        The three accepted shapes - one metric, a sequence (plus positional extras), a dict - are first flattened
+        into one list of `(name, metric)` entries by `_named_entries`; nested collections contribute their members
+        with the nested prefix / postfix carried along.  The entries are then inserted in one loop.
+        """
+        for name, metric in self._named_entries(metrics, additional_metrics):
+            self[name] = metric
         self._groups_checked = False
         if self._enable_compute_groups:
             self._init_compute_groups()
         else:
             self._groups = {}
+
+    def _named_entries(self, metrics: Any, extras: Sequence[Any]) -> List[Tuple[str, Metric]]:
+        by_key = isinstance(metrics, dict)
+        if by_key:
+            if extras:
+                raise ValueError(
+                    f"You have passes extra arguments {extras} which are not compatible"
+                    f" with first passed dictionary {metrics} so they will be ignored."
+                )
+            items = [(key, metrics[key]) for key in sorted(metrics)]
+        elif isinstance(metrics, Metric) or (isinstance(metrics, Sequence) and not isinstance(metrics, str)):
+            head = [metrics] if isinstance(metrics, Metric) else list(metrics)
+            ignored = [m for m in extras if not isinstance(m, Metric)]
+            if ignored:
+                rank_zero_warn(
+                    f"You have passes extra arguments {ignored} which are not `Metric` so they will be ignored."
+                )
+            items = [(None, m) for m in head + [m for m in extras if isinstance(m, Metric)]]
+        else:
+            raise ValueError(
+                "Unknown input to MetricCollection. Expected, `Metric`, `MetricCollection` or `dict`/`sequence` of the"
+                f" previous, but got {metrics}"
+            )
+
+        entries: List[Tuple[str, Metric]] = []
+        taken = set(self.keys(keep_base=True))
+        for key, obj in items:
+            if isinstance(obj, MetricCollection):
+                for inner, member in obj.items(keep_base=False):
+                    member.prefix, member.postfix = obj.prefix, obj.postfix
+                    member._from_collection = True
+                    entries.append((inner if key is None else f"{key}_{inner}", member))
+            elif isinstance(obj, Metric):
+                name = key if key is not None else obj.__class__.__name__
+                if key is None and (name in taken or any(name == n for n, _ in entries)):
+                    raise ValueError(f"Encountered two metrics both named {name}")
+                entries.append((name, obj))
+            elif by_key:
+                raise ValueError(
+                    f"Value {obj} belonging to key {key} is not an instance of"
+                    " `torchmetrics.Metric` or `torchmetrics.MetricCollection`"
+                )
+            else:
+                raise ValueError(
+                    f"Input {obj} to `MetricCollection` is not a instance of"
+                    " `torchmetrics.Metric` or `torchmetrics.MetricCollection`"
+                )
+        return entries
 
     def _init_compute_groups(self) -> None:
         if isinstance(self._enable_compute_groups, list):
@@ -315,8 +317,9 @@ class MetricCollection(ModuleDict):
         name = base if self.prefix is None else self.prefix + base
         return name if self.postfix is None else name + self.postfix
 
-    def _to_renamed_ordered_dict(self) -> OrderedDict:
-        return OrderedDict((self._set_name(k), v) for k, v in self._modules.items())
+    def _to_renamed_ordered_dict(self) -> Dict[str, Metric]:
+        # same mapping type as `_modules`, so keys()/items() views have one type whichever way they are asked for
+        return type(self._modules)((self._set_name(k), v) for k, v in self._modules.items())
 
     def __iter__(self) -> Iterator[Hashable]:
         return iter(self.keys())

@@ -292,6 +292,160 @@ static int launch_stat(StatParams P, int prob_mode, cudaStream_t st) {
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Row-wise statistics (multidim_average="samplewise"; the legacy `_stat_scores` with reduce="samples"): the four
+// counts of every row of an (n_rows, width) pair of tensors.  The reference builds bool / int64 temporaries of the
+// input size and calls four `sum(dim)` reductions (stat_scores.py:127-130, :677-680, :891-906); here a row is read
+// once by a group of 1..32 lanes (the group size follows the row width, so short rows do not idle a warp and
+// long rows are read with coalesced 16/32-byte loads), reduced with shuffles and written as four int64.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kRowsThreads = 256;
+
+template <typename PT, typename TT, bool SIGMOID, int V>
+__global__ void __launch_bounds__(kRowsThreads) stat_scores_rows_kernel(const StatParams P, long long width,
+                                                                         int lpr_log2) {
+  using CT = typename CmpType<PT>::type;
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  const CT thr = threshold_as<PT>(P.threshold);
+  const int lane = threadIdx.x & 31;
+  const int lpr = 1 << lpr_log2;
+  const int sub = lane & (lpr - 1);
+  const long long rows_per_warp = 32 >> lpr_log2;
+  const long long warp0 = ((long long)blockIdx.x * kRowsThreads + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * kRowsThreads) >> 5;
+  long long* out = reinterpret_cast<long long*>(P.out);
+  for (long long row0 = warp0 * rows_per_warp; row0 < P.n_rows; row0 += nwarps * rows_per_warp) {
+    const long long row = row0 + (lane >> lpr_log2);
+    Counts c{0, 0, 0, 0};
+    int oor = 0;
+    Seen seen{0, 0, 0};
+    if (row < P.n_rows) {
+      const long long base = row * width;
+      if constexpr (V == 4) {
+        for (long long j = (long long)sub * 4; j < width; j += (long long)lpr * 4) {
+          const Vec4<PT> pv = load4(preds + base + j);
+          const Vec4<TT> tv = load4(target + base + j);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) tally<PT, TT, SIGMOID>(pv.v[q], tv.v[q], P, thr, c, oor, seen);
+        }
+      } else {
+        for (long long j = sub; j < width; j += lpr) tally<PT, TT, SIGMOID>(preds[base + j], target[base + j], P, thr, c, oor, seen);
+      }
+    }
+    for (int o = lpr >> 1; o; o >>= 1) {
+      c.tp += __shfl_xor_sync(0xffffffffu, c.tp, o);
+      c.fp += __shfl_xor_sync(0xffffffffu, c.fp, o);
+      c.tn += __shfl_xor_sync(0xffffffffu, c.tn, o);
+      c.fn += __shfl_xor_sync(0xffffffffu, c.fn, o);
+    }
+    if (row < P.n_rows && sub == 0) {
+      out[row] = c.tp;
+      out[P.n_rows + row] = c.fp;
+      out[2 * P.n_rows + row] = c.tn;
+      out[3 * P.n_rows + row] = c.fn;
+    }
+  }
+}
+
+template <typename PT, typename TT>
+static int launch_rows(StatParams P, long long width, int prob_mode, cudaStream_t st) {
+  P.check_range = 0;
+  P.only_if_flag = 0;
+  const bool v4 = (width % 4) == 0;
+  const long long per = v4 ? 8 : 2;  // elements a lane should have to itself before another lane joins the row
+  int lpr_log2 = 0;
+  while (lpr_log2 < 5 && ((long long)per << lpr_log2) < width) ++lpr_log2;
+  const long long rows_per_warp = 32 >> lpr_log2;
+  const long long warps = (P.n_rows + rows_per_warp - 1) / rows_per_warp;
+  const long long want = (warps + kRowsThreads / 32 - 1) / (kRowsThreads / 32);
+  const long long cap = (long long)sm_count() * 16;
+  const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
+  bool sigmoid = false;
+  if constexpr (IsFloatScore<PT>::value) {
+    if (prob_mode == TMB_PROB_SIGMOID) sigmoid = true;
+    else if (prob_mode != TMB_PROB_AS_IS) return TMB_ERR_ARG;
+  }
+  if constexpr (IsFloatScore<PT>::value) {
+    if (sigmoid) {
+      if (v4) stat_scores_rows_kernel<PT, TT, true, 4><<<grid, kRowsThreads, 0, st>>>(P, width, lpr_log2);
+      else stat_scores_rows_kernel<PT, TT, true, 1><<<grid, kRowsThreads, 0, st>>>(P, width, lpr_log2);
+      TMB_CUDA_CHECK(cudaGetLastError());
+      return TMB_OK;
+    }
+  }
+  if (v4) stat_scores_rows_kernel<PT, TT, false, 4><<<grid, kRowsThreads, 0, st>>>(P, width, lpr_log2);
+  else stat_scores_rows_kernel<PT, TT, false, 1><<<grid, kRowsThreads, 0, st>>>(P, width, lpr_log2);
+  TMB_CUDA_CHECK(cudaGetLastError());
+  return TMB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Row-wise multiclass statistics: per sample n and class c, tp / fp / tn / fn of the (X,) label vectors of that sample.
+// The reference one-hots both tensors to (N, X, C) and takes four masked sums (stat_scores.py:363-393); here a warp
+// keeps three length-C histograms of one sample in shared memory (hits of c, predictions of c, targets of c) and
+// converts them on the way out.
+// ---------------------------------------------------------------------------------------------------------------
+struct ClassRowsParams {
+  const void* preds;
+  const void* target;
+  long long n_rows, width, C;
+  int has_ignore;
+  long long ignore;
+  long long* out;  // [4][n_rows][C]
+  int* status;
+};
+
+template <typename PT, typename TT>
+__global__ void __launch_bounds__(kRowsThreads) class_stats_rows_kernel(const ClassRowsParams P, int warps_per_cta) {
+  extern __shared__ u32 s_hist[];  // [warps_per_cta][3][C]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (warp >= warps_per_cta) return;
+  const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
+  const TT* __restrict__ target = static_cast<const TT*>(P.target);
+  const long long C = P.C;
+  u32* hit = s_hist + (size_t)warp * 3 * C;
+  u32* pred_of = hit + C;
+  u32* targ_of = pred_of + C;
+  int bad = 0;
+  for (long long row = (long long)blockIdx.x * warps_per_cta + warp; row < P.n_rows;
+       row += (long long)gridDim.x * warps_per_cta) {
+    for (long long c = lane; c < 3 * C; c += 32) hit[c] = 0;
+    __syncwarp();
+    const long long base = row * P.width;
+    u32 valid = 0;
+    for (long long j = lane; j < P.width; j += 32) {
+      const long long t = as_i64(target[base + j]), p = as_i64(preds[base + j]);
+      if (P.has_ignore && t == P.ignore) continue;
+      if ((u64)t >= (u64)C || (u64)p >= (u64)C) {
+        bad = 1;  // the reference's one_hot raises on such a label
+        continue;
+      }
+      ++valid;
+      if (p == t) {
+        atomicAdd(&hit[t], 1u);
+      } else {
+        atomicAdd(&pred_of[p], 1u);
+        atomicAdd(&targ_of[t], 1u);
+      }
+    }
+    valid = __reduce_add_sync(0xffffffffu, valid);
+    __syncwarp();
+    long long* o = P.out + row * C;
+    const long long plane = P.n_rows * C;
+    for (long long c = lane; c < C; c += 32) {
+      const long long tp = hit[c], fp = pred_of[c], fn = targ_of[c];
+      o[c] = tp;
+      o[plane + c] = fp;
+      o[2 * plane + c] = (long long)valid - tp - fp - fn;
+      o[3 * plane + c] = fn;
+    }
+    __syncwarp();
+  }
+  if (bad) report_status(P.status, TMB_STATUS_LABEL_RANGE);
+}
+
 }  // namespace tmb
 
 using namespace tmb;
@@ -332,5 +486,85 @@ extern "C" int tmb_stat_scores_update(const void* preds, int preds_dtype, const 
       TMB_DISPATCH_INT(target_dtype, TT, { return launch_stat<PT, TT>(P, prob_mode, st); })
     })
   }
+  return TMB_ERR_ARG;
+}
+
+extern "C" int tmb_stat_scores_rows(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                    int64_t n_rows, int64_t width, double threshold, int prob_mode, int has_ignore,
+                                    int64_t ignore_index, int64_t* out, void* stream) {
+  if (n_rows < 0 || width < 0 || !out) return TMB_ERR_ARG;
+  if (n_rows == 0) return TMB_OK;
+  if (width >= (1LL << 31)) return TMB_ERR_TOO_LARGE;  // 32-bit counters per row
+  cudaStream_t st = (cudaStream_t)stream;
+  if (width == 0) {
+    TMB_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)4 * n_rows * sizeof(int64_t), st));
+    return TMB_OK;
+  }
+  if (!preds || !target) return TMB_ERR_ARG;
+  if (!aligned32(preds) || !aligned32(target)) return TMB_ERR_ALIGN;
+  StatParams P{};
+  P.preds = preds;
+  P.target = target;
+  P.n_rows = n_rows;
+  P.L = 1;
+  P.threshold = threshold;
+  P.has_ignore = has_ignore ? 1 : 0;
+  P.ignore = ignore_index;
+  P.out = (u64*)out;
+  if (is_float_dtype(preds_dtype)) {
+    TMB_DISPATCH_FLOAT(preds_dtype, PT, {
+      TMB_DISPATCH_INT(target_dtype, TT, { return launch_rows<PT, TT>(P, width, prob_mode, st); })
+    })
+  } else {
+    TMB_DISPATCH_INT(preds_dtype, PT, {
+      TMB_DISPATCH_INT(target_dtype, TT, { return launch_rows<PT, TT>(P, width, prob_mode, st); })
+    })
+  }
+  return TMB_ERR_ARG;
+}
+
+extern "C" int tmb_class_stats_rows(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                    int64_t n_rows, int64_t width, int64_t num_classes, int has_ignore,
+                                    int64_t ignore_index, int64_t* out, int32_t* status, void* stream) {
+  if (n_rows < 0 || width < 0 || num_classes < 1 || !out || !status) return TMB_ERR_ARG;
+  if (n_rows == 0) return TMB_OK;
+  if (width >= (1LL << 31)) return TMB_ERR_TOO_LARGE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (width == 0) {
+    TMB_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)4 * n_rows * num_classes * sizeof(int64_t), st));
+    return TMB_OK;
+  }
+  if (!preds || !target) return TMB_ERR_ARG;
+  const size_t per_warp = (size_t)3 * num_classes * sizeof(u32);
+  const size_t room = (size_t)max_optin_smem() - 1024;
+  if (per_warp > room) {
+    set_error_text("tmb_class_stats_rows: three per-sample histograms of num_classes bins do not fit shared memory");
+    return TMB_ERR_TOO_LARGE;
+  }
+  int warps = (int)(room / per_warp);
+  if (warps > kRowsThreads / 32) warps = kRowsThreads / 32;
+  const size_t smem = per_warp * warps;
+  ClassRowsParams P{};
+  P.preds = preds;
+  P.target = target;
+  P.n_rows = n_rows;
+  P.width = width;
+  P.C = num_classes;
+  P.has_ignore = has_ignore ? 1 : 0;
+  P.ignore = ignore_index;
+  P.out = (long long*)out;
+  P.status = status;
+  const long long want = (n_rows + warps - 1) / warps;
+  const long long cap = (long long)sm_count() * 8;
+  const int grid = (int)(want < cap ? want : cap);
+  TMB_DISPATCH_INT(preds_dtype, PT, {
+    TMB_DISPATCH_INT(target_dtype, TT, {
+      auto k = class_stats_rows_kernel<PT, TT>;
+      TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, kRowsThreads, smem, st>>>(P, warps);
+      TMB_CUDA_CHECK(cudaGetLastError());
+      return TMB_OK;
+    })
+  })
   return TMB_ERR_ARG;
 }

@@ -4,8 +4,10 @@
 runs K1 (confusion matrix, then diag / row / column sums exactly as stat_scores.py:405-418) or the match-count kernel
 for `average="micro"` (:394-404).  `_*_update_fused` folds `_format` into the kernel pass.
 
-`multidim_average="samplewise"` and `top_k > 1` follow the reference's one-hot formulation with device-side torch
-ops (:363-393): they return per-sample rows rather than O(C) counts and are outside the streaming-histogram path.
+`multidim_average="samplewise"` returns per-sample rows instead of O(C) counts: the binary / multilabel forms run the
+row-wise K2 kernel (`tmb_stat_scores_rows`, one pass over the raw scores), the multiclass form the row-wise K1c kernel
+(`tmb_class_stats_rows`, three per-sample histograms instead of (N, X, C) one-hot tensors).  Only samplewise
+`top_k > 1` still follows the reference's one-hot formulation with device-side torch ops (:363-393).
 """
 from importlib import import_module
 from typing import Optional, Tuple
@@ -73,8 +75,8 @@ def _binary_stat_scores_update(preds: Tensor, target: Tensor, multidim_average: 
         stats = torch.zeros(4, 1, dtype=torch.int64, device=preds.device)
         _native.stat_scores_update_(stats, preds, target, 1, 0.5, None, _native.PROB_AS_IS, report_values=False)
         return stats[0, 0], stats[1, 0], stats[2, 0], stats[3, 0]
-    tp, fp, tn, fn = _four_masked_sums(preds, target, [1])
-    return tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze()
+    rows = _native.stat_scores_rows(preds, target, preds.shape[1] if preds.ndim > 1 else 1)
+    return rows[0].squeeze(), rows[1].squeeze(), rows[2].squeeze(), rows[3].squeeze()
 
 
 def _binary_stat_scores_update_fused(preds: Tensor, target: Tensor, threshold: float = 0.5,
@@ -82,8 +84,12 @@ def _binary_stat_scores_update_fused(preds: Tensor, target: Tensor, threshold: f
                                      out: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
     """_format + _update in one K2 pass (global); `out` is an optional (4,1) int64 accumulator."""
     if multidim_average != "global":
-        return _binary_stat_scores_update(*_binary_stat_scores_format(preds, target, threshold, ignore_index),
-                                          multidim_average)
+        # one row per sample: threshold, sigmoid and ignore filter happen in the row-wise kernel; only the reference's
+        # batch-wide range decision (stat_scores.py:104-106) is taken here
+        n = preds.shape[0]
+        sigmoid = preds.is_floating_point() and not C.in_unit_interval(preds)
+        rows = _native.stat_scores_rows(preds, target, preds.numel() // n if n else 0, threshold, ignore_index, sigmoid)
+        return rows[0].squeeze(), rows[1].squeeze(), rows[2].squeeze(), rows[3].squeeze()
     stats = out if out is not None else torch.zeros(4, 1, dtype=torch.int64, device=preds.device)
     _native.stat_scores_update_(stats, preds, target, 1, threshold, ignore_index, _native.PROB_AUTO)
     return stats[0, 0], stats[1, 0], stats[2, 0], stats[3, 0]
@@ -154,6 +160,10 @@ def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: i
         stats = torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
         _native.class_stats_topk_update_(stats, idx, target.reshape(-1), num_classes, ignore_index)
         return stats[0], stats[1], stats[2], stats[3]
+    if multidim_average == "samplewise" and top_k == 1 and not preds.is_floating_point():
+        # (N, X) label tensors: per sample and class counts from three per-sample histograms (K1c, row-wise form)
+        rows = _native.class_stats_rows(preds, target, num_classes, ignore_index)
+        return rows[0], rows[1], rows[2], rows[3]
     if multidim_average == "samplewise" or top_k != 1:
         return _multiclass_stat_scores_onehot(preds, target, num_classes, top_k, multidim_average, ignore_index)
     if average == "micro":
@@ -293,8 +303,9 @@ def _multilabel_stat_scores_update(preds: Tensor, target: Tensor, multidim_avera
         _native.stat_scores_update_(stats, _label_major(preds, L), _label_major(target, L), L, 0.5, None,
                                     _native.PROB_AS_IS, report_values=False)
         return stats[0], stats[1], stats[2], stats[3]
-    tp, fp, tn, fn = _four_masked_sums(preds, target, [-1])
-    return tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze()
+    n, L = preds.shape[:2]
+    rows = _native.stat_scores_rows(preds, target, preds.shape[2]).view(4, n, L)
+    return rows[0].squeeze(), rows[1].squeeze(), rows[2].squeeze(), rows[3].squeeze()
 
 
 def _multilabel_stat_scores_update_fused(preds: Tensor, target: Tensor, num_labels: int, threshold: float = 0.5,
@@ -302,8 +313,12 @@ def _multilabel_stat_scores_update_fused(preds: Tensor, target: Tensor, num_labe
                                          out: Optional[Tensor] = None):
     """_format + _update in one K2 pass over the raw scores; `out` is an optional (4, L) int64 accumulator."""
     if multidim_average != "global":
-        return _multilabel_stat_scores_update(
-            *_multilabel_stat_scores_format(preds, target, num_labels, threshold, ignore_index), multidim_average)
+        # rows = (sample, label) pairs of the (N, L, X) layout the inputs already have
+        n = preds.shape[0]
+        width = preds.numel() // (n * num_labels) if n else 0
+        sigmoid = preds.is_floating_point() and not C.in_unit_interval(preds)
+        rows = _native.stat_scores_rows(preds, target, width, threshold, ignore_index, sigmoid).view(4, n, num_labels)
+        return rows[0].squeeze(), rows[1].squeeze(), rows[2].squeeze(), rows[3].squeeze()
     stats = out if out is not None else torch.zeros(4, num_labels, dtype=torch.int64, device=preds.device)
     _native.stat_scores_update_(stats, _label_major(preds, num_labels), _label_major(target, num_labels), num_labels,
                                 threshold, ignore_index, _native.PROB_AUTO)

@@ -510,8 +510,9 @@ class Metric(Module, ABC):
                 parts.append(id(val))
         return hash(tuple(parts))
 
-    def __iter__(self):
-        raise NotImplementedError("Metrics does not support iteration.")
+    # `__getitem__` below is metric algebra, not a sequence protocol: without this, `for x in metric` would loop
+    # forever over CompositionalMetrics.  None makes Python raise "'X' object is not iterable" (metric.py:1081).
+    __iter__ = None
 
     # ------------------------------------------------------------------ operator algebra -> CompositionalMetric
     def __add__(self, other): return CompositionalMetric(torch.add, self, other)
