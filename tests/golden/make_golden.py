@@ -510,6 +510,93 @@ def make_derived():
     b.save()
 
 
+def make_consumers2():
+    """Second batch of consumers of the same update kernels: operating points on the binned / exact
+    curves, group fairness on the binary stat scores, nominal association measures on the confusion matrix."""
+    import torchmetrics.functional.nominal as FN
+
+    b = Book("consumers2")
+    g = rng(91)
+    n, C, L = 311, 4, 3
+    minima = (0.0, 0.25, 0.5, 0.9, 1.0)
+    fams = {"recall_at_fixed_precision": "min_precision", "precision_at_fixed_recall": "min_recall",
+            "sensitivity_at_specificity": "min_specificity", "specificity_at_sensitivity": "min_sensitivity"}
+    bt = torch.randint(0, 2, (n,), generator=g)
+    bp = (torch.rand(n, generator=g) * 0.6 + 0.4 * bt * torch.rand(n, generator=g)).clamp(0, 1)
+    mt = torch.randint(0, C, (n,), generator=g)
+    mp = (torch.randn(n, C, generator=g) + 1.5 * torch.nn.functional.one_hot(mt, C)).softmax(1)
+    lt = torch.randint(0, 2, (n, L), generator=g)
+    lp = (torch.rand(n, L, generator=g) * 0.7 + 0.3 * lt * torch.rand(n, L, generator=g)).clamp(0, 1)
+    for thresholds in (None, 17):
+        for ii in (None, -1):
+            tb, tm_, tl = bt.clone(), mt.clone(), lt.clone()
+            if ii is not None:
+                tb[::9] = ii
+                tm_[::7] = ii
+                tl[::5, 1] = ii
+            for task, (p, t, extra) in {"binary": (bp, tb, {}), "multiclass": (mp, tm_, {"num_classes": C}),
+                                        "multilabel": (lp, tl, {"num_labels": L})}.items():
+                out = {}
+                for fam, arg in fams.items():
+                    fn = getattr(F, f"{task}_{fam}")
+                    for m in minima:
+                        val, thr = fn(p, t, **extra, **{arg: m}, thresholds=thresholds, ignore_index=ii)
+                        out[f"{fam}@{m}"] = torch.stack([val.float().reshape(-1), thr.float().reshape(-1)])
+                b.add({"what": "operating_point", "task": task, "thresholds": thresholds, "ignore_index": ii, **extra},
+                      preds=p, target=t, **out)
+    # group fairness: three groups (one of them rare), probabilities and logits, with and without ignore_index
+    groups = torch.randint(0, 3, (n,), generator=g)
+    groups[groups == 2] = torch.where(torch.rand(int((groups == 2).sum()), generator=g) < 0.8, 0, 2)
+    for kind, p in {"probs": bp, "logits": torch.randn(n, generator=g) * 2}.items():
+        for ii in (None, -1):
+            t = bt.clone()
+            if ii is not None:
+                t[::9] = ii
+            rates = F.binary_groups_stat_rates(p, t, groups, 3, ignore_index=ii)
+            fair = F.binary_fairness(p, t, groups, "all", ignore_index=ii)
+            dp = F.demographic_parity(p, groups, ignore_index=ii)
+            b.add({"what": "group_fairness", "kind": kind, "ignore_index": ii,
+                   "fair_keys": sorted(fair.keys()), "dp_keys": sorted(dp.keys())}, preds=p, target=t, groups=groups,
+                  rates=torch.stack([rates[f"group_{i}"] for i in range(len(rates))]),
+                  fair=torch.stack([fair[k] for k in sorted(fair.keys())]),
+                  dp=torch.stack([dp[k] for k in sorted(dp.keys())]))
+    # nominal association: label tensors (int and float with NaN), a 2 x 2 table (Yates), a constant variable
+    cases = {}
+    x = torch.randint(0, 5, (n,), generator=g)
+    y = torch.where(torch.rand(n, generator=g) < 0.5, x, torch.randint(0, 5, (n,), generator=g))
+    cases["labels5"] = (x, y)
+    xf = x.float()
+    xf[::11] = float("nan")
+    cases["nan"] = (xf, y.float())
+    cases["two_by_two"] = (torch.randint(0, 2, (n,), generator=g), torch.randint(0, 2, (n,), generator=g))
+    cases["constant"] = (torch.zeros(n, dtype=torch.long), torch.randint(0, 3, (n,), generator=g))
+    for name, (p, t) in cases.items():
+        for strat in ("replace", "drop"):
+            def stateful(cls, **kw):
+                # the functional form of the reference fails on a 2 x 2 table with bias correction (in-place float add
+                # into its int64 matrix, utils.py:56); its stateful form keeps a float table and works
+                m = cls(num_classes=len(torch.cat([p, t]).unique()), nan_strategy=strat, **kw)
+                m.update(p, t)
+                return m.compute()
+
+            import torchmetrics.nominal as N_
+
+            if name == "two_by_two":
+                cb, tb_ = stateful(N_.CramersV, bias_correction=True), stateful(N_.TschuprowsT, bias_correction=True)
+            else:
+                cb, tb_ = FN.cramers_v(p, t, True, strat), FN.tschuprows_t(p, t, True, strat)
+            out = {"cramers_bias": cb, "cramers": FN.cramers_v(p, t, False, strat),
+                   "tschuprows_bias": tb_, "tschuprows": FN.tschuprows_t(p, t, False, strat),
+                   "pearson": FN.pearsons_contingency_coefficient(p, t, strat), "theils_u": FN.theils_u(p, t, strat),
+                   "theils_u_rev": FN.theils_u(t, p, strat)}
+            b.add({"what": "nominal", "kind": name, "nan_strategy": strat}, preds=p, target=t,
+                  **{k: v.float() for k, v in out.items()})
+    mat = torch.randint(0, 4, (200, 4), generator=g)
+    b.add({"what": "nominal_matrix"}, matrix=mat, cramers=FN.cramers_v_matrix(mat), theils_u=FN.theils_u_matrix(mat),
+          tschuprows=FN.tschuprows_t_matrix(mat), pearson=FN.pearsons_contingency_coefficient_matrix(mat))
+    b.save()
+
+
 if __name__ == "__main__":
     make_readme()
     make_confmat()
@@ -518,3 +605,4 @@ if __name__ == "__main__":
     make_exact()
     make_doctests()
     make_derived()
+    make_consumers2()

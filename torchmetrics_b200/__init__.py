@@ -13,6 +13,8 @@ from torchmetrics_b200 import functional  # noqa: E402,F401
 from torchmetrics_b200.classification import *  # noqa: E402,F401,F403
 from torchmetrics_b200.classification import __all__ as _cls_all  # noqa: E402
 from torchmetrics_b200.collections import MetricCollection  # noqa: E402
+from torchmetrics_b200.nominal import CramersV, PearsonsContingencyCoefficient, TheilsU, TschuprowsT  # noqa: E402
 from torchmetrics_b200.metric import CompositionalMetric, Metric  # noqa: E402
 
-__all__ = ["Metric", "MetricCollection", "CompositionalMetric", "functional", *_cls_all]
+__all__ = ["Metric", "MetricCollection", "CompositionalMetric", "functional", "CramersV",
+           "PearsonsContingencyCoefficient", "TheilsU", "TschuprowsT", *_cls_all]

@@ -35,6 +35,7 @@ from torchmetrics_b200.classification.f_beta import (
     MultilabelF1Score,
     MultilabelFBetaScore,
 )
+from torchmetrics_b200.classification.group_fairness import BinaryFairness, BinaryGroupStatRates
 from torchmetrics_b200.classification.hamming import (
     BinaryHammingDistance,
     HammingDistance,
@@ -57,7 +58,31 @@ from torchmetrics_b200.classification.precision_recall_curve import (
     MultilabelPrecisionRecallCurve,
     PrecisionRecallCurve,
 )
+from torchmetrics_b200.classification.precision_fixed_recall import (
+    BinaryPrecisionAtFixedRecall,
+    MulticlassPrecisionAtFixedRecall,
+    MultilabelPrecisionAtFixedRecall,
+    PrecisionAtFixedRecall,
+)
+from torchmetrics_b200.classification.recall_fixed_precision import (
+    BinaryRecallAtFixedPrecision,
+    MulticlassRecallAtFixedPrecision,
+    MultilabelRecallAtFixedPrecision,
+    RecallAtFixedPrecision,
+)
 from torchmetrics_b200.classification.roc import ROC, BinaryROC, MulticlassROC, MultilabelROC
+from torchmetrics_b200.classification.sensitivity_specificity import (
+    BinarySensitivityAtSpecificity,
+    MulticlassSensitivityAtSpecificity,
+    MultilabelSensitivityAtSpecificity,
+    SensitivityAtSpecificity,
+)
+from torchmetrics_b200.classification.specificity_sensitivity import (
+    BinarySpecificityAtSensitivity,
+    MulticlassSpecificityAtSensitivity,
+    MultilabelSpecificityAtSensitivity,
+    SpecificityAtSensitivity,
+)
 from torchmetrics_b200.classification.specificity import (
     BinarySpecificity,
     MulticlassSpecificity,

@@ -28,6 +28,12 @@ from torchmetrics_b200.functional.classification.f_beta import (
     multilabel_f1_score,
     multilabel_fbeta_score,
 )
+from torchmetrics_b200.functional.classification.group_fairness import (
+    binary_fairness,
+    binary_groups_stat_rates,
+    demographic_parity,
+    equal_opportunity,
+)
 from torchmetrics_b200.functional.classification.hamming import (
     binary_hamming_distance,
     hamming_distance,
@@ -55,6 +61,30 @@ from torchmetrics_b200.functional.classification.precision_recall import (
     multilabel_recall,
     precision,
     recall,
+)
+from torchmetrics_b200.functional.classification.precision_fixed_recall import (
+    binary_precision_at_fixed_recall,
+    multiclass_precision_at_fixed_recall,
+    multilabel_precision_at_fixed_recall,
+    precision_at_fixed_recall,
+)
+from torchmetrics_b200.functional.classification.recall_fixed_precision import (
+    binary_recall_at_fixed_precision,
+    multiclass_recall_at_fixed_precision,
+    multilabel_recall_at_fixed_precision,
+    recall_at_fixed_precision,
+)
+from torchmetrics_b200.functional.classification.sensitivity_specificity import (
+    binary_sensitivity_at_specificity,
+    multiclass_sensitivity_at_specificity,
+    multilabel_sensitivity_at_specificity,
+    sensitivity_at_specificity,
+)
+from torchmetrics_b200.functional.classification.specificity_sensitivity import (
+    binary_specificity_at_sensitivity,
+    multiclass_specificity_at_sensitivity,
+    multilabel_specificity_at_sensitivity,
+    specificity_at_sensitivity,
 )
 from torchmetrics_b200.functional.classification.precision_recall_curve import (
     binary_precision_recall_curve,
