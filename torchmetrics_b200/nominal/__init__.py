@@ -10,10 +10,13 @@ from torch import Tensor
 from typing_extensions import Literal
 
 from torchmetrics_b200 import _native
-from torchmetrics_b200.functional.nominal import cramers as _cr
-from torchmetrics_b200.functional.nominal import pearson as _pe
-from torchmetrics_b200.functional.nominal import theils_u as _th
-from torchmetrics_b200.functional.nominal import tschuprows as _ts
+from importlib import import_module
+
+# the functional package re-exports functions named like its sub-modules, so fetch the modules explicitly
+_cr = import_module("torchmetrics_b200.functional.nominal.cramers")
+_pe = import_module("torchmetrics_b200.functional.nominal.pearson")
+_th = import_module("torchmetrics_b200.functional.nominal.theils_u")
+_ts = import_module("torchmetrics_b200.functional.nominal.tschuprows")
 from torchmetrics_b200.functional.nominal.utils import _handle_nan_in_data, _nominal_input_validation
 from torchmetrics_b200.metric import Metric
 
