@@ -597,6 +597,55 @@ def make_consumers2():
     b.save()
 
 
+def make_dice():
+    """Legacy `_stat_scores_update` + Dice: every input case the reference's test_dice.py / legacy
+    inputs cover, with the raw statistics and the functional's value for each valid parameter combination."""
+    from torchmetrics.functional.classification.dice import dice as ref_dice
+
+    b = Book("dice_legacy")
+    g = rng(123)
+    n, C, X = 64, 5, 7
+    inputs = {
+        "binary_probs": (torch.rand(n, generator=g), torch.randint(0, 2, (n,), generator=g), {}),
+        "multiclass_labels": (torch.randint(0, C, (n,), generator=g), torch.randint(0, C, (n,), generator=g),
+                              {"num_classes": C}),
+        "multiclass_probs": (torch.randn(n, C, generator=g).softmax(1), torch.randint(0, C, (n,), generator=g),
+                             {"num_classes": C}),
+        "multilabel_probs": (torch.rand(n, C, generator=g), torch.randint(0, 2, (n, C), generator=g),
+                             {"num_classes": C}),
+        "mdmc_labels": (torch.randint(0, C, (n, X), generator=g), torch.randint(0, C, (n, X), generator=g),
+                        {"num_classes": C}),
+        "mdmc_probs": (torch.randn(n, C, X, generator=g).softmax(1), torch.randint(0, C, (n, X), generator=g),
+                       {"num_classes": C}),
+    }
+    for kind, (p, t, base) in inputs.items():
+        for reduce in ("micro", "macro", "samples"):
+            for mdmc in ((None,) if "mdmc" not in kind else ("global", "samplewise")):
+                for ii in (None, 0):
+                    for top_k in ((None, 2) if kind in ("multiclass_probs", "mdmc_probs") else (None,)):
+                        kw = dict(base, reduce=reduce, mdmc_reduce=mdmc, ignore_index=ii, top_k=top_k)
+                        try:
+                            tp, fp, tn, fn = Fss._stat_scores_update(p, t, **kw)
+                        except Exception:
+                            continue
+                        out = {"tp": tp, "fp": fp, "tn": tn, "fn": fn}
+                        for avg in ("micro", "macro", "weighted", "none", "samples"):
+                            if ("macro" if avg in ("weighted", "none") else avg) != reduce:
+                                continue
+                            try:
+                                out[f"dice_{avg}"] = ref_dice(p, t, average=avg, mdmc_average=mdmc, ignore_index=ii,
+                                                              top_k=top_k, **base).float()
+                            except Exception:
+                                pass
+                        b.add({"kind": kind, "reduce": reduce, "mdmc_reduce": mdmc, "ignore_index": ii, "top_k": top_k,
+                               **base}, preds=p, target=t, **out)
+    # the reference's doctest (dice.py:196-199)
+    p, t = torch.tensor([2, 0, 2, 1]), torch.tensor([1, 1, 2, 0])
+    b.add({"kind": "doctest", "reduce": "micro", "mdmc_reduce": None, "ignore_index": None, "top_k": None},
+          preds=p, target=t, dice_micro=ref_dice(p, t, average="micro").float())
+    b.save()
+
+
 if __name__ == "__main__":
     make_readme()
     make_confmat()
@@ -606,3 +655,4 @@ if __name__ == "__main__":
     make_doctests()
     make_derived()
     make_consumers2()
+    make_dice()

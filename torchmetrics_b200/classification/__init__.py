@@ -25,6 +25,7 @@ from torchmetrics_b200.classification.confusion_matrix import (
     MulticlassConfusionMatrix,
     MultilabelConfusionMatrix,
 )
+from torchmetrics_b200.classification.dice import Dice
 from torchmetrics_b200.classification.f_beta import (
     BinaryF1Score,
     BinaryFBetaScore,

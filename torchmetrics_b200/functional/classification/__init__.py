@@ -18,6 +18,7 @@ from torchmetrics_b200.functional.classification.confusion_matrix import (
     multiclass_confusion_matrix,
     multilabel_confusion_matrix,
 )
+from torchmetrics_b200.functional.classification.dice import dice
 from torchmetrics_b200.functional.classification.f_beta import (
     binary_f1_score,
     binary_fbeta_score,

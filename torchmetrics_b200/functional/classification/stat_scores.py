@@ -356,6 +356,126 @@ def multilabel_stat_scores(preds: Tensor, target: Tensor, num_labels: int, thres
     return _multilabel_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
 
 
+# ======================================================================================= legacy (Dice) path
+def _del_column(data: Tensor, idx: int) -> Tensor:
+    """stat_scores.py:820-822."""
+    return torch.cat([data[:, :idx], data[:, (idx + 1):]], 1)
+
+
+def _drop_negative_ignored_indices(preds: Tensor, target: Tensor, ignore_index: int, mode) -> Tuple[Tensor, Tensor]:
+    """Remove samples whose target is a negative `ignore_index` before the case inference (stat_scores.py:825-858)."""
+    from torchmetrics_b200.utilities.enums import DataType
+
+    if mode == DataType.MULTIDIM_MULTICLASS and preds.dtype == torch.float:
+        num_classes = preds.shape[1]
+        preds = preds.transpose(1, preds.ndim - 1).reshape(-1, num_classes)
+        target = target.reshape(-1)
+    if mode in (DataType.MULTICLASS, DataType.MULTIDIM_MULTICLASS):
+        keep = target != ignore_index
+        preds, target = preds[keep], target[keep]
+    return preds, target
+
+
+def _stat_scores(preds: Tensor, target: Tensor, reduce: Optional[str] = "micro") -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """tp / fp / tn / fn of 0/1 tensors of shape (N, C) or (N, C, X) (stat_scores.py:861-906).
+
+    The reference takes four masked sums over the dims `reduce` selects.  Every combination is either a column-wise
+    count (K2: (N, C) with reduce="macro"), a whole-tensor count (K2 with one label) or a row-wise count (K2 row-wise
+    form) of a contiguous view, so each runs as one pass of those kernels."""
+    preds, target = preds.contiguous(), target.contiguous()
+    dev = preds.device
+    if preds.ndim == 2:
+        n, c = preds.shape
+        if reduce == "micro":
+            stats = torch.zeros(4, 1, dtype=torch.int64, device=dev)
+            _native.stat_scores_update_(stats, preds, target, 1, 0.5, None, _native.PROB_AS_IS, report_values=False)
+            return stats[0, 0], stats[1, 0], stats[2, 0], stats[3, 0]
+        if reduce == "macro":
+            stats = torch.zeros(4, c, dtype=torch.int64, device=dev)
+            if n:
+                _native.stat_scores_update_(stats, preds, target, c, 0.5, None, _native.PROB_AS_IS,
+                                            report_values=False)
+            return stats[0], stats[1], stats[2], stats[3]
+        rows = _native.stat_scores_rows(preds, target, c)  # "samples": one row per sample
+        return rows[0], rows[1], rows[2], rows[3]
+    n, c, x = preds.shape
+    if reduce == "micro":
+        rows = _native.stat_scores_rows(preds, target, c * x)
+        return rows[0], rows[1], rows[2], rows[3]
+    if reduce == "macro":
+        rows = _native.stat_scores_rows(preds, target, x).view(4, n, c)
+        return rows[0], rows[1], rows[2], rows[3]
+    # "samples": the class dimension is summed out -> make it the fastest one
+    rows = _native.stat_scores_rows(preds.transpose(1, 2).contiguous(), target.transpose(1, 2).contiguous(), c)
+    rows = rows.view(4, n, x)
+    return rows[0], rows[1], rows[2], rows[3]
+
+
+def _stat_scores_update(preds: Tensor, target: Tensor, reduce: Optional[str] = "micro",
+                        mdmc_reduce: Optional[str] = None, num_classes: Optional[int] = None,
+                        top_k: Optional[int] = 1, threshold: float = 0.5, multiclass: Optional[bool] = None,
+                        ignore_index: Optional[int] = None, mode=None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """The legacy update behind Dice (stat_scores.py:909-995): case inference, then `_stat_scores`."""
+    from torchmetrics_b200.utilities.checks import _input_format_classification
+
+    negative_dropped = False
+    if ignore_index is not None and ignore_index < 0 and mode is not None:
+        preds, target = _drop_negative_ignored_indices(preds, target, ignore_index, mode)
+        negative_dropped = True
+    preds, target, _ = _input_format_classification(preds, target, threshold=threshold, num_classes=num_classes,
+                                                    multiclass=multiclass, top_k=top_k, ignore_index=ignore_index)
+    if ignore_index is not None and ignore_index >= preds.shape[1]:
+        raise ValueError(f"The `ignore_index` {ignore_index} is not valid for inputs with {preds.shape[1]} classes")
+    if ignore_index is not None and preds.shape[1] == 1:
+        raise ValueError("You can not use `ignore_index` with binary data.")
+    if preds.ndim == 3:
+        if not mdmc_reduce:
+            raise ValueError(
+                "When your inputs are multi-dimensional multi-class, you have to set the `mdmc_reduce` parameter"
+            )
+        if mdmc_reduce == "global":
+            preds = torch.transpose(preds, 1, 2).reshape(-1, preds.shape[1])
+            target = torch.transpose(target, 1, 2).reshape(-1, target.shape[1])
+    drop_column = ignore_index is not None and not negative_dropped
+    if drop_column and reduce != "macro":
+        preds, target = _del_column(preds, ignore_index), _del_column(target, ignore_index)
+    tp, fp, tn, fn = _stat_scores(preds, target, reduce=reduce)
+    if drop_column and reduce == "macro":
+        for stat in (tp, fp, tn, fn):
+            stat[..., ignore_index] = -1
+    return tp, fp, tn, fn
+
+
+def _stat_scores_compute(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor) -> Tensor:
+    """[tp, fp, tn, fn, support] along a new last dim, negatives (ignored classes) kept at -1 (:998-1018)."""
+    out = torch.stack([tp, fp, tn, fn, tp + fn], dim=-1)
+    return torch.where(out < 0, torch.full_like(out, -1), out)
+
+
+def _reduce_stat_scores(numerator: Tensor, denominator: Tensor, weights: Optional[Tensor], average: Optional[str],
+                        mdmc_average: Optional[str], zero_division: int = 0) -> Tensor:
+    """numerator / denominator (optionally weighted) with ignored (< 0) and empty (== 0) denominators handled
+    (stat_scores.py:1021-1075)."""
+    numerator, denominator = numerator.float(), denominator.float()
+    empty = denominator == 0
+    ignored = denominator < 0
+    weights = torch.ones_like(denominator) if weights is None else weights.float()
+    numerator = torch.where(empty, torch.full_like(numerator, float(zero_division)), numerator)
+    denominator = torch.where(empty | ignored, torch.ones_like(denominator), denominator)
+    weights = torch.where(ignored, torch.zeros_like(weights), weights)
+    if average not in ("micro", "none", None):
+        weights = weights / weights.sum(dim=-1, keepdim=True)
+    scores = weights * (numerator / denominator)
+    # sum(weights) == 0: the only class present was ignored under average="weighted"
+    scores = torch.where(torch.isnan(scores), torch.full_like(scores, float(zero_division)), scores)
+    if mdmc_average == "samplewise":
+        scores = scores.mean(dim=0)
+        ignored = ignored.sum(dim=0).bool()
+    if average in ("none", None):
+        return torch.where(ignored, torch.full_like(scores, float("nan")), scores)
+    return scores.sum()
+
+
 # ======================================================================================= task wrapper
 def stat_scores(preds: Tensor, target: Tensor, task: Literal["binary", "multiclass", "multilabel"],
                 threshold: float = 0.5, num_classes: Optional[int] = None, num_labels: Optional[int] = None,

@@ -88,3 +88,12 @@ def select_topk(prob_tensor: Tensor, topk: int = 1, dim: int = 1) -> Tensor:
     else:
         idx = prob_tensor.topk(k=topk, dim=dim).indices
     return torch.zeros_like(prob_tensor, dtype=torch.int32).scatter_(dim, idx, 1)
+
+
+def to_onehot(label_tensor: Tensor, num_classes: Optional[int] = None) -> Tensor:
+    """(N, d1, ...) labels -> (N, C, d1, ...) 0/1 tensor of the labels' dtype (data.py:80-111)."""
+    if num_classes is None:
+        num_classes = int(label_tensor.max().detach().item() + 1)
+    out = torch.zeros(label_tensor.shape[0], num_classes, *label_tensor.shape[1:], dtype=label_tensor.dtype,
+                      device=label_tensor.device)
+    return out.scatter_(1, label_tensor.long().unsqueeze(1).expand_as(out), 1.0)

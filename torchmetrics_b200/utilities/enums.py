@@ -45,3 +45,37 @@ class ClassificationTaskNoMultilabel(EnumStr):
     @staticmethod
     def _name() -> str:
         return "Classification"
+
+
+class DataType(EnumStr):
+    """Input case inferred by the legacy `_input_format_classification` (reference: utilities/enums.py:56-73)."""
+
+    BINARY = "binary"
+    MULTILABEL = "multi-label"
+    MULTICLASS = "multi-class"
+    MULTIDIM_MULTICLASS = "multi-dim multi-class"
+
+    @staticmethod
+    def _name() -> str:
+        return "Data type"
+
+
+class AverageMethod(EnumStr):
+    MICRO = "micro"
+    MACRO = "macro"
+    WEIGHTED = "weighted"
+    NONE = None
+    SAMPLES = "samples"
+
+    @staticmethod
+    def _name() -> str:
+        return "Average method"
+
+
+class MDMCAverageMethod(EnumStr):
+    GLOBAL = "global"
+    SAMPLEWISE = "samplewise"
+
+    @staticmethod
+    def _name() -> str:
+        return "MDMC Average method"
