@@ -85,39 +85,189 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+CONFIG = {"workload": "configs[1]: MulticlassConfusionMatrix num_classes=1000, 2^24-sample int64 batches",
+          "samples_per_step_per_gpu": BATCH, "validate_args": False}
+
+
+def _import_reference():
+    """The unmodified reference (pure Python): TM_REFERENCE_SRC, /root/reference/src, or the copy pip-installed into
+    baseline/_ref (which travels to the GPU box), with the 4-symbol lightning_utilities stand-in the golden-vector
+    generator uses.  Returns the module or None."""
+    shim = os.path.join(ROOT, "tests", "golden", "_refshim")
+    for cand in (os.environ.get("TM_REFERENCE_SRC"), "/root/reference/src", os.path.join(ROOT, "baseline", "_ref")):
+        if cand and os.path.isdir(os.path.join(cand, "torchmetrics")):
+            sys.path[:0] = [cand, shim]
+            try:
+                import torchmetrics
+
+                return torchmetrics, cand
+            except Exception:
+                del sys.path[:2]
+    return None, None
+
+
+def _reference_steps(args):
+    """(value, seconds per step, description) of the reference's own CPU implementation, or None."""
+    ref, where = _import_reference()
+    if ref is None:
+        return None
+    import torch
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    g = torch.Generator().manual_seed(1234)
+    batches = [(torch.randint(0, NUM_CLASSES, (BATCH,), generator=g), torch.randint(0, NUM_CLASSES, (BATCH,), generator=g))
+               for _ in range(2)]
+    metric = ref.classification.MulticlassConfusionMatrix(num_classes=NUM_CLASSES, validate_args=False)
+    for i in range(args.warmup):
+        metric.update(*batches[i % 2])
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        metric.update(*batches[i % 2])
+    dt = time.perf_counter() - t0
+    assert int(metric.confmat.sum()) == (args.warmup + args.steps) * BATCH
+    return args.steps * BATCH / dt, dt / args.steps, torch.get_num_threads(), (
+        f"{args.steps} full 2^24-sample batches through torchmetrics {ref.__version__} "
+        f"MulticlassConfusionMatrix.update on CPU tensors ({where})")
+
+
 def run_reference(args, rank, world):
-    """CPU arm: oracle/oracle.c (C + OpenMP restatement of confusion_matrix.py:333-337) on the box's host cores."""
+    """CPU arm: the reference's own code on the box's host cores (kind "reference"); if it cannot be imported, the
+    C + OpenMP restatement oracle/oracle.c (kind "port")."""
     if rank != 0:
         return
+    res = _reference_steps(args)
+    if res is not None:
+        value, step_s, cores, sample = res
+        kind = "reference"
+    else:
+        import numpy as np
+
+        from oracle import oracle_c as OC
+
+        # torchrun exports OMP_NUM_THREADS=1 to its children; the CPU arm is meant to use every host core
+        OC.set_num_threads(os.cpu_count() or 1)
+        rng = np.random.default_rng(1234)
+        batches = [(rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)) for _ in range(2)]
+        state = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)
+        for i in range(args.warmup):
+            OC.confmat_update(*batches[i % 2], NUM_CLASSES, out=state)
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            OC.confmat_update(*batches[i % 2], NUM_CLASSES, out=state)
+        dt = time.perf_counter() - t0
+        assert int(state.sum()) == (args.warmup + args.steps) * BATCH
+        value, step_s, cores, kind = args.steps * BATCH / dt, dt / args.steps, OC.num_threads(), "port"
+        sample = f"{args.steps} full 2^24-sample batches (oracle/oracle.c, OpenMP)"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": dict(CONFIG),
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "note": "CPU arm runs on rank 0 only, one batch per step",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_sample(seconds=10.0):
+    """Bounded CPU sample of the same workload on the box's host cores: the reference's own code when it can be
+    imported (kind "reference"), else the C/OpenMP port."""
+    ref, where = _import_reference()
+    if ref is not None:
+        import torch
+
+        torch.set_num_threads(os.cpu_count() or 1)
+        g = torch.Generator().manual_seed(1234)
+        p = torch.randint(0, NUM_CLASSES, (BATCH,), generator=g)
+        t = torch.randint(0, NUM_CLASSES, (BATCH,), generator=g)
+        m = ref.classification.MulticlassConfusionMatrix(num_classes=NUM_CLASSES, validate_args=False)
+        m.update(p, t)
+        t0, reps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < seconds and reps < 200:
+            m.update(p, t)
+            reps += 1
+        dt = time.perf_counter() - t0
+        return {"value": reps * BATCH / dt, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "reference",
+                "sample": f"{reps} repetitions of one 2^24-sample batch (~{seconds:.0f} s) through torchmetrics "
+                          f"{ref.__version__} MulticlassConfusionMatrix.update on CPU tensors ({where})"}
     import numpy as np
 
     from oracle import oracle_c as OC
 
-    # torchrun exports OMP_NUM_THREADS=1 to its children; the CPU arm is meant to use every host core
     OC.set_num_threads(os.cpu_count() or 1)
     rng = np.random.default_rng(1234)
-    batches = [(rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)) for _ in range(2)]
-    state = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)
-    for i in range(args.warmup):
-        OC.confmat_update(*batches[i % 2], NUM_CLASSES, out=state)
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        OC.confmat_update(*batches[i % 2], NUM_CLASSES, out=state)
+    p, t = rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)
+    st = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)
+    OC.confmat_update(p, t, NUM_CLASSES, out=st)
+    t0, reps = time.perf_counter(), 0
+    while time.perf_counter() - t0 < seconds and reps < 200:
+        OC.confmat_update(p, t, NUM_CLASSES, out=st)
+        reps += 1
     dt = time.perf_counter() - t0
-    assert int(state.sum()) == (args.warmup + args.steps) * BATCH
-    value = args.steps * BATCH / dt
-    line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": {"workload": "configs[1]: MulticlassConfusionMatrix num_classes=1000, 2^24-sample int64 batches",
-                   "samples_per_step": BATCH, "note": "CPU arm runs on rank 0 only, one batch per step"},
-        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": OC.num_threads(), "kind": "port",
-                         "sample": f"{args.steps} full 2^24-sample batches (oracle/oracle.c, OpenMP)"},
-        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
-    print(json.dumps(line), flush=True)
+    return {"value": reps * BATCH / dt, "unit": "samples/s", "cores": OC.num_threads(), "kind": "port",
+            "sample": f"{reps} repetitions of one 2^24-sample batch (~{seconds:.0f} s), oracle/oracle.c with OpenMP"}
+
+
+def measure_sync(tm, dist, dev, local_rank, world, confmat_metric, binned_metric, max_over_ranks):
+    """SURVEY 8(d) "Sync us": for each state size, `Metric.sync()` of this package next to (a) the reference protocol
+    on the same NCCL group (one gather per state: `Metric._sync_dist(gather_all_tensors)`, metric.py:427-457) and
+    (b) the bare collective on a tensor of the same bytes.  Median of 30, host-timed around a stream sync AND
+    device-timed with CUDA events, max over ranks."""
+    import torch
+
+    from torchmetrics_b200.utilities.distributed import gather_all_tensors
+
+    def timed(fn, undo=None, reps=30):
+        host, devt = [], []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            dist.barrier(device_ids=[local_rank])
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            host.append((time.perf_counter() - t0) * 1e6)
+            devt.append(a.elapsed_time(b) * 1e3)
+            if undo:
+                undo()
+        return {"host_us": max_over_ranks(statistics.median(host)), "device_us": max_over_ranks(statistics.median(devt))}
+
+    def metric_rows(m):
+        def legacy():
+            m._cache = {name: getattr(m, name) for name in m._defaults}
+            m._sync_dist(gather_all_tensors)
+            m._is_synced = True
+
+        return {"ours": timed(m.sync, m.unsync), "reference_protocol": timed(legacy, m.unsync)}
+
+    out = {}
+    # 8 MB confusion matrix, 6.4 KB binned curve state
+    for key, m, nbytes in (("confmat_8MB", confmat_metric, NUM_CLASSES * NUM_CLASSES * 8),
+                           ("binned_6.4KB", binned_metric, 200 * 4 * 8)):
+        buf = torch.zeros(nbytes // 8, dtype=torch.int64, device=dev)
+        out[key] = dict(metric_rows(m), bare_all_reduce=timed(lambda: dist.all_reduce(buf)), bytes=nbytes)
+    # 4 x (100,) int64 = 3.2 KB: the multilabel collection's shared state
+    L = 100
+    ss = tm.MultilabelStatScores(num_labels=L, validate_args=False).to(dev)
+    ss.update(torch.rand(64, L, device=dev), torch.randint(0, 2, (64, L), device=dev))
+    buf = torch.zeros(4 * L, dtype=torch.int64, device=dev)
+    out["stat_scores_3.2KB"] = dict(metric_rows(ss), bare_all_reduce=timed(lambda: dist.all_reduce(buf)), bytes=3200)
+    # cat states: 2^23 x (4 + 1) B per rank (scores fp32 + positives uint8) of the exact curve
+    n = 1 << 23
+    ex = tm.BinaryAUROC(thresholds=None, validate_args=False).to(dev)
+    ex.update(torch.rand(n, device=dev), torch.randint(0, 2, (n,), device=dev))
+    per_rank = sum(t.numel() * t.element_size() for t in (ex.preds[0], ex.target[0]))
+    send = torch.zeros(per_rank, dtype=torch.uint8, device=dev)
+    recv = torch.empty(per_rank * world, dtype=torch.uint8, device=dev)
+    out["cat_2p23_per_rank"] = dict(metric_rows(ex),
+                                    bare_all_gather=timed(lambda: dist.all_gather_into_tensor(recv, send)),
+                                    bytes_per_rank=per_rank)
+    out["note"] = ("ours = Metric.sync() (packed all_reduce / padded all_gather); reference_protocol = one "
+                   "gather_all_tensors + stack + reduce per state on the same group; bare = the collective alone")
+    return out
 
 
 def main():
@@ -182,7 +332,18 @@ def main():
     e1.record()
     barrier()
     step_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
-    assert int(metric.compute().sum()) == (args.warmup + args.steps) * BATCH * world  # synced count, exact
+    # parity of the timed state itself: the whole synced 1000 x 1000 matrix against torch.bincount(t*C+p) of the
+    # batches this rank fed, summed over the ranks (confusion_matrix.py:333-337), bit for bit
+    want = torch.zeros(NUM_CLASSES * NUM_CLASSES, dtype=torch.int64, device=dev)
+    for j, (bp, bt) in enumerate(batches):
+        times = sum(1 for i in range(args.warmup) if i % 2 == j) + sum(1 for i in range(args.steps) if i % 2 == j)
+        want += times * torch.bincount(bt * NUM_CLASSES + bp, minlength=NUM_CLASSES * NUM_CLASSES)
+    if world > 1:
+        dist.all_reduce(want)
+    synced = metric.compute()
+    assert torch.equal(synced.reshape(-1), want), "synced confusion matrix differs from torch.bincount"
+    assert int(synced.sum()) == (args.warmup + args.steps) * BATCH * world
+    del want, synced
     value = BATCH * world / (step_ms * 1e-3)
 
     # dominant kernel alone (roofline.achieved): same launches through the C ABI, CUDA events on the launch stream
@@ -310,23 +471,8 @@ def main():
             "auroc": float(out["BinaryAUROC"]), "ap": float(out["BinaryAveragePrecision"]),
         }
         if world > 1:
-            def sync_us(m, reps=30):
-                ts = []
-                for _ in range(reps):
-                    torch.cuda.synchronize()
-                    dist.barrier(device_ids=[local_rank])
-                    t0 = time.perf_counter()
-                    m.sync()
-                    torch.cuda.synchronize()
-                    ts.append((time.perf_counter() - t0) * 1e6)
-                    m.unsync()
-                return max_over_ranks(statistics.median(ts))
-
-            extra["sync_us"] = {
-                "confmat_8MB_one_allreduce": sync_us(metric),
-                "binned_6.4KB_one_allreduce": sync_us(coll.__getitem__("BinaryAUROC", copy_state=False)),
-                "note": "median host-timed Metric.sync() incl. stream sync, max over ranks",
-            }
+            extra["sync_us"] = measure_sync(tm, dist, dev, local_rank, world, metric,
+                                            coll.__getitem__("BinaryAUROC", copy_state=False), max_over_ranks)
         del preds, target, coll
         torch.cuda.empty_cache()
 
@@ -351,12 +497,15 @@ def main():
         barrier()
         cms = max_over_ranks(c0.elapsed_time(c1)) / reps
         mcoll.compute()  # warm-up (lazy kernel loading of the small torch reducers)
-        mcoll.update(mp, mt)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        res = mcoll.compute()
-        torch.cuda.synchronize()
-        compute_ms = (time.perf_counter() - t0) * 1e3
+        ctimes = []
+        for _ in range(5):
+            mcoll.update(mp, mt)
+            barrier()  # ranks aligned: the number below is compute + sync, not waiting for a slower rank's update
+            t0 = time.perf_counter()
+            res = mcoll.compute()
+            torch.cuda.synchronize()
+            ctimes.append((time.perf_counter() - t0) * 1e3)
+        compute_ms = max_over_ranks(statistics.median(ctimes))
         extra["multilabel_collection_L100"] = {
             "workload": "configs[4]: MetricCollection[MultilabelStatScores, Precision, Recall, F1] num_labels=100, "
                         "2^23-row batches per rank (weak), one compute group => one K2 pass per update",
@@ -394,37 +543,42 @@ def main():
             "update_ms": upd_ms, "compute_ms_incl_gather": cmp_ms, "value": (1 << 26) / (cmp_ms * 1e-3),
             "unit": "samples/s (compute)", "auroc": val,
         }
+        if world > 1:
+            # the same scores without replication: range partition + local sort (distributed_exact="partition")
+            pm = tm.BinaryAUROC(thresholds=None, validate_args=False, distributed_exact="partition").to(dev)
+            pm.update(ep, et)
+            pm.compute()
+            ptimes = []
+            for _ in range(3):
+                pm._computed = None
+                barrier()
+                t0 = time.perf_counter()
+                pval = float(pm.compute())
+                torch.cuda.synchronize()
+                ptimes.append((time.perf_counter() - t0) * 1e3)
+            pms = max_over_ranks(statistics.median(ptimes))
+            assert abs(pval - val) < 1e-6, (pval, val)
+            extra["exact_auroc_2p26_partitioned"] = {
+                "workload": "configs[3] with distributed_exact='partition': splitters from a sample, all-to-all range "
+                            "partition (5 B/sample), local sort + reduce (K4b with offsets), scalar all_reduce",
+                "compute_ms": pms, "value": (1 << 26) / (pms * 1e-3), "unit": "samples/s (compute)", "auroc": pval,
+            }
+            del pm
         del ep, et, em
 
     # ------------------------------------------------------------------ CPU baseline (rank 0, N=1 only)
     cpu_baseline = None
     if rank == 0 and world == 1:
-        import numpy as np
-
-        from oracle import oracle_c as OC
-
-        OC.set_num_threads(os.cpu_count() or 1)
-        rng = np.random.default_rng(1234)
-        p, t = rng.integers(0, NUM_CLASSES, BATCH), rng.integers(0, NUM_CLASSES, BATCH)
-        st = np.zeros((NUM_CLASSES, NUM_CLASSES), dtype=np.int64)
-        OC.confmat_update(p, t, NUM_CLASSES, out=st)
-        t0, reps = time.perf_counter(), 0
-        while time.perf_counter() - t0 < 10.0 and reps < 200:
-            OC.confmat_update(p, t, NUM_CLASSES, out=st)
-            reps += 1
-        dt = time.perf_counter() - t0
-        cpu_baseline = {"value": reps * BATCH / dt, "unit": "samples/s", "cores": OC.num_threads(), "kind": "port",
-                        "sample": f"{reps} repetitions of one 2^24-sample batch (~10 s), oracle/oracle.c with OpenMP"}
+        cpu_baseline = cpu_baseline_sample()
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-            "config": {"workload": "configs[1]: MulticlassConfusionMatrix num_classes=1000, 2^24-sample int64 batches",
-                       "samples_per_step_per_gpu": BATCH, "validate_args": False,
-                       "l2_policy": "inputs larger than L2: 268 MB read per step, two alternating batches (L2 126 MB)",
-                       "api": "torchmetrics_b200.MulticlassConfusionMatrix.update"},
+            "config": dict(CONFIG),
+            "l2_policy": "inputs larger than L2: 268 MB read per step, two alternating batches (L2 126 MB)",
+            "api": "torchmetrics_b200.MulticlassConfusionMatrix.update",
             "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "extra": extra,
         }

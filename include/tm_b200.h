@@ -195,6 +195,16 @@ TMB_API int tmb_exact_auroc_ap(const float* preds_dev, const void* target_dev, i
                                int64_t pos_label, double* out4_dev, void* workspace_dev, size_t workspace_bytes,
                                void* stream);
 
+/* K4b for one SHARD of a score range partition (distributed exact curve, SURVEY.md section 8(f) N4: no reference
+ * counterpart does this step - the reference gathers every sample on every rank, metric.py:427-457, and sorts the
+ * whole set there).  The shard holds all samples of a contiguous score range; tp_offset / fp_offset are the numbers
+ * of positives / negatives ranked above it (summed over the shards with higher scores).  The two sums of out4 are
+ * then this shard's terms of the GLOBAL sums, so adding out4[0] and out4[1] over the shards gives exactly what
+ * tmb_exact_auroc_ap returns for the concatenated input; out4[2], out4[3] stay local (positives, distinct scores). */
+TMB_API int tmb_exact_auroc_ap_offset(const float* preds_dev, const void* target_dev, int target_dtype, int64_t n,
+                                      int64_t pos_label, int64_t tp_offset, int64_t fp_offset, double* out4_dev,
+                                      void* workspace_dev, size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * K1c  per-class tp / fp / tn / fn of multiclass label pairs, without the C x C matrix.
  * Replaces: functional/classification/stat_scores.py:395-419, the non-one-hot branch of

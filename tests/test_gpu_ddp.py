@@ -97,6 +97,34 @@ def _body_sum_and_cat_states(rank, world):
     assert np.array_equal(thr.cpu().numpy(), wthr)
 
 
+def _body_partitioned_exact(rank, world):
+    """distributed_exact="partition": range partition + local sort, against the gathered result and the oracle."""
+    import numpy as np
+
+    import torchmetrics_b200 as tm
+    from oracle import oracle_np as O
+
+    dev = torch.device("cuda", rank)
+    for quantise in (False, True):  # heavy ties must stay on one rank
+        p, t, _, _ = (x.to(dev) for x in _data(rank, 200_000, world))
+        ap_, at_, _, _ = _data(None, 200_000, world)
+        if quantise:
+            p, ap_ = (p * 64).floor() / 64, (ap_ * 64).floor() / 64
+        part_auc = tm.BinaryAUROC(thresholds=None, distributed_exact="partition").to(dev)
+        part_ap = tm.BinaryAveragePrecision(thresholds=None, distributed_exact="partition").to(dev)
+        gath_auc = tm.BinaryAUROC(thresholds=None).to(dev)
+        gath_ap = tm.BinaryAveragePrecision(thresholds=None).to(dev)
+        for m in (part_auc, part_ap, gath_auc, gath_ap):
+            m.update(p[: p.numel() // 2], t[: p.numel() // 2])
+            m.update(p[p.numel() // 2:], t[p.numel() // 2:])
+        a, b = float(part_auc.compute()), float(part_ap.compute())
+        assert abs(a - float(gath_auc.compute())) < 1e-6 and abs(b - float(gath_ap.compute())) < 1e-6
+        assert abs(a - float(O.binary_auroc_exact(ap_.numpy(), at_.numpy(), np.float64))) < 1e-6
+        assert abs(b - float(O.binary_average_precision_exact(ap_.numpy(), at_.numpy(), np.float64))) < 1e-6
+        # the states stayed local: nothing was gathered
+        assert sum(x.numel() for x in part_auc.preds) == p.numel()
+
+
 def _body_multilabel_collection(rank, world):
     import torchmetrics_b200 as tm
 
@@ -118,7 +146,7 @@ def _body_multilabel_collection(rank, world):
 
 
 @pytest.mark.parametrize("world", WORLDS)
-@pytest.mark.parametrize("body", ["_body_sum_and_cat_states", "_body_multilabel_collection"])
+@pytest.mark.parametrize("body", ["_body_sum_and_cat_states", "_body_multilabel_collection", "_body_partitioned_exact"])
 def test_nccl_sync(body, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")

@@ -77,6 +77,8 @@ _SIGNATURES = {
                                    _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
     "tmb_exact_auroc_ap": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p,
                                       _c.c_void_p, _c.c_size_t, _c.c_void_p]),
+    "tmb_exact_auroc_ap_offset": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_int64,
+                                             _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
     "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                           _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,
@@ -479,9 +481,11 @@ def exact_curve(preds: Tensor, target: Tensor, pos_label: int = 1):
     return fps[:d], tps[:d], thr[:d]
 
 
-def exact_auroc_ap(preds: Tensor, target: Tensor, pos_label: int = 1) -> Tuple[float, float, float, float]:
+def exact_auroc_ap(preds: Tensor, target: Tensor, pos_label: int = 1, tp_offset: int = 0,
+                   fp_offset: int = 0) -> Tuple[float, float, float, float]:
     """(sum_k dFP_k (TP_k + TP_{k-1}),  sum_k dTP_k TP_k / (TP_k + FP_k),  positives,  distinct scores) of the exact
-    curve, reduced on the device (K4b): the curve itself is never written.  One 32-byte read back."""
+    curve, reduced on the device (K4b): the curve itself is never written.  One 32-byte read back.
+    `tp_offset` / `fp_offset`: counts ranked above this input when it is one shard of a score-range partition."""
     dev = require_cuda(preds, target)
     preds = _aligned(preds.detach().reshape(-1).to(torch.float32))
     target = as_kernel_labels(target.reshape(-1))
@@ -491,9 +495,10 @@ def exact_auroc_ap(preds: Tensor, target: Tensor, pos_label: int = 1) -> Tuple[f
     out4 = torch.empty(4, dtype=torch.float64, device=dev)
     ws = torch.empty(lib.tmb_exact_curve_workspace_bytes(n), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        rc = lib.tmb_exact_auroc_ap(preds.data_ptr(), target.data_ptr(), dtype_code(target), n, int(pos_label),
-                                    out4.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
-    _check(rc, "tmb_exact_auroc_ap")
+        rc = lib.tmb_exact_auroc_ap_offset(preds.data_ptr(), target.data_ptr(), dtype_code(target), n, int(pos_label),
+                                           int(tp_offset), int(fp_offset), out4.data_ptr(), ws.data_ptr(), ws.numel(),
+                                           _stream_ptr(dev))
+    _check(rc, "tmb_exact_auroc_ap_offset")
     a, b, c, d = out4.tolist()
     return a, b, c, d
 

@@ -2,6 +2,7 @@
 from importlib import import_module
 from typing import Any, Optional
 
+import torch
 from torch import Tensor
 from typing_extensions import Literal
 
@@ -32,7 +33,18 @@ class BinaryAUROC(BinaryPrecisionRecallCurve):
         self.validate_args = validate_args
         self.max_fpr = max_fpr
 
+    _supports_partition = True
+
     def compute(self) -> Tensor:
+        sums = self._partitioned_sums()
+        if sums is not None:
+            if self.max_fpr not in (None, 1):
+                raise ValueError("`distributed_exact='partition'` does not support `max_fpr`")
+            area2, _, npos, n = sums
+            nneg = n - npos
+            if npos <= 0 or nneg <= 0:  # the reference warns and integrates an all-zero curve (roc.py:60-75)
+                return torch.tensor(0.0, device=self.device)
+            return torch.tensor(area2 / (2.0 * npos * nneg), dtype=torch.float32, device=self.device)
         return F._binary_auroc_compute(self._state(), self.thresholds, self.max_fpr)
 
 

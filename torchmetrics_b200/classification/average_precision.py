@@ -2,6 +2,7 @@
 from importlib import import_module
 from typing import Any, Optional
 
+import torch
 from torch import Tensor
 from typing_extensions import Literal
 
@@ -24,7 +25,15 @@ class BinaryAveragePrecision(BinaryPrecisionRecallCurve):
     plot_lower_bound = 0.0
     plot_upper_bound = 1.0
 
+    _supports_partition = True
+
     def compute(self) -> Tensor:
+        sums = self._partitioned_sums()
+        if sums is not None:
+            _, apsum, npos, _ = sums
+            if npos <= 0:  # no positive sample anywhere: recall is 0/0 (average_precision.py:39-46 gives nan)
+                return torch.tensor(float("nan"), device=self.device)
+            return torch.tensor(apsum / npos, dtype=torch.float32, device=self.device)
         return F._binary_average_precision_compute(self._state(), self.thresholds)
 
 

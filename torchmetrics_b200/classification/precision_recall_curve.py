@@ -50,9 +50,23 @@ class _CurveBase(Metric):
 
 
 class BinaryPrecisionRecallCurve(_CurveBase):
+    # AUROC / AveragePrecision can finish the exact curve without gathering every sample on every rank
+    _supports_partition = False
+
     def __init__(self, thresholds: _Thresholds = None, ignore_index: Optional[int] = None, validate_args: bool = True,
                  **kwargs: Any) -> None:
+        # distributed_exact="partition" (extension): with thresholds=None, `compute` range-partitions
+        # the samples by score across the ranks instead of all_gathering them; the states stay local
+        mode = kwargs.pop("distributed_exact", "gather")
+        if mode not in ("gather", "partition"):
+            raise ValueError(f"Expected `distributed_exact` to be 'gather' or 'partition', got {mode}")
+        if mode == "partition":
+            if thresholds is not None or not self._supports_partition:
+                raise ValueError("`distributed_exact='partition'` applies to BinaryAUROC / BinaryAveragePrecision with "
+                                 "`thresholds=None` (binned states are a single all_reduce already)")
+            kwargs["sync_on_compute"] = False
         super().__init__(**kwargs)
+        self.distributed_exact = mode
         if validate_args:
             F._binary_precision_recall_curve_arg_validation(thresholds, ignore_index)
         self.ignore_index = ignore_index
@@ -67,7 +81,9 @@ class BinaryPrecisionRecallCurve(_CurveBase):
         if self.thresholds is None:
             p, t, _ = F._binary_precision_recall_curve_format(preds, target, None, self.ignore_index)
             self.preds.append(p)
-            self.target.append(t)
+            # the exact curve only ever asks `target == 1` (precision_recall_curve.py:66): keep that answer as one
+            # byte per sample - an eighth of the int64 labels in memory and on the wire of the cat-state gather
+            self.target.append((t == 1).to(torch.uint8))
         else:
             def step(out: Tensor) -> None:
                 F._binary_precision_recall_curve_update_fused(preds, target, self.thresholds, self.ignore_index,
@@ -81,6 +97,21 @@ class BinaryPrecisionRecallCurve(_CurveBase):
             return dim_zero_cat(self.preds), dim_zero_cat(self.target)
         self._check_device_status()
         return self.confmat
+
+    def _partitioned_sums(self) -> Optional[Tuple[float, float, float, float]]:
+        """(area2, ap_sum, positives, samples) over all ranks in partition mode, None otherwise."""
+        import torch.distributed as dist
+
+        if self.distributed_exact != "partition" or not (dist.is_available() and dist.is_initialized()):
+            return None
+        from torchmetrics_b200.functional.classification._exact import partitioned_exact_sums
+
+        if len(self.preds):
+            p, t = dim_zero_cat(self.preds), dim_zero_cat(self.target)
+        else:
+            p = torch.empty(0, device=self.device)
+            t = torch.empty(0, dtype=torch.uint8, device=self.device)
+        return partitioned_exact_sums(p, t, self.process_group)
 
     def compute(self) -> Tuple[Tensor, Tensor, Tensor]:
         return F._binary_precision_recall_curve_compute(self._state(), self.thresholds)

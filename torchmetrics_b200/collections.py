@@ -180,8 +180,11 @@ class MetricCollection(ModuleDict):
                 for m in followers:          # followers read the leader's synced tensors
                     for state in ld._defaults:
                         setattr(m, state, getattr(ld, state))
+        # link the group members to their leader's state once; the loops below walk the module table directly
+        self._compute_groups_create_state_ref(False)
+        members = list(self._modules.items())
         try:
-            for k, m in self.items(keep_base=True, copy_state=False):
+            for k, m in members:
                 result[k] = m.compute() if method_name == "compute" else m(*args, **m._filter_kwargs(**kwargs))
         finally:
             if fused:
@@ -195,7 +198,7 @@ class MetricCollection(ModuleDict):
 
         _, duplicates = _flatten_dict(result)
         flat: Dict[str, Any] = {}
-        for k, m in self.items(keep_base=True, copy_state=False):
+        for k, m in members:
             res = result[k]
             if not isinstance(res, dict):
                 flat[k] = res

@@ -661,7 +661,7 @@ __global__ void __launch_bounds__(kSortThreads) k4_reduce_tiles(const u32* __res
                                                                 const u64* __restrict__ tile_last_idx1,
                                                                 const u64* __restrict__ tile_last_tp,
                                                                 double* __restrict__ tile_auc,
-                                                                double* __restrict__ tile_ap) {
+                                                                double* __restrict__ tile_ap, u64 tp_off, u64 fp_off) {
   __shared__ u32 wp[kSortWarps], wl[kSortWarps], wt[kSortWarps];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long long tbase = (long long)blockIdx.x * kSortTile;
@@ -721,13 +721,16 @@ __global__ void __launch_bounds__(kSortThreads) k4_reduce_tiles(const u32* __res
     tpp = tile_last_tp[blockIdx.x];
     fpp = tile_last_idx1[blockIdx.x] - tpp;
   }
+  // counts of a score range sorted elsewhere (distributed curve: everything ranked above this shard)
+  tpp += tp_off;
+  fpp += fp_off;
   double auc = 0.0, ap = 0.0;
   u32 e = it.ends;
   while (e) {
     const u32 r = __ffs(e) - 1;
     e &= e - 1;
-    const u64 tpk = pos0 + tp_before + __popc(it.labels & (0xffffffffu >> (31u - r)));
-    const u64 idx1 = (u64)tbase + j0 + r + 1;  // TP_k + FP_k
+    const u64 tpk = tp_off + pos0 + tp_before + __popc(it.labels & (0xffffffffu >> (31u - r)));
+    const u64 idx1 = tp_off + fp_off + (u64)tbase + j0 + r + 1;  // TP_k + FP_k
     const u64 fpk = idx1 - tpk;
     auc += (double)(fpk - fpp) * (double)(tpk + tpp);
     if (tpk != tpp) ap += (double)(tpk - tpp) * ((double)tpk / (double)idx1);
@@ -927,9 +930,21 @@ extern "C" int tmb_exact_curve(const float* preds, const void* target, int targe
   return TMB_OK;
 }
 
+extern "C" int tmb_exact_auroc_ap_offset(const float* preds, const void* target, int target_dtype, int64_t n,
+                                         int64_t pos_label, int64_t tp_offset, int64_t fp_offset, double* out4,
+                                         void* workspace, size_t workspace_bytes, void* stream);
+
 extern "C" int tmb_exact_auroc_ap(const float* preds, const void* target, int target_dtype, int64_t n,
                                   int64_t pos_label, double* out4, void* workspace, size_t workspace_bytes,
                                   void* stream) {
+  return tmb_exact_auroc_ap_offset(preds, target, target_dtype, n, pos_label, 0, 0, out4, workspace, workspace_bytes,
+                                   stream);
+}
+
+extern "C" int tmb_exact_auroc_ap_offset(const float* preds, const void* target, int target_dtype, int64_t n,
+                                         int64_t pos_label, int64_t tp_offset, int64_t fp_offset, double* out4,
+                                         void* workspace, size_t workspace_bytes, void* stream) {
+  if (tp_offset < 0 || fp_offset < 0) return TMB_ERR_ARG;
   if (n < 0 || !out4 || !workspace) return TMB_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   if (n == 0) {
@@ -948,7 +963,8 @@ extern "C" int tmb_exact_auroc_ap(const float* preds, const void* target, int ta
                                                      ws.tile_last_idx1, ws.tile_last_tp);
   k4_scan_tiles_last<<<1, 1024, 0, st>>>(ws.tile_pos, ws.tile_ends, ws.tile_last_idx1, ws.tile_last_tp, ntiles, out4);
   k4_reduce_tiles<<<ntiles, kSortThreads, 0, st>>>(ws.keys[cur], ws.labs[cur], n, ws.tile_pos, ws.tile_last_idx1,
-                                                   ws.tile_last_tp, ws.tile_auc, ws.tile_ap);
+                                                   ws.tile_last_tp, ws.tile_auc, ws.tile_ap, (u64)tp_offset,
+                                                   (u64)fp_offset);
   k4_sum_tiles<<<1, 1024, 0, st>>>(ws.tile_auc, ws.tile_ap, ntiles, out4);
   TMB_CUDA_CHECK(cudaGetLastError());
   return TMB_OK;

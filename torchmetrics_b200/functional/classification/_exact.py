@@ -41,3 +41,91 @@ def fused_binary_average_precision(state, pos_label: int = 1) -> Optional[Tensor
     if npos <= 0:
         return None
     return torch.tensor(apsum / npos, dtype=torch.float32, device=preds.device)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Distributed exact AUROC / average precision WITHOUT replication.
+#
+# The reference (and the default mode here) all_gathers every rank's scores and targets and then sorts the whole set
+# on every rank (metric.py:427-457, then precision_recall_curve.py:28-80): W times the sort work and (W-1)/W of all
+# samples received per rank.  Here the samples are range-partitioned by score instead:
+#   1. every rank contributes a sample of its scores; the weighted quantiles of the gathered sample are W-1 splitters;
+#   2. an all-to-all moves each (score, positive?) pair - 5 bytes - to the rank owning its score range, equal scores
+#      always to the same rank, rank 0 taking the highest range;
+#   3. each rank sorts only its range with K4b, told how many positives / negatives rank above it (one tiny
+#      all_gather of per-range counts), so its two partial sums are its terms of the GLOBAL sums;
+#   4. one all_reduce of four numbers finishes AUROC and AP.
+# Every rank sends and receives about n/W samples once and sorts n/W samples.
+# ---------------------------------------------------------------------------------------------------------------
+_SPLITTER_SAMPLES = 4096
+
+
+def partitioned_exact_sums(preds: Tensor, positive: Tensor, group=None) -> Tuple[float, float, float, float]:
+    """(area2, ap_sum, num_positive, num_samples) of the union of all ranks' (preds, positive) - the quantities
+    `_native.exact_auroc_ap` returns for the concatenated input - computed collectively.  `preds` float32 (n_local,)
+    CUDA, `positive` (n_local,) uint8/bool; ranks may hold different (also zero) numbers of samples."""
+    import torch.distributed as dist
+
+    group = group if group is not None else dist.group.WORLD
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = preds.device
+    preds = preds.detach().reshape(-1).to(torch.float32)
+    positive = positive.reshape(-1).to(torch.uint8)
+    n_local = preds.numel()
+
+    # 1. splitters from a weighted sample (a rank's sample stands for n_local / S of its scores)
+    S = _SPLITTER_SAMPLES
+    mine = torch.full((S + 1,), float("nan"), device=dev)
+    if n_local:
+        idx = torch.randint(0, n_local, (S,), device=dev)
+        mine[:S] = preds[idx]
+    mine[S] = float(n_local)
+    everyone = torch.empty(world * (S + 1), device=dev)
+    dist.all_gather_into_tensor(everyone, mine, group=group)
+    everyone = everyone.view(world, S + 1)
+    counts = everyone[:, S]
+    weights = (counts / S).unsqueeze(1).expand(world, S).reshape(-1)
+    values = everyone[:, :S].reshape(-1)
+    keep = ~values.isnan()
+    values, weights = values[keep], weights[keep]
+    if values.numel():
+        order = torch.argsort(values)
+        values, cum = values[order], torch.cumsum(weights[order], 0)
+        marks = cum[-1] * torch.arange(1, world, device=dev) / world
+        splitters = values[torch.searchsorted(cum, marks).clamp(max=values.numel() - 1)]
+    else:
+        splitters = torch.zeros(world - 1, device=dev)
+
+    # 2. destination = score range; range 0 (rank 0) holds the highest scores, NaN ranks above everything
+    bucket = torch.bucketize(preds, splitters)  # equal scores -> equal bucket
+    dest = (world - 1) - bucket
+    order = torch.argsort(dest, stable=True)
+    send_p, send_t = preds[order].contiguous(), positive[order].contiguous()
+    send_counts = torch.bincount(dest, minlength=world)
+    recv_counts = torch.empty_like(send_counts)
+    dist.all_to_all_single(recv_counts, send_counts, group=group)
+    both = torch.stack([send_counts, recv_counts]).tolist()  # the split sizes have to be host integers
+    send_sizes, recv_sizes = [int(v) for v in both[0]], [int(v) for v in both[1]]
+    n_mine = sum(recv_sizes)
+    recv_p = torch.empty(n_mine, dtype=torch.float32, device=dev)
+    recv_t = torch.empty(n_mine, dtype=torch.uint8, device=dev)
+    dist.all_to_all_single(recv_p, send_p, recv_sizes, send_sizes, group=group)
+    dist.all_to_all_single(recv_t, send_t, recv_sizes, send_sizes, group=group)
+
+    # 3. counts ranked above this range, then the range's own terms of the global sums
+    mine2 = torch.stack([recv_t.sum(dtype=torch.int64), torch.tensor(n_mine, device=dev)])
+    table = torch.empty(world * 2, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(table, mine2, group=group)
+    table = table.view(world, 2).tolist()
+    tp_off = sum(int(r[0]) for r in table[:rank])
+    fp_off = sum(int(r[1]) - int(r[0]) for r in table[:rank])
+    if n_mine:
+        area2, apsum, _, _ = _native.exact_auroc_ap(recv_p, recv_t, 1, tp_off, fp_off)
+    else:
+        area2, apsum = 0.0, 0.0
+
+    # 4. global sums
+    sums = torch.tensor([area2, apsum], dtype=torch.float64, device=dev)
+    dist.all_reduce(sums, group=group)
+    area2, apsum = sums.tolist()
+    return area2, apsum, float(sum(int(r[0]) for r in table)), float(sum(int(r[1]) for r in table))
