@@ -205,6 +205,19 @@ TMB_API int tmb_exact_auroc_ap_offset(const float* preds_dev, const void* target
                                       int64_t pos_label, int64_t tp_offset, int64_t fp_offset, double* out4_dev,
                                       void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* Regroup (score, target) pairs by score range for the same distributed curve (no reference counterpart: the
+ * reference never partitions, it gathers).  splitters_dev: num_ranges - 1 ascending float32 boundaries; a sample goes
+ * to range (num_ranges - 1) - #{splitters < score}, NaN to range 0, so range 0 holds the highest scores and equal
+ * scores always share a range.  out_scores_dev / out_positive_dev (n entries each) receive the samples grouped by
+ * range, range 0 first; the label becomes one byte (target == pos_label).  totals2_dev: int64[2 * num_ranges] =
+ * samples per range, then positives per range.  num_ranges <= 64, n < 2^32.
+ * workspace_dev: tmb_range_partition_workspace_bytes(n, num_ranges) bytes, contents irrelevant. */
+TMB_API size_t tmb_range_partition_workspace_bytes(int64_t n, int num_ranges);
+TMB_API int tmb_range_partition(const float* scores_dev, const void* target_dev, int target_dtype, int64_t n,
+                                int64_t pos_label, const float* splitters_dev, int num_ranges, float* out_scores_dev,
+                                uint8_t* out_positive_dev, int64_t* totals2_dev, void* workspace_dev,
+                                size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * K1c  per-class tp / fp / tn / fn of multiclass label pairs, without the C x C matrix.
  * Replaces: functional/classification/stat_scores.py:395-419, the non-one-hot branch of

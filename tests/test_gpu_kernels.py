@@ -858,3 +858,58 @@ def test_samplewise_paths_are_native(monkeypatch):
     assert F.multiclass_stat_scores(pc, tc, 7, multidim_average="samplewise", average=None).shape == (6, 7, 5)
     with pytest.raises(RuntimeError, match="CUDA tensors only"):
         F.binary_stat_scores(pb.cpu(), tb.cpu(), multidim_average="samplewise")
+
+
+# =========================================================================== score-range partition (N4)
+@pytest.mark.parametrize("n", [0, 1, 33, 1025, 100_003, (1 << 21) + 5])
+@pytest.mark.parametrize("R", [1, 2, 8, 64])
+def test_range_partition_vs_bucketize(n, R):
+    """tmb_range_partition against torch.bucketize + a stable sort by range: same grouping, same order, NaN on top,
+    ties on a splitter stay together."""
+    N = _native()
+    g = torch.Generator().manual_seed(n * 7 + R)
+    p = torch.rand(n, generator=g)
+    p = (p * 50).floor() / 50  # many ties, some exactly on splitters
+    if n > 40:
+        p[::37] = float("nan")
+        p[5] = float("inf")
+        p[6] = -float("inf")
+    t = torch.randint(0, 3, (n,), generator=g)  # positives are the samples with target == 1
+    splitters = torch.sort(torch.rand(R - 1, generator=g)).values
+    if R > 2:
+        splitters[1] = 0.5  # a splitter equal to many scores
+        splitters = torch.sort(splitters).values
+    out_p, out_t, totals = N.range_partition(p.to(DEV), t.to(DEV), splitters.to(DEV), 1)
+    dest = (R - 1) - torch.bucketize(p, splitters)
+    dest[p.isnan()] = 0
+    order = torch.argsort(dest, stable=True)
+    want_p, want_t = p[order], (t[order] == 1).to(torch.uint8)
+    got_p = out_p.cpu()
+    assert torch.equal(got_p.isnan(), want_p.isnan())
+    assert torch.equal(got_p.nan_to_num(7.0), want_p.nan_to_num(7.0))
+    assert torch.equal(out_t.cpu(), want_t)
+    assert totals[0].cpu().tolist() == torch.bincount(dest, minlength=R).tolist()
+    assert totals[1].cpu().tolist() == torch.bincount(dest[t == 1], minlength=R).tolist()
+
+
+def test_exact_auroc_ap_offsets_add_up():
+    """K4b per score range with rank offsets == K4b of the whole input (what the distributed mode relies on)."""
+    N = _native()
+    g = torch.Generator(device=DEV).manual_seed(5)
+    n = 300_000
+    p = (torch.rand(n, device=DEV, generator=g) * 4096).floor() / 4096
+    t = (torch.rand(n, device=DEV, generator=g) < 0.2 + 0.5 * p).to(torch.uint8)
+    whole = N.exact_auroc_ap(p, t, 1)
+    splitters = torch.tensor([0.2, 0.55, 0.8], device=DEV)
+    sp, st, totals = N.range_partition(p, t, splitters, 1)
+    counts, pos = totals[0].tolist(), totals[1].tolist()
+    a = b = 0.0
+    start = tp_off = fp_off = 0
+    for r in range(4):
+        part = N.exact_auroc_ap(sp[start:start + counts[r]].clone(), st[start:start + counts[r]].clone(), 1, tp_off,
+                                fp_off)
+        a, b = a + part[0], b + part[1]
+        start, tp_off, fp_off = start + counts[r], tp_off + pos[r], fp_off + counts[r] - pos[r]
+    assert a == whole[0]  # integer-valued terms below 2^53: exact
+    assert abs(b - whole[1]) <= 1e-9 * whole[1]
+    assert sum(pos) == whole[2]

@@ -79,6 +79,10 @@ _SIGNATURES = {
                                       _c.c_void_p, _c.c_size_t, _c.c_void_p]),
     "tmb_exact_auroc_ap_offset": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_int64,
                                              _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
+    "tmb_range_partition_workspace_bytes": (_c.c_size_t, [_c.c_int64, _c.c_int]),
+    "tmb_range_partition": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p,
+                                       _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t,
+                                       _c.c_void_p]),
     "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                           _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,
@@ -482,10 +486,11 @@ def exact_curve(preds: Tensor, target: Tensor, pos_label: int = 1):
 
 
 def exact_auroc_ap(preds: Tensor, target: Tensor, pos_label: int = 1, tp_offset: int = 0,
-                   fp_offset: int = 0) -> Tuple[float, float, float, float]:
+                   fp_offset: int = 0, as_tensor: bool = False):
     """(sum_k dFP_k (TP_k + TP_{k-1}),  sum_k dTP_k TP_k / (TP_k + FP_k),  positives,  distinct scores) of the exact
     curve, reduced on the device (K4b): the curve itself is never written.  One 32-byte read back.
-    `tp_offset` / `fp_offset`: counts ranked above this input when it is one shard of a score-range partition."""
+    `tp_offset` / `fp_offset`: counts ranked above this input when it is one shard of a score-range partition.
+    `as_tensor`: return the float64[4] device tensor instead (no host sync)."""
     dev = require_cuda(preds, target)
     preds = _aligned(preds.detach().reshape(-1).to(torch.float32))
     target = as_kernel_labels(target.reshape(-1))
@@ -499,8 +504,31 @@ def exact_auroc_ap(preds: Tensor, target: Tensor, pos_label: int = 1, tp_offset:
                                            int(tp_offset), int(fp_offset), out4.data_ptr(), ws.data_ptr(), ws.numel(),
                                            _stream_ptr(dev))
     _check(rc, "tmb_exact_auroc_ap_offset")
+    if as_tensor:
+        return out4
     a, b, c, d = out4.tolist()
     return a, b, c, d
+
+
+def range_partition(preds: Tensor, target: Tensor, splitters: Tensor, pos_label: int = 1):
+    """(scores grouped by score range, positives as uint8, int64 (2, R) [samples | positives] per range) - range 0
+    holds the highest scores (tmb_range_partition)."""
+    dev = require_cuda(preds, target, splitters)
+    preds = preds.detach().reshape(-1).to(torch.float32).contiguous()
+    target = as_kernel_labels(target.reshape(-1))
+    splitters = splitters.to(torch.float32).contiguous()
+    n, R = preds.numel(), splitters.numel() + 1
+    lib = load()
+    out_p = torch.empty(n, dtype=torch.float32, device=dev)
+    out_t = torch.empty(n, dtype=torch.uint8, device=dev)
+    totals = torch.empty(2, R, dtype=torch.int64, device=dev)
+    ws = torch.empty(max(lib.tmb_range_partition_workspace_bytes(n, R), 256), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.tmb_range_partition(preds.data_ptr(), target.data_ptr(), dtype_code(target), n, int(pos_label),
+                                     splitters.data_ptr(), R, out_p.data_ptr(), out_t.data_ptr(), totals.data_ptr(),
+                                     ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _check(rc, "tmb_range_partition")
+    return out_p, out_t, totals
 
 
 def binned_curve_update_static_(confmat: Tensor, preds: Tensor, target: Tensor, thresholds: Tensor,

@@ -96,36 +96,33 @@ def partitioned_exact_sums(preds: Tensor, positive: Tensor, group=None) -> Tuple
     else:
         splitters = torch.zeros(world - 1, device=dev)
 
-    # 2. destination = score range; range 0 (rank 0) holds the highest scores, NaN ranks above everything
-    bucket = torch.bucketize(preds, splitters)  # equal scores -> equal bucket
-    dest = (world - 1) - bucket
-    order = torch.argsort(dest, stable=True)
-    send_p, send_t = preds[order].contiguous(), positive[order].contiguous()
-    send_counts = torch.bincount(dest, minlength=world)
-    recv_counts = torch.empty_like(send_counts)
-    dist.all_to_all_single(recv_counts, send_counts, group=group)
-    both = torch.stack([send_counts, recv_counts]).tolist()  # the split sizes have to be host integers
-    send_sizes, recv_sizes = [int(v) for v in both[0]], [int(v) for v in both[1]]
+    # 2. destination = score range; range 0 (rank 0) holds the highest scores, NaN ranks above everything.
+    # Samples are regrouped by destination in two coalesced passes (tmb_range_partition); per destination every
+    # rank publishes how many samples and how many positives it sends, so ONE all_gather tells every rank its
+    # receive sizes and the counts ranked above its range.
+    send_p, send_t, totals = _native.range_partition(preds, positive, splitters, 1)
+    table = torch.empty(world, 2, world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(table.view(-1), totals.view(-1), group=group)
+    table = table.tolist()  # [sender][0 = samples, 1 = positives][destination]; the split sizes must be host ints
+    send_sizes = [int(v) for v in table[rank][0]]
+    recv_sizes = [int(table[r][0][rank]) for r in range(world)]
+    range_n = [sum(int(table[r][0][d]) for r in range(world)) for d in range(world)]
+    range_p = [sum(int(table[r][1][d]) for r in range(world)) for d in range(world)]
     n_mine = sum(recv_sizes)
     recv_p = torch.empty(n_mine, dtype=torch.float32, device=dev)
     recv_t = torch.empty(n_mine, dtype=torch.uint8, device=dev)
     dist.all_to_all_single(recv_p, send_p, recv_sizes, send_sizes, group=group)
     dist.all_to_all_single(recv_t, send_t, recv_sizes, send_sizes, group=group)
 
-    # 3. counts ranked above this range, then the range's own terms of the global sums
-    mine2 = torch.stack([recv_t.sum(dtype=torch.int64), torch.tensor(n_mine, device=dev)])
-    table = torch.empty(world * 2, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(table, mine2, group=group)
-    table = table.view(world, 2).tolist()
-    tp_off = sum(int(r[0]) for r in table[:rank])
-    fp_off = sum(int(r[1]) - int(r[0]) for r in table[:rank])
+    # 3. this range's terms of the global sums: K4b told how many positives / negatives rank above the range
+    tp_off = sum(range_p[:rank])
+    fp_off = sum(range_n[:rank]) - tp_off
     if n_mine:
-        area2, apsum, _, _ = _native.exact_auroc_ap(recv_p, recv_t, 1, tp_off, fp_off)
+        sums = _native.exact_auroc_ap(recv_p, recv_t, 1, tp_off, fp_off, as_tensor=True)[:2].clone()
     else:
-        area2, apsum = 0.0, 0.0
+        sums = torch.zeros(2, dtype=torch.float64, device=dev)
 
     # 4. global sums
-    sums = torch.tensor([area2, apsum], dtype=torch.float64, device=dev)
     dist.all_reduce(sums, group=group)
     area2, apsum = sums.tolist()
-    return area2, apsum, float(sum(int(r[0]) for r in table)), float(sum(int(r[1]) for r in table))
+    return area2, apsum, float(sum(range_p)), float(sum(range_n))
