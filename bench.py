@@ -441,6 +441,24 @@ def main():
             "value": BATCH * world / (vms * 1e-3), "unit": "samples/s", "ms_per_update": vms,
         }
         del mv
+        md = tm.MulticlassConfusionMatrix(NUM_CLASSES, validate_args="deferred").to(dev)
+        for i in range(3):
+            md.update(*batches[i % len(batches)])
+        barrier()
+        v0, v1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        v0.record()
+        for i in range(20):
+            md.update(*batches[i % len(batches)])
+        v1.record()
+        barrier()
+        dms = max_over_ranks(v0.elapsed_time(v1)) / 20
+        md.compute()
+        extra["confmat_validate_args_deferred"] = {
+            "workload": "configs[1] with validate_args='deferred': the same fused validation, the status words copied "
+                        "to pinned host memory behind each kernel and looked at one call later (no per-update sync)",
+            "value": BATCH * world / (dms * 1e-3), "unit": "samples/s", "ms_per_update": dms,
+        }
+        del md
         del batches, cm
         torch.cuda.empty_cache()
         n_total = 1 << 28

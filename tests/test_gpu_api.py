@@ -508,6 +508,47 @@ def test_fused_validation_raises_like_the_reference_and_restores_state(monkeypat
     F.binary_stat_scores(ps, tb)
 
 
+def test_deferred_validation_raises_one_call_late_and_restores_state():
+    """validate_args="deferred": no host sync per update; a bad batch is reported (with the reference's message) at the
+    next update / compute / reset, after its counts have been taken out of the state again."""
+    tm = _tm()
+    g = torch.Generator().manual_seed(4)
+    n = 2048
+    good_t = torch.randint(0, 5, (n,), generator=g).to(DEV)
+    good_p = torch.randint(0, 5, (n,), generator=g).to(DEV)
+    bad_t = torch.arange(n, device=DEV) % 9
+    cm = tm.MulticlassConfusionMatrix(5, validate_args="deferred").to(DEV)
+    cm.update(good_p, good_t)
+    one = cm.confmat.clone()
+    cm.update(good_p, bad_t)          # nothing raised yet
+    with pytest.raises(RuntimeError, match="Detected more unique values in `target` than `num_classes`"):
+        cm.update(good_p, good_t)     # the verdict of the previous batch; this batch itself is applied
+    assert torch.equal(cm.confmat, 2 * one)
+    cm.update(good_p, bad_t)
+    with pytest.raises(RuntimeError, match="Detected more unique values"):
+        cm.compute()
+    assert torch.equal(cm.compute(), 2 * one)
+    cm.update(good_p, bad_t)
+    with pytest.raises(RuntimeError, match="Detected more unique values"):
+        cm.reset()
+    # curve classes take the same route
+    tb = torch.randint(0, 2, (n,), generator=g).to(DEV)
+    ps = torch.rand(n, generator=g).to(DEV)
+    bad_tb = tb.clone()
+    bad_tb[17] = 3
+    au = tm.classification.BinaryAUROC(thresholds=32, validate_args="deferred").to(DEV)
+    au.update(ps, tb)
+    one = au.confmat.clone()
+    au.update(ps, bad_tb)
+    with pytest.raises(RuntimeError, match="Detected the following values in `target`"):
+        au.compute()
+    assert torch.equal(au.confmat, one)
+    import pickle
+
+    au.update(ps, tb)
+    assert torch.equal(pickle.loads(pickle.dumps(au)).confmat, 2 * one)  # an outstanding verdict is not pickled
+
+
 def test_multiclass_binned_curve_rejects_targets_outside_the_classes():
     """The multiclass binned family reads the error word in the middle of its update (softmax decision); the
     fused-validation finding next to it must survive until `finish` (reference: the `torch.unique` check in

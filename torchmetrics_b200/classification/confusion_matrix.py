@@ -51,7 +51,7 @@ class BinaryConfusionMatrix(_ConfmatBase):
             F._binary_confusion_matrix_update_fused(preds, target, self.threshold, self.ignore_index, out=out)
 
         step(self.confmat)
-        fv.finish(preds.device, 2, undo=lambda: C.rollback(self.confmat, step))
+        fv.finish(preds.device, 2, undo=lambda: C.rollback(self.confmat, step), owner=self)
 
     def compute(self) -> Tensor:
         self._check_device_status(2)
@@ -83,7 +83,7 @@ class MulticlassConfusionMatrix(_ConfmatBase):
             F._multiclass_confusion_matrix_update_fused(preds, target, self.num_classes, self.ignore_index, out=out)
 
         step(self.confmat)
-        fv.finish(preds.device, self.num_classes, undo=lambda: C.rollback(self.confmat, step))
+        fv.finish(preds.device, self.num_classes, undo=lambda: C.rollback(self.confmat, step), owner=self)
 
     def compute(self) -> Tensor:
         self._check_device_status(self.num_classes)
@@ -117,7 +117,7 @@ class MultilabelConfusionMatrix(_ConfmatBase):
                                                         self.ignore_index, out=out)
 
         step(self.confmat)
-        fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
+        fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step), owner=self)
 
     def compute(self) -> Tensor:
         return F._multilabel_confusion_matrix_compute(self.confmat, self.normalize)

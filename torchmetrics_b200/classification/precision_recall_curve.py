@@ -90,7 +90,7 @@ class BinaryPrecisionRecallCurve(_CurveBase):
                                                               out=out, assume_sorted=self._thresholds_ascending)
 
             step(self.confmat)
-            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
+            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step), owner=self)
 
     def _state(self):
         if self.thresholds is None:
@@ -148,7 +148,7 @@ class MulticlassPrecisionRecallCurve(_CurveBase):
                                                                   assume_sorted=self._thresholds_ascending)
 
             step(self.confmat)
-            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
+            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step), owner=self)
 
     def _state(self):
         if self.thresholds is None:
@@ -189,7 +189,7 @@ class MultilabelPrecisionRecallCurve(_CurveBase):
                                                                   assume_sorted=self._thresholds_ascending)
 
             step(self.confmat)
-            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step))
+            fv.finish(preds.device, undo=lambda: C.rollback(self.confmat, step), owner=self)
 
     def _state(self):
         if self.thresholds is None:

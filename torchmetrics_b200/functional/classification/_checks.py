@@ -92,8 +92,22 @@ class FusedValidation:
         _tls.sink = None
 
     def finish(self, dev: torch.device, num_classes: Optional[int] = None,
-               undo: Optional[Callable[[], None]] = None, errors: bool = False) -> None:
-        """`errors`: also settle the kernel's error bits (label outside the matrix) when validation is off."""
+               undo: Optional[Callable[[], None]] = None, errors: bool = False, owner=None) -> None:
+        """`errors`: also settle the kernel's error bits (label outside the matrix) when validation is off.
+        `owner`: the metric; with `validate_args="deferred"` the verdict of this batch is collected at the owner's
+        next update / compute / reset instead of now (see `DeferredVerdict`)."""
+        if self.enabled and owner is not None and getattr(owner, "validate_args", True) == "deferred":
+            slots = owner.__dict__.get("_validation_slots")
+            if slots is None:  # two pinned status copies per metric, used alternately (pinning is a slow call)
+                slots = [torch.empty(2, dtype=torch.int32).pin_memory(), torch.empty(2, dtype=torch.int32).pin_memory(), 0]
+                owner.__dict__["_validation_slots"] = slots
+            slots[2] ^= 1
+            verdict = DeferredVerdict(dev, self.pending, num_classes, undo, slots[slots[2]])
+            previous = owner.__dict__.get("_pending_validation")
+            owner.__dict__["_pending_validation"] = verdict
+            if previous is not None:
+                previous.settle()
+            return
         if not self.enabled:
             if errors and dev.type == "cuda":
                 _native.raise_on_status(dev, num_classes)
@@ -111,6 +125,50 @@ class FusedValidation:
             if undo is not None:
                 undo()
             raise
+
+
+class DeferredVerdict:
+    """`validate_args="deferred"`: the status words of one update, copied to pinned host memory behind the kernel.
+
+    The synchronous mode reads the 8 status bytes right after every update, which drains the stream once per update
+    (configs[1]: 0.114 ms instead of 0.069 ms per update).  Here the copy is only enqueued; the words are looked at
+    when the owner's NEXT update has been launched (or at compute / reset), by which time the copy has long finished,
+    so the GPU never waits for the host.  The price: a bad batch raises one call late.  Its counts are still taken
+    out of the state first (`undo`), and the exception is the reference's.
+    """
+
+    def __init__(self, dev: torch.device, pending: List[Callable[[], None]], num_classes: Optional[int],
+                 undo: Optional[Callable[[], None]], host: Tensor) -> None:
+        self.pending, self.num_classes, self.undo = pending, num_classes, undo
+        status = _native.scratch(dev).status
+        self.host = host
+        self.host.copy_(status[:2], non_blocking=True)
+        status[:2].zero_()  # stream-ordered behind the copy: the next update starts from clean words
+        self.event = torch.cuda.Event()
+        self.event.record(torch.cuda.current_stream(dev))
+
+    def settle(self) -> None:
+        self.event.synchronize()
+        err, val = self.host.tolist()
+        if not (err or val):
+            return
+        try:
+            if val:
+                for chk in self.pending:
+                    chk()
+            _native.raise_for_bits(err, self.num_classes)
+        except Exception:
+            if self.undo is not None:
+                self.undo()
+            raise
+
+
+def settle_deferred(owner) -> None:
+    """Collect the outstanding deferred verdict of a metric, if any (called before compute / reset)."""
+    verdict = owner.__dict__.get("_pending_validation")
+    if verdict is not None:
+        owner.__dict__["_pending_validation"] = None
+        verdict.settle()
 
 
 def _deferred(fn: Callable, t: Tensor, *args) -> bool:

@@ -288,6 +288,11 @@ class Metric(Module, ABC):
                 )
             if self._computed is not None:
                 return self._computed
+            if self.__dict__.get("_pending_validation") is not None:
+                # validate_args="deferred": the last update's verdict is still outstanding
+                from torchmetrics_b200.functional.classification._checks import settle_deferred
+
+                settle_deferred(self)
             with self.sync_context(dist_sync_fn=self.dist_sync_fn, should_sync=self._to_sync,
                                    should_unsync=self._should_unsync):
                 value = _squeeze_if_scalar(compute(*args, **kwargs))
@@ -378,6 +383,10 @@ class Metric(Module, ABC):
 
     # ------------------------------------------------------------------ reset / copy / pickle
     def reset(self) -> None:
+        if self.__dict__.get("_pending_validation") is not None:
+            from torchmetrics_b200.functional.classification._checks import settle_deferred
+
+            settle_deferred(self)
         self._update_count = 0
         self._forward_cache = None
         self._computed = None
@@ -394,7 +403,8 @@ class Metric(Module, ABC):
 
     def __getstate__(self) -> Dict[str, Any]:
         # the wrapped bound methods are closures over `self`; rebuild them on load
-        return {k: v for k, v in self.__dict__.items() if k not in ("update", "compute", "_update_signature")}
+        skip = ("update", "compute", "_update_signature", "_pending_validation", "_validation_slots")
+        return {k: v for k, v in self.__dict__.items() if k not in skip}
 
     def __setstate__(self, state: Dict[str, Any]) -> None:
         self.__dict__.update(state)
