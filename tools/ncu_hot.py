@@ -14,11 +14,11 @@ for row in csv.reader(io.StringIO(raw)):
     elif cur is not None and cur["hdr"] and len(row) == len(cur["hdr"]):
         cur["rows"].append(row)
 for b in blocks:
-    if sub not in b["name"]:
+    if sub not in b["name"] or b["name"] in globals().get("_seen", set()):
         continue
     h = b["hdr"]
     isamp, isrc, iex = h.index("# Samples"), h.index("Source"), h.index("Instructions Executed")
-    tot = sum(int(r[isamp]) for r in b["rows"])
+    tot = sum(int(r[isamp]) for r in b["rows"]) or 1
     print("==", b["name"][:100], "samples", tot, "instructions", len(b["rows"]))
     # cumulative by position to see phases
     acc = 0
@@ -35,4 +35,7 @@ for b in blocks:
     for k in sorted(order):
         r = b["rows"][k]
         print(f"  {k:5d} {100*int(r[isamp])/tot:5.1f}%  exec {r[iex]:>8s}  {r[isrc].strip()[:90]}")
-    break
+    seen = globals().setdefault("_seen", set())
+    if sub or len(seen) > 12:
+        break
+    seen.add(b["name"])

@@ -1,4 +1,4 @@
-"""Run one kernel a few times (for ncu). Usage: python tools/prof_one.py binned|binned_multi|confmat|class_stats|stat|exact|exact_auroc [log2n]"""
+"""Run one kernel a few times (for ncu). Usage: python tools/prof_one.py binned|binned_multi|confmat|class_stats|stat|rows|partition|exact|exact_auroc [log2n]"""
 import os
 import sys
 
@@ -53,6 +53,23 @@ elif what == "exact_auroc":
     target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
     for _ in range(2):
         N.exact_auroc_ap(preds, target, 1)
+elif what == "rows":
+    width = 1024
+    p = torch.rand(n // width, width, device=DEV, generator=g)
+    t = torch.randint(0, 2, (n // width, width), device=DEV, generator=g)
+    for _ in range(4):
+        N.stat_scores_rows(p, t, width, 0.5, None)
+    C = 100
+    pl = torch.randint(0, C, (n // width, width), device=DEV, generator=g)
+    tl = torch.randint(0, C, (n // width, width), device=DEV, generator=g)
+    for _ in range(4):
+        N.class_stats_rows(pl, tl, C)
+elif what == "partition":
+    preds = torch.rand(n, device=DEV, generator=g)
+    target = (torch.rand(n, device=DEV, generator=g) < 0.4).to(torch.uint8)
+    spl = torch.linspace(0, 1, 9, device=DEV)[1:-1].contiguous()
+    for _ in range(4):
+        N.range_partition(preds, target, spl, 1)
 elif what == "exact":
     preds = torch.rand(n, device=DEV, generator=g)
     target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()

@@ -196,6 +196,7 @@ def _stream_ptr(dev: torch.device) -> int:
 class _Scratch:
     def __init__(self, dev: torch.device) -> None:
         self.status = torch.zeros(8, dtype=torch.int32, device=dev)
+        self.status_words = self.status[:2]  # [errors, fused-validation findings]
         self.ws: Dict[str, Tensor] = {}
 
     def workspace(self, kind: str, nbytes: int, dev: torch.device) -> Tensor:

@@ -41,7 +41,9 @@ __device__ __forceinline__ int range_of(float x, const float* s_split, int R) {
   return (R - 1) - below;
 }
 
-template <typename TT, bool SCATTER>
+// RR > 0: at most RR ranges, the per-range cursors live in registers (every lane keeps the same copy), the loop over
+// the ranges is unrolled and touches no shared memory.  RR == 0: any R <= 64, cursors in shared memory.
+template <typename TT, bool SCATTER, int RR>
 __global__ void __launch_bounds__(kRpThreads) range_partition_kernel(const RpParams P) {
   __shared__ float s_split[kRpMaxRanges];
   __shared__ u32 s_cur[kRpWarps][kRpMaxRanges];
@@ -64,6 +66,13 @@ __global__ void __launch_bounds__(kRpThreads) range_partition_kernel(const RpPar
   const long long begin = gw * P.per_warp;
   const long long end = begin + P.per_warp < P.n ? begin + P.per_warp : P.n;
   const u32 lt = (1u << lane) - 1u;
+  constexpr int NR = RR > 0 ? RR : 1;
+  u32 cur[NR], pcnt[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    cur[r] = (RR > 0 && r < R) ? s_cur[warp][r] : 0u;
+    pcnt[r] = 0;
+  }
   constexpr int kBatch = 4;  // steps whose loads are issued together
   for (long long i0 = begin; i0 < end; i0 += 32 * kBatch) {
     float xs[kBatch];
@@ -86,33 +95,60 @@ __global__ void __launch_bounds__(kRpThreads) range_partition_kernel(const RpPar
       const int d = ds[k];
       const float x = xs[k];
       const bool pos = ps[k];
-      for (int r = 0; r < R; ++r) {
-        const u32 m = __ballot_sync(0xffffffffu, d == r);
-        if (m == 0) continue;  // uniform
-        if constexpr (SCATTER) {
-          if (d == r) {
-            const u32 slot = s_cur[warp][r] + __popc(m & lt);
-            P.out_scores[slot] = x;
-            P.out_pos[slot] = pos ? 1 : 0;
+      if constexpr (RR > 0) {
+#pragma unroll
+        for (int r = 0; r < RR; ++r) {
+          const u32 m = __ballot_sync(0xffffffffu, d == r);
+          if constexpr (SCATTER) {
+            if (d == r) {
+              const u32 slot = cur[r] + __popc(m & lt);
+              P.out_scores[slot] = x;
+              P.out_pos[slot] = pos ? 1 : 0;
+            }
+          } else {
+            pcnt[r] += __popc(__ballot_sync(0xffffffffu, d == r && pos));
+          }
+          cur[r] += __popc(m);
+        }
+      } else {
+        for (int r = 0; r < R; ++r) {
+          const u32 m = __ballot_sync(0xffffffffu, d == r);
+          if (m == 0) continue;  // uniform
+          if constexpr (SCATTER) {
+            if (d == r) {
+              const u32 slot = s_cur[warp][r] + __popc(m & lt);
+              P.out_scores[slot] = x;
+              P.out_pos[slot] = pos ? 1 : 0;
+            }
+            __syncwarp();
+            if (lane == 0) s_cur[warp][r] += __popc(m);
+          } else {
+            const u32 mp = __ballot_sync(0xffffffffu, d == r && pos);
+            if (lane == 0) {
+              s_cur[warp][r] += __popc(m);
+              s_pos[warp][r] += __popc(mp);
+            }
           }
           __syncwarp();
-          if (lane == 0) s_cur[warp][r] += __popc(m);
-        } else {
-          const u32 mp = __ballot_sync(0xffffffffu, d == r && pos);
-          if (lane == 0) {
-            s_cur[warp][r] += __popc(m);
-            s_pos[warp][r] += __popc(mp);
-          }
         }
-        __syncwarp();
       }
     }
   }
   if constexpr (!SCATTER) {
-    __syncwarp();
-    for (int r = lane; r < R; r += 32) {
-      P.counts[gw * R + r] = s_cur[warp][r];
-      P.poscnt[gw * R + r] = s_pos[warp][r];
+    if constexpr (RR > 0) {
+#pragma unroll
+      for (int r = 0; r < RR; ++r) {
+        if (lane == 0 && r < R) {
+          P.counts[gw * R + r] = cur[r];
+          P.poscnt[gw * R + r] = pcnt[r];
+        }
+      }
+    } else {
+      __syncwarp();
+      for (int r = lane; r < R; r += 32) {
+        P.counts[gw * R + r] = s_cur[warp][r];
+        P.poscnt[gw * R + r] = s_pos[warp][r];
+      }
     }
   }
 }
@@ -214,9 +250,15 @@ extern "C" int tmb_range_partition(const float* scores, const void* target, int 
   P.totals = (long long*)totals2;
   const int grid = (int)((P.total_warps + kRpWarps - 1) / kRpWarps);
   TMB_DISPATCH_INT(target_dtype, TT, {
-    range_partition_kernel<TT, false><<<grid, kRpThreads, 0, st>>>(P);
-    range_offsets_kernel<<<1, 1024, 0, st>>>(P);
-    range_partition_kernel<TT, true><<<grid, kRpThreads, 0, st>>>(P);
+    if (num_ranges <= 8) {
+      range_partition_kernel<TT, false, 8><<<grid, kRpThreads, 0, st>>>(P);
+      range_offsets_kernel<<<1, 1024, 0, st>>>(P);
+      range_partition_kernel<TT, true, 8><<<grid, kRpThreads, 0, st>>>(P);
+    } else {
+      range_partition_kernel<TT, false, 0><<<grid, kRpThreads, 0, st>>>(P);
+      range_offsets_kernel<<<1, 1024, 0, st>>>(P);
+      range_partition_kernel<TT, true, 0><<<grid, kRpThreads, 0, st>>>(P);
+    }
     TMB_CUDA_CHECK(cudaGetLastError());
     return TMB_OK;
   })

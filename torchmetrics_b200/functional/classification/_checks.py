@@ -98,11 +98,11 @@ class FusedValidation:
         next update / compute / reset instead of now (see `DeferredVerdict`)."""
         if self.enabled and owner is not None and getattr(owner, "validate_args", True) == "deferred":
             slots = owner.__dict__.get("_validation_slots")
-            if slots is None:  # two pinned status copies per metric, used alternately (pinning is a slow call)
-                slots = [torch.empty(2, dtype=torch.int32).pin_memory(), torch.empty(2, dtype=torch.int32).pin_memory(), 0]
+            if slots is None:  # two pinned status copies + events per metric, used alternately (creating them is slow)
+                slots = [[torch.empty(2, dtype=torch.int32).pin_memory(), torch.cuda.Event()] for _ in range(2)] + [0]
                 owner.__dict__["_validation_slots"] = slots
             slots[2] ^= 1
-            verdict = DeferredVerdict(dev, self.pending, num_classes, undo, slots[slots[2]])
+            verdict = DeferredVerdict(dev, self.pending, num_classes, undo, *slots[slots[2]])
             previous = owner.__dict__.get("_pending_validation")
             owner.__dict__["_pending_validation"] = verdict
             if previous is not None:
@@ -138,13 +138,13 @@ class DeferredVerdict:
     """
 
     def __init__(self, dev: torch.device, pending: List[Callable[[], None]], num_classes: Optional[int],
-                 undo: Optional[Callable[[], None]], host: Tensor) -> None:
+                 undo: Optional[Callable[[], None]], host: Tensor, event: "torch.cuda.Event") -> None:
         self.pending, self.num_classes, self.undo = pending, num_classes, undo
-        status = _native.scratch(dev).status
+        words = _native.scratch(dev).status_words
         self.host = host
-        self.host.copy_(status[:2], non_blocking=True)
-        status[:2].zero_()  # stream-ordered behind the copy: the next update starts from clean words
-        self.event = torch.cuda.Event()
+        self.host.copy_(words, non_blocking=True)
+        words.zero_()  # stream-ordered behind the copy: the next update starts from clean words
+        self.event = event
         self.event.record(torch.cuda.current_stream(dev))
 
     def settle(self) -> None:
