@@ -363,7 +363,12 @@ def main():
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("confmat_partition_plus_hist_bytes_per_update")
+            tj = json.load(f)
+            pk = tj.get("per_kernel", {})
+            # DRAM bytes of the two launches of one update, from the round-2 `ncu --set full` capture
+            a = pk.get("confmat_partition_tma_kernel@r2_confmat", {}).get("dram_bytes_per_launch")
+            b = pk.get("confmat_bucket_hist_kernel@r2_confmat", {}).get("dram_bytes_per_launch")
+            traffic = a + b if a and b else tj.get("confmat_partition_plus_hist_bytes_per_update")
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": "confmat_partition_tma_kernel<int64,int64> + confmat_bucket_hist_kernel (2 launches per update)", "achieved": achieved, "peak": peak,
