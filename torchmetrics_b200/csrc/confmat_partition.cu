@@ -451,20 +451,48 @@ __global__ void __launch_bounds__(kHistThreads) confmat_bucket_hist_kernel(const
     atomicAdd(&h[w.w & 0xffff], 1u); atomicAdd(&h[w.w >> 16], 1u);
   };
   // the bucket's G segments are dealt round-robin to the warps of the kHistSplit CTAs that share the bucket; a
-  // segment is a few hundred entries, i.e. one or two 16-byte vectors per lane
+  // segment is a few hundred entries.  The loop is software-pipelined: the (up to four) 16-byte vectors a lane takes
+  // from its warp's NEXT segment are in flight while it counts the current one, and the fill count two segments
+  // ahead is loaded alongside - the plain loop waited for one queue load per eight atomics (48 % of its stall samples,
+  // profiles/r2_confmat_hot.txt).
   const u32 lane = threadIdx.x & 31;
   const u32 wid = blockIdx.y * (kHistThreads / 32) + (threadIdx.x >> 5);
   const u32 nw = gridDim.y * (kHistThreads / 32);
   const u32* fill_b = P.fill + (size_t)b * P.G;
-  u32 next_fill = wid < P.G ? fill_b[wid] : 0;
+  auto seg_vecs = [&](u32 seg) {
+    return reinterpret_cast<const uint4*>(P.queue + ((size_t)b * P.G + seg) * P.segcap);  // segcap % 8 == 0
+  };
+  constexpr int kVecs = 4;  // covers segments of up to 1024 entries; longer ones finish in the tail loop
+  uint4 cur[kVecs];
+  u32 len = wid < P.G ? fill_b[wid] : 0;
+  u32 len1 = wid + nw < P.G ? fill_b[wid + nw] : 0;
+  if (wid < P.G) {
+    const uint4* qv = seg_vecs(wid);
+#pragma unroll
+    for (int k = 0; k < kVecs; ++k)
+      if (lane + 32 * k < (len >> 3)) cur[k] = load16_hint(qv + lane + 32 * k, pol_done);
+  }
   for (u32 seg = wid; seg < P.G; seg += nw) {
-    const u32 len = next_fill;  // <= segcap
-    if (seg + nw < P.G) next_fill = fill_b[seg + nw];  // overlaps this segment's work
-    const unsigned short* q = P.queue + ((size_t)b * P.G + seg) * P.segcap;  // 16-byte aligned (segcap % 8 == 0)
-    const uint4* qv = reinterpret_cast<const uint4*>(q);
+    uint4 nxt[kVecs];
+    const u32 len2 = seg + 2 * nw < P.G ? fill_b[seg + 2 * nw] : 0;
+    if (seg + nw < P.G) {
+      const uint4* qn = seg_vecs(seg + nw);
+#pragma unroll
+      for (int k = 0; k < kVecs; ++k)
+        if (lane + 32 * k < (len1 >> 3)) nxt[k] = load16_hint(qn + lane + 32 * k, pol_done);
+    }
+    const uint4* qv = seg_vecs(seg);
     const u32 nvec = len >> 3;
-    for (u32 i = lane; i < nvec; i += 32) count8(load16_hint(qv + i, pol_done));
+#pragma unroll
+    for (int k = 0; k < kVecs; ++k)
+      if (lane + 32 * k < nvec) count8(cur[k]);
+    for (u32 i = lane + 32 * kVecs; i < nvec; i += 32) count8(load16_hint(qv + i, pol_done));
+    const unsigned short* q = reinterpret_cast<const unsigned short*>(qv);
     for (u32 k = (nvec << 3) + lane; k < len; k += 32) atomicAdd(&h[q[k]], 1u);
+#pragma unroll
+    for (int k = 0; k < kVecs; ++k) cur[k] = nxt[k];
+    len = len1;
+    len1 = len2;
   }
   __syncthreads();
   for (u32 lbin = threadIdx.x; lbin < kBinsPerBucket; lbin += kHistThreads) {
