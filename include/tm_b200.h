@@ -57,6 +57,7 @@ extern "C" {
  * value checks would pass; a set bit sends the caller to the exact (slow) check for the error message. */
 #define TMB_STATUS_TARGET_VALUES 8    /* a non-ignored target outside [0, C) (K1, class-index K3) or {0, 1} (K2, K3) */
 #define TMB_STATUS_PREDS_VALUES 16    /* an integer pred outside [0, C) (K1) or {0, 1} (K2)                         */
+#define TMB_STATUS_PEER_TIMEOUT 32    /* word 0: tmb_oneshot_allreduce gave up waiting for a peer (result invalid)  */
 
 /* element types (labels: I64, I32, U8; scores: F32, F16, BF16, F64 — cast anything else first) */
 #define TMB_I64 0
@@ -73,6 +74,12 @@ extern "C" {
 #define TMB_PROB_SIGMOID 2 /* always apply sigmoid                                                                 */
 #define TMB_PROB_CHECK 3 /* as-is, but if any score lies outside [0,1] discard the update and set
                             TMB_STATUS_OUT_OF_UNIT_RANGE (multiclass: the caller then applies softmax itself)     */
+
+/* reductions of tmb_oneshot_allreduce */
+#define TMB_REDUCE_SUM 0
+#define TMB_REDUCE_MAX 1
+#define TMB_REDUCE_MIN 2
+#define TMB_ONESHOT_SLOT_BYTES 65536 /* largest arena one call can reduce */
 
 TMB_API int tmb_abi_version(void);
 TMB_API const char* tmb_last_cuda_error(void);
@@ -305,6 +312,26 @@ TMB_API int tmb_stat_scores_rows(const void* preds_dev, int preds_dtype, const v
 TMB_API int tmb_class_stats_rows(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
                                  int64_t n_rows, int64_t width, int64_t num_classes, int has_ignore,
                                  int64_t ignore_index, int64_t* out_dev, int32_t* status_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K5  one-shot all-reduce of a small state arena over NVLink peer memory.
+ * Replaces: the collective behind `Metric._sync_dist` (metric.py:427-457: one `gather_all_tensors`,
+ *           utilities/distributed.py:97-147, per state, then stack + sum) for arenas up to TMB_ONESHOT_SLOT_BYTES:
+ *           the packed sum / max / min states of a metric or a whole MetricCollection are a few KB.
+ * peer_buffers_dev: DEVICE array of `world` pointers; entry r is rank r's buffer of tmb_oneshot_buffer_bytes() bytes
+ *   as mapped into THIS process (symmetric memory / IPC / cuMemMap; entry `rank` is this rank's own buffer).  The
+ *   buffers must be zero before the first call.
+ * Collective: every rank calls it with the same count / dtype / op and the same `epoch`, a counter that starts at 1
+ *   and is incremented by one per call on that set of buffers.  src_dev may equal dst_dev.  dtype: TMB_I64, TMB_I32,
+ *   TMB_F32, TMB_F64.  The result is reduced in rank order on every rank (bit-identical everywhere).
+ * One kernel (one CTA) per rank: publish the arena in the own buffer, raise a flag on every peer, wait for all peers'
+ *   flags, read all peers' arenas with P2P loads.  Calls on one set of buffers must be stream-ordered on every rank.
+ *   A peer that does not arrive within ~2 s raises TMB_STATUS_PEER_TIMEOUT in status_dev[0] instead of hanging.
+ * ------------------------------------------------------------------------------------------- */
+TMB_API size_t tmb_oneshot_buffer_bytes(void);
+TMB_API int tmb_oneshot_allreduce(void* const* peer_buffers_dev, int world, int rank, const void* src_dev,
+                                  void* dst_dev, int64_t count, int dtype, int op, uint32_t epoch,
+                                  int32_t* status_dev, void* stream);
 
 #ifdef __cplusplus
 }

@@ -125,6 +125,42 @@ def _body_partitioned_exact(rank, world):
         assert sum(x.numel() for x in part_auc.preds) == p.numel()
 
 
+def _body_oneshot_allreduce(rank, world):
+    """K5 against NCCL: every dtype / op, sizes from 1 element to the 64 KB limit, many calls in a row (the two-slot
+    epoch scheme), bit-identical results on every rank."""
+    from torchmetrics_b200 import _native
+    from torchmetrics_b200.utilities import distributed as D
+
+    dev = torch.device("cuda", rank)
+    g = torch.Generator(device=dev).manual_seed(1000 + rank)
+    used = 0
+    for it in range(40):
+        for dtype, n in ((torch.int64, 1), (torch.int64, 800), (torch.int64, 8192), (torch.float32, 777),
+                         (torch.float64, 100), (torch.int32, 16384)):
+            for op in ("sum", "max", "min"):
+                if dtype.is_floating_point:
+                    x = torch.randn(n, device=dev, generator=g, dtype=dtype)
+                else:
+                    x = torch.randint(-1000, 1000, (n,), device=dev, generator=g, dtype=dtype)
+                want = x.clone()
+                dist.all_reduce(want, op={"sum": dist.ReduceOp.SUM, "max": dist.ReduceOp.MAX, "min": dist.ReduceOp.MIN}[op])
+                got = D.fused_reduce([(op, x)])[0]
+                if dtype.is_floating_point and op == "sum":
+                    assert torch.allclose(got, want, rtol=1e-5, atol=1e-5)
+                    # rank-ordered summation: the bits agree on every rank
+                    ref = got.clone()
+                    dist.broadcast(ref, 0)
+                    assert torch.equal(got, ref)
+                else:
+                    assert torch.equal(got, want), (it, dtype, n, op)
+                used += 1
+    assert D._ONESHOT and all(v is not False for v in D._ONESHOT.values()), "one-shot path was not taken"
+    assert _native.read_status(dev) == 0
+    # above the slot size the packed reduce goes through NCCL as before
+    big = torch.ones(1 << 16, dtype=torch.int64, device=dev)
+    assert int(D.fused_reduce([("sum", big)])[0][0]) == world
+
+
 def _body_multilabel_collection(rank, world):
     import torchmetrics_b200 as tm
 
@@ -146,7 +182,7 @@ def _body_multilabel_collection(rank, world):
 
 
 @pytest.mark.parametrize("world", WORLDS)
-@pytest.mark.parametrize("body", ["_body_sum_and_cat_states", "_body_multilabel_collection", "_body_partitioned_exact"])
+@pytest.mark.parametrize("body", ["_body_sum_and_cat_states", "_body_multilabel_collection", "_body_partitioned_exact", "_body_oneshot_allreduce"])
 def test_nccl_sync(body, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")

@@ -27,6 +27,7 @@ STATUS_OUT_OF_UNIT_RANGE = 4
 # fused-validation findings, reported in the second status word (include/tm_b200.h)
 STATUS_TARGET_VALUES = 8
 STATUS_PREDS_VALUES = 16
+STATUS_PEER_TIMEOUT = 32
 
 PROB_AS_IS, PROB_AUTO, PROB_SIGMOID, PROB_CHECK = 0, 1, 2, 3
 
@@ -83,6 +84,9 @@ _SIGNATURES = {
     "tmb_range_partition": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64, _c.c_void_p,
                                        _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t,
                                        _c.c_void_p]),
+    "tmb_oneshot_buffer_bytes": (_c.c_size_t, []),
+    "tmb_oneshot_allreduce": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int64,
+                                         _c.c_int, _c.c_int, _c.c_uint32, _c.c_void_p, _c.c_void_p]),
     "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                           _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,
@@ -251,6 +255,9 @@ def raise_for_bits(v: int, num_classes: Optional[int] = None) -> None:
             + (f" (expected values in [0, {num_classes - 1}])" if num_classes else "")
             + "; the reference raises on the same input when it reshapes its bincount."
         )
+    if v & STATUS_PEER_TIMEOUT:
+        raise RuntimeError("one-shot all-reduce: a peer rank did not arrive within the time limit; the synced state "
+                           "is invalid (set TM_B200_ONESHOT=0 to use NCCL for small states)")
     if v & STATUS_THRESHOLD_ORDER:
         raise RuntimeError("thresholds handed to the binned-curve kernel must be sorted ascending")
 

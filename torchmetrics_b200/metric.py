@@ -417,9 +417,13 @@ class Metric(Module, ABC):
         # forward; nn.Module.__setattr__ walks its parameter / buffer / module tables on every one of them.  A name
         # that already lives directly in __dict__ is none of those, so a non-Parameter, non-Module value can go
         # straight in.
-        if name in self.__dict__ and not isinstance(value, (torch.nn.Parameter, torch.nn.Module)):
-            object.__setattr__(self, name, value)
-            return
+        if name in self.__dict__:
+            # exact-type test first: `isinstance(x, Parameter)` goes through a Python-level __instancecheck__
+            t = type(value)
+            if t is Tensor or value is None or t in _PLAIN_TYPES or not isinstance(value, (torch.nn.Parameter,
+                                                                                            torch.nn.Module)):
+                object.__setattr__(self, name, value)
+                return
         super().__setattr__(name, value)
 
     # ------------------------------------------------------------------ device / dtype
@@ -562,6 +566,9 @@ class Metric(Module, ABC):
 
     def __getnewargs__(self) -> Tuple:
         return tuple(Metric.__str__(self))
+
+
+_PLAIN_TYPES = frozenset((bool, int, float, str, list, dict, tuple))
 
 
 def _neg(x: Tensor) -> Tensor:

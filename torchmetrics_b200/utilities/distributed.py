@@ -81,6 +81,79 @@ def _wire_dtype(op: str, dtype: torch.dtype) -> torch.dtype:
     return dtype
 
 
+# -------------------------------------------------------------------------------------------------
+# K5: one-shot all-reduce of KB-sized arenas over NVLink peer memory (tmb_oneshot_allreduce)
+# -------------------------------------------------------------------------------------------------
+import os as _os
+
+_ONESHOT: Dict[Any, Any] = {}
+_ONESHOT_OFF = _os.environ.get("TM_B200_ONESHOT", "1") == "0"
+_ONESHOT_OPS = {dist.ReduceOp.SUM: 0, dist.ReduceOp.MAX: 1, dist.ReduceOp.MIN: 2}
+_ONESHOT_DTYPES = (torch.int64, torch.int32, torch.float32, torch.float64)
+
+
+class _OneShot:
+    """Per process group: this rank's symmetric buffer, the device table of every rank's mapping of it, the epoch."""
+
+    def __init__(self, group: Any, device: torch.device) -> None:
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from torchmetrics_b200 import _native
+
+        self.lib = _native.load()
+        nbytes = self.lib.tmb_oneshot_buffer_bytes()
+        self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        hdl = symm_mem.rendezvous(self.buf, group.group_name)
+        self.rank, self.world = hdl.rank, hdl.world_size
+        self.peers = torch.tensor(list(hdl.buffer_ptrs), dtype=torch.int64, device=device)
+        torch.cuda.synchronize(device)
+        hdl.barrier()  # every rank's flags are zero before anybody's first call
+        torch.cuda.synchronize(device)
+        self.hdl = hdl
+        self.epoch = 0
+        self._status_ptr, self._dev = None, None
+
+    def all_reduce(self, src: Tensor, dst: Tensor, rop: Any) -> None:
+        """dst = reduce over ranks of src (same shape / dtype, contiguous; may be the same tensor)."""
+        from torchmetrics_b200 import _native
+
+        self.epoch += 1
+        dev = src.device
+        if self._status_ptr is None or self._dev != dev:
+            self._dev, self._status_ptr = dev, _native.scratch(dev).status.data_ptr()
+            self._peers_ptr, self._fn = self.peers.data_ptr(), self.lib.tmb_oneshot_allreduce
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        if torch.cuda.current_device() == dev.index:
+            rc = self._fn(self._peers_ptr, self.world, self.rank, src.data_ptr(), dst.data_ptr(), src.numel(),
+                          _native._DTYPES[src.dtype], _ONESHOT_OPS[rop], self.epoch, self._status_ptr, stream)
+        else:
+            with torch.cuda.device(dev):
+                rc = self._fn(self._peers_ptr, self.world, self.rank, src.data_ptr(), dst.data_ptr(), src.numel(),
+                              _native._DTYPES[src.dtype], _ONESHOT_OPS[rop], self.epoch, self._status_ptr, stream)
+        if rc:
+            _native._check(rc, "tmb_oneshot_allreduce")
+
+
+def _oneshot_for(device: torch.device, dtype: torch.dtype, nbytes: int, rop: Any, group: Any) -> Optional[_OneShot]:
+    """The one-shot context when this reduction qualifies (CUDA arena of at most 64 KB, NCCL group, supported dtype and
+    op; TM_B200_ONESHOT=0 switches it off), else None.  The decision depends only on things every rank agrees on."""
+    if (device.type != "cuda" or dtype not in _ONESHOT_DTYPES or rop not in _ONESHOT_OPS or nbytes > 65536
+            or nbytes == 0 or _ONESHOT_OFF):
+        return None
+    key = id(group)
+    ctx = _ONESHOT.get(key)
+    if ctx is None:
+        try:
+            if "nccl" not in str(dist.get_backend(group)) or dist.get_world_size(group) > 64:
+                raise RuntimeError("not an NCCL group of at most 64 ranks")
+            ctx = _OneShot(group, device)
+        except Exception:  # no symmetric memory on this system / group: NCCL it is, on every rank alike
+            ctx = False
+        _ONESHOT[key] = ctx
+    return ctx or None
+
+
 def fused_reduce(tensors: Sequence[Tuple[str, Tensor]], group: Optional[Any] = None) -> List[Tensor]:
     """All-reduce several tensors with as few collectives as possible.
 
@@ -97,12 +170,22 @@ def fused_reduce(tensors: Sequence[Tuple[str, Tensor]], group: Optional[Any] = N
     for i, (op, t) in enumerate(tensors):
         buckets.setdefault((_REDUCE_OPS[op], _wire_dtype(op, t.dtype), t.device), []).append(i)
     for (rop, wire, device), idxs in buckets.items():
-        if len(idxs) == 1:
-            t = tensors[idxs[0]][1].detach()
-            arena = t.reshape(-1).to(wire, copy=True)
+        single = tensors[idxs[0]][1].detach() if len(idxs) == 1 else None
+        nbytes = sum(tensors[i][1].numel() for i in idxs) * wire.itemsize
+        oneshot = _oneshot_for(device, wire, nbytes, rop, group)
+        if oneshot is not None and single is not None and single.dtype == wire and single.is_contiguous():
+            # one state, KB-sized: the kernel reads the state itself and writes the merged copy (no packing pass)
+            arena = torch.empty(single.numel(), dtype=wire, device=device)
+            oneshot.all_reduce(single, arena, rop)
         else:
-            arena = torch.cat([tensors[i][1].detach().reshape(-1).to(wire) for i in idxs])
-        dist.all_reduce(arena, op=rop, group=group)
+            if single is not None:
+                arena = single.reshape(-1).to(wire, copy=True)
+            else:
+                arena = torch.cat([tensors[i][1].detach().reshape(-1).to(wire) for i in idxs])
+            if oneshot is not None:
+                oneshot.all_reduce(arena, arena, rop)  # one kernel over NVLink peer memory instead of NCCL
+            else:
+                dist.all_reduce(arena, op=rop, group=group)
         off = 0
         for i in idxs:
             op, t = tensors[i]
