@@ -80,6 +80,7 @@ extern "C" {
 #define TMB_REDUCE_MAX 1
 #define TMB_REDUCE_MIN 2
 #define TMB_ONESHOT_SLOT_BYTES 65536 /* largest arena one call can reduce */
+#define TMB_ONESHOT_MAX_SEGMENTS 16  /* source tensors one packed call can take */
 
 TMB_API int tmb_abi_version(void);
 TMB_API const char* tmb_last_cuda_error(void);
@@ -332,6 +333,13 @@ TMB_API size_t tmb_oneshot_buffer_bytes(void);
 TMB_API int tmb_oneshot_allreduce(void* const* peer_buffers_dev, int world, int rank, const void* src_dev,
                                   void* dst_dev, int64_t count, int dtype, int op, uint32_t epoch,
                                   int32_t* status_dev, void* stream);
+/* The same with the local arena scattered over up to TMB_ONESHOT_MAX_SEGMENTS device tensors of one dtype (the
+ * tp / fp / tn / fn states of a metric, say): srcs / counts are HOST arrays; the segments are packed on the way into
+ * the rank's slot and dst_dev receives the reduced arena in segment order (sum of counts elements). */
+TMB_API int tmb_oneshot_allreduce_packed(void* const* peer_buffers_dev, int world, int rank,
+                                         const void* const* srcs_dev_ptrs, const int64_t* counts, int num_segments,
+                                         void* dst_dev, int dtype, int op, uint32_t epoch, int32_t* status_dev,
+                                         void* stream);
 
 #ifdef __cplusplus
 }

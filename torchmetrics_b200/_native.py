@@ -87,6 +87,9 @@ _SIGNATURES = {
     "tmb_oneshot_buffer_bytes": (_c.c_size_t, []),
     "tmb_oneshot_allreduce": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int64,
                                          _c.c_int, _c.c_int, _c.c_uint32, _c.c_void_p, _c.c_void_p]),
+    "tmb_oneshot_allreduce_packed": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int,
+                                                _c.c_void_p, _c.c_int, _c.c_int, _c.c_uint32, _c.c_void_p,
+                                                _c.c_void_p]),
     "tmb_stat_scores_workspace_bytes": (_c.c_size_t, [_c.c_int64]),
     "tmb_stat_scores_update": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                           _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_int, _c.c_void_p,

@@ -40,9 +40,16 @@ __device__ __forceinline__ T combine(T a, T b) {
   else return b < a ? b : a;
 }
 
+// the local arena may be scattered over several state tensors: they are packed on the way into the slot
+struct OsaSegments {
+  const void* ptr[TMB_ONESHOT_MAX_SEGMENTS];
+  long long count[TMB_ONESHOT_MAX_SEGMENTS];
+  int n;
+};
+
 template <typename T, int OP>
 __global__ void __launch_bounds__(kOsaThreads) oneshot_allreduce_kernel(unsigned char* const* __restrict__ peers,
-                                                                        int world, int rank, const T* __restrict__ src,
+                                                                        int world, int rank, const OsaSegments segs,
                                                                         T* __restrict__ dst, long long count, u32 epoch,
                                                                         int* status) {
   __shared__ int s_timeout;
@@ -52,7 +59,14 @@ __global__ void __launch_bounds__(kOsaThreads) oneshot_allreduce_kernel(unsigned
   if (tid == 0) s_timeout = 0;
   // 1. publish the local arena in this rank's slot
   T* mine = reinterpret_cast<T*>(peers[rank] + slot_off);
-  for (long long i = tid; i < count; i += kOsaThreads) mine[i] = src[i];
+  {
+    long long base = 0;
+    for (int k = 0; k < segs.n; ++k) {
+      const T* __restrict__ src = static_cast<const T*>(segs.ptr[k]);
+      for (long long i = tid; i < segs.count[k]; i += kOsaThreads) mine[base + i] = src[i];
+      base += segs.count[k];
+    }
+  }
   __threadfence_system();
   __syncthreads();
   // 2. tell every peer (and this rank) that the slot of this epoch is complete
@@ -82,19 +96,19 @@ __global__ void __launch_bounds__(kOsaThreads) oneshot_allreduce_kernel(unsigned
 }
 
 template <typename T>
-static int launch_osa(unsigned char* const* peers, int world, int rank, const void* src, void* dst, long long count,
-                      int op, u32 epoch, int* status, cudaStream_t st) {
+static int launch_osa(unsigned char* const* peers, int world, int rank, const OsaSegments& src, void* dst,
+                      long long count, int op, u32 epoch, int* status, cudaStream_t st) {
   switch (op) {
     case TMB_REDUCE_SUM:
-      oneshot_allreduce_kernel<T, TMB_REDUCE_SUM><<<1, kOsaThreads, 0, st>>>(peers, world, rank, (const T*)src, (T*)dst,
+      oneshot_allreduce_kernel<T, TMB_REDUCE_SUM><<<1, kOsaThreads, 0, st>>>(peers, world, rank, src, (T*)dst,
                                                                              count, epoch, status);
       break;
     case TMB_REDUCE_MAX:
-      oneshot_allreduce_kernel<T, TMB_REDUCE_MAX><<<1, kOsaThreads, 0, st>>>(peers, world, rank, (const T*)src, (T*)dst,
+      oneshot_allreduce_kernel<T, TMB_REDUCE_MAX><<<1, kOsaThreads, 0, st>>>(peers, world, rank, src, (T*)dst,
                                                                              count, epoch, status);
       break;
     case TMB_REDUCE_MIN:
-      oneshot_allreduce_kernel<T, TMB_REDUCE_MIN><<<1, kOsaThreads, 0, st>>>(peers, world, rank, (const T*)src, (T*)dst,
+      oneshot_allreduce_kernel<T, TMB_REDUCE_MIN><<<1, kOsaThreads, 0, st>>>(peers, world, rank, src, (T*)dst,
                                                                              count, epoch, status);
       break;
     default:
@@ -112,23 +126,50 @@ extern "C" size_t tmb_oneshot_buffer_bytes(void) {
   return (size_t)2 * TMB_ONESHOT_SLOT_BYTES + (size_t)2 * kOsaMaxWorld * sizeof(u32);
 }
 
-extern "C" int tmb_oneshot_allreduce(void* const* peer_buffers_dev, int world, int rank, const void* src, void* dst,
-                                     int64_t count, int dtype, int op, uint32_t epoch, int32_t* status, void* stream) {
+static int osa_dispatch(void* const* peer_buffers_dev, int world, int rank, const OsaSegments& segs, void* dst,
+                        int64_t count, int dtype, int op, uint32_t epoch, int32_t* status, void* stream) {
   if (!peer_buffers_dev || world < 1 || world > kOsaMaxWorld || rank < 0 || rank >= world || count < 0 || !status ||
       epoch == 0)
     return TMB_ERR_ARG;
   if (count == 0) return TMB_OK;
-  if (!src || !dst) return TMB_ERR_ARG;
+  if (!dst) return TMB_ERR_ARG;
   const int esize = dtype_size(dtype);
   if (esize == 0) return TMB_ERR_ARG;
   if ((size_t)count * esize > (size_t)TMB_ONESHOT_SLOT_BYTES) return TMB_ERR_TOO_LARGE;
   cudaStream_t st = (cudaStream_t)stream;
   unsigned char* const* peers = reinterpret_cast<unsigned char* const*>(peer_buffers_dev);
   switch (dtype) {
-    case TMB_I64: return launch_osa<long long>(peers, world, rank, src, dst, count, op, epoch, status, st);
-    case TMB_I32: return launch_osa<int>(peers, world, rank, src, dst, count, op, epoch, status, st);
-    case TMB_F32: return launch_osa<float>(peers, world, rank, src, dst, count, op, epoch, status, st);
-    case TMB_F64: return launch_osa<double>(peers, world, rank, src, dst, count, op, epoch, status, st);
+    case TMB_I64: return launch_osa<long long>(peers, world, rank, segs, dst, count, op, epoch, status, st);
+    case TMB_I32: return launch_osa<int>(peers, world, rank, segs, dst, count, op, epoch, status, st);
+    case TMB_F32: return launch_osa<float>(peers, world, rank, segs, dst, count, op, epoch, status, st);
+    case TMB_F64: return launch_osa<double>(peers, world, rank, segs, dst, count, op, epoch, status, st);
     default: return TMB_ERR_ARG;
   }
+}
+
+extern "C" int tmb_oneshot_allreduce(void* const* peer_buffers_dev, int world, int rank, const void* src, void* dst,
+                                     int64_t count, int dtype, int op, uint32_t epoch, int32_t* status, void* stream) {
+  if (count > 0 && !src) return TMB_ERR_ARG;
+  OsaSegments segs{};
+  segs.ptr[0] = src;
+  segs.count[0] = count;
+  segs.n = 1;
+  return osa_dispatch(peer_buffers_dev, world, rank, segs, dst, count, dtype, op, epoch, status, stream);
+}
+
+extern "C" int tmb_oneshot_allreduce_packed(void* const* peer_buffers_dev, int world, int rank,
+                                            const void* const* srcs, const int64_t* counts, int num_segments,
+                                            void* dst, int dtype, int op, uint32_t epoch, int32_t* status,
+                                            void* stream) {
+  if (!srcs || !counts || num_segments < 1 || num_segments > TMB_ONESHOT_MAX_SEGMENTS) return TMB_ERR_ARG;
+  OsaSegments segs{};
+  int64_t total = 0;
+  for (int k = 0; k < num_segments; ++k) {
+    if (counts[k] < 0 || (counts[k] > 0 && !srcs[k])) return TMB_ERR_ARG;
+    segs.ptr[k] = srcs[k];
+    segs.count[k] = counts[k];
+    total += counts[k];
+  }
+  segs.n = num_segments;
+  return osa_dispatch(peer_buffers_dev, world, rank, segs, dst, total, dtype, op, epoch, status, stream);
 }

@@ -134,6 +134,33 @@ class _OneShot:
         if rc:
             _native._check(rc, "tmb_oneshot_allreduce")
 
+    def all_reduce_packed(self, parts: Sequence[Tensor], dst: Tensor, rop: Any) -> None:
+        """dst (flat) = reduce over ranks of the concatenation of `parts` (device tensors of dst's dtype)."""
+        from torchmetrics_b200 import _native
+
+        if len(parts) == 1:
+            return self.all_reduce(parts[0], dst, rop)
+        self.epoch += 1
+        dev = dst.device
+        if self._status_ptr is None or self._dev != dev:
+            self._dev, self._status_ptr = dev, _native.scratch(dev).status.data_ptr()
+            self._peers_ptr, self._fn = self.peers.data_ptr(), self.lib.tmb_oneshot_allreduce
+        srcs, counts, k = _packed_args(parts)
+        with torch.cuda.device(dev):
+            rc = self.lib.tmb_oneshot_allreduce_packed(self._peers_ptr, self.world, self.rank, srcs, counts, k,
+                                                       dst.data_ptr(), _native._DTYPES[dst.dtype], _ONESHOT_OPS[rop],
+                                                       self.epoch, self._status_ptr,
+                                                       torch.cuda.current_stream(dev).cuda_stream)
+        if rc:
+            _native._check(rc, "tmb_oneshot_allreduce_packed")
+
+
+def _packed_args(parts: Sequence[Tensor]):
+    import ctypes
+
+    k = len(parts)
+    return ((ctypes.c_void_p * k)(*[p.data_ptr() for p in parts]), (ctypes.c_int64 * k)(*[p.numel() for p in parts]), k)
+
 
 def _oneshot_for(device: torch.device, dtype: torch.dtype, nbytes: int, rop: Any, group: Any) -> Optional[_OneShot]:
     """The one-shot context when this reduction qualifies (CUDA arena of at most 64 KB, NCCL group, supported dtype and
@@ -173,10 +200,13 @@ def fused_reduce(tensors: Sequence[Tuple[str, Tensor]], group: Optional[Any] = N
         single = tensors[idxs[0]][1].detach() if len(idxs) == 1 else None
         nbytes = sum(tensors[i][1].numel() for i in idxs) * wire.itemsize
         oneshot = _oneshot_for(device, wire, nbytes, rop, group)
-        if oneshot is not None and single is not None and single.dtype == wire and single.is_contiguous():
-            # one state, KB-sized: the kernel reads the state itself and writes the merged copy (no packing pass)
-            arena = torch.empty(single.numel(), dtype=wire, device=device)
-            oneshot.all_reduce(single, arena, rop)
+        parts = [tensors[i][1].detach() for i in idxs]
+        if (oneshot is not None and len(parts) <= 16
+                and all(p.dtype == wire and p.is_contiguous() for p in parts)):
+            # KB-sized states: the kernel reads the state tensors themselves, packs them on the way into this rank's
+            # slot and writes the merged arena (no torch.cat / clone pass, no NCCL call)
+            arena = torch.empty(nbytes // wire.itemsize, dtype=wire, device=device)
+            oneshot.all_reduce_packed(parts, arena, rop)
         else:
             if single is not None:
                 arena = single.reshape(-1).to(wire, copy=True)
