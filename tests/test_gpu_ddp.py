@@ -145,7 +145,8 @@ def _body_oneshot_allreduce(rank, world):
                 want = x.clone()
                 dist.all_reduce(want, op={"sum": dist.ReduceOp.SUM, "max": dist.ReduceOp.MAX, "min": dist.ReduceOp.MIN}[op])
                 got = D.fused_reduce([(op, x)])[0]
-                if n * x.element_size() * world <= 131072:
+                wire_bytes = n * D._wire_dtype(op, dtype).itemsize  # narrow integer sums travel as int64
+                if wire_bytes <= 65536 and wire_bytes * world <= 131072:
                     used += 1
                 if dtype.is_floating_point and op == "sum":
                     assert torch.allclose(got, want, rtol=1e-5, atol=1e-5)
