@@ -315,6 +315,34 @@ TMB_API int tmb_class_stats_rows(const void* preds_dev, int preds_dtype, const v
                                  int64_t ignore_index, int64_t* out_dev, int32_t* status_dev, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Fused reducer: count states -> score, one launch.
+ * Replaces: the chain of elementwise / reduction ops behind `compute()` of the stat-score family:
+ *           `_safe_divide` + `_adjust_weights_safe_divide` (utilities/compute.py:46-69) as used by
+ *           `_precision_recall_reduce` (precision_recall.py:37-57), `_fbeta_reduce` (f_beta.py:37-57),
+ *           `_accuracy_reduce` (accuracy.py:37-86), `_specificity_reduce` (specificity.py:37-58).
+ * tp / fp / tn / fn: int64[rows * num_labels], row-major (rows = 1 for `multidim_average="global"`).
+ * kind: TMB_STAT_*; accuracy of a multiclass task is TMB_STAT_RECALL (tp / (tp + fn)), of a binary / multilabel task
+ *   TMB_STAT_ACCURACY ((tp + tn) / all).  beta is only read for TMB_STAT_FBETA.
+ * average: TMB_AVERAGE_NONE (also the reference's "binary"): one score per element, out: float32[rows * num_labels];
+ *   _MICRO: the counts are summed over the labels first, out: float32[rows];
+ *   _MACRO, _WEIGHTED: out: float32[rows * num_labels] holds the terms w_l * score_l / sum_l w_l whose sum over the
+ *   labels is the average (the caller adds them with the same torch.sum the reference uses, so the last bit agrees).
+ *   multilabel == 0 gives a class with tp + fp + fn == 0 weight 0 in the macro average.
+ * Every value written is bit-identical to the reference's float32 arithmetic. */
+#define TMB_STAT_PRECISION 0
+#define TMB_STAT_RECALL 1
+#define TMB_STAT_SPECIFICITY 2
+#define TMB_STAT_ACCURACY 3
+#define TMB_STAT_FBETA 4
+#define TMB_AVERAGE_NONE 0
+#define TMB_AVERAGE_MICRO 1
+#define TMB_AVERAGE_MACRO 2
+#define TMB_AVERAGE_WEIGHTED 3
+TMB_API int tmb_stat_reduce(const int64_t* tp_dev, const int64_t* fp_dev, const int64_t* tn_dev, const int64_t* fn_dev,
+                            int64_t rows, int64_t num_labels, int kind, int average, int multilabel, double beta,
+                            float* out_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * K5  one-shot all-reduce of a small state arena over NVLink peer memory.
  * Replaces: the collective behind `Metric._sync_dist` (metric.py:427-457: one `gather_all_tensors`,
  *           utilities/distributed.py:97-147, per state, then stack + sum) for arenas up to TMB_ONESHOT_SLOT_BYTES:

@@ -913,3 +913,97 @@ def test_exact_auroc_ap_offsets_add_up():
     assert a == whole[0]  # integer-valued terms below 2^53: exact
     assert abs(b - whole[1]) <= 1e-9 * whole[1]
     assert sum(pos) == whole[2]
+
+
+# ---------------------------------------------------------------------------------------------
+# fused reducers (tmb_stat_reduce): the CUDA path against the torch-op path of the same functions on CPU copies
+# ---------------------------------------------------------------------------------------------
+def _reduce_states(shape, big, seed):
+    g = torch.Generator().manual_seed(seed)
+    hi = (1 << 40) if big else 50
+    st = [torch.randint(0, hi, shape, generator=g, dtype=torch.int64) for _ in range(4)]
+    if len(shape):  # classes that never occur, zero denominators
+        for t in st:
+            t[..., 0] = 0
+        if shape[-1] > 2:
+            st[0][..., 2] = 0
+            st[1][..., 2] = 0
+    return st
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("big", [False, True])
+@pytest.mark.parametrize("shape,mda", [((), "global"), ((1,), "global"), ((5,), "global"), ((100,), "global"),
+                                       ((1000,), "global"), ((37, 7), "samplewise"), ((3, 100), "samplewise"),
+                                       ((37,), "samplewise")])
+def test_stat_reduce_matches_torch_ops(shape, mda, big):
+    from torchmetrics_b200.functional.classification.accuracy import _accuracy_reduce
+    from torchmetrics_b200.functional.classification.f_beta import _fbeta_reduce
+    from torchmetrics_b200.functional.classification.precision_recall import _precision_recall_reduce
+    from torchmetrics_b200.functional.classification.specificity import _specificity_reduce
+
+    tp, fp, tn, fn = _reduce_states(shape, big, 7 + len(shape))
+    dev = [t.to(DEV) for t in (tp, fp, tn, fn)]
+    reducers = [
+        ("precision", lambda *a, **k: _precision_recall_reduce("precision", *a, **k)),
+        ("recall", lambda *a, **k: _precision_recall_reduce("recall", *a, **k)),
+        ("specificity", _specificity_reduce),
+        ("accuracy", _accuracy_reduce),
+        ("f1", lambda tp, fp, tn, fn, **k: _fbeta_reduce(tp, fp, tn, fn, 1.0, **k)),
+        ("f0.5", lambda tp, fp, tn, fn, **k: _fbeta_reduce(tp, fp, tn, fn, 0.5, **k)),
+        ("f2", lambda tp, fp, tn, fn, **k: _fbeta_reduce(tp, fp, tn, fn, 2.0, **k)),
+    ]
+    if len(shape) == 0 or (mda == "samplewise" and len(shape) == 1):
+        averages = ["binary"]
+    else:
+        averages = ["micro", "macro", "weighted", "none", None]
+    from torchmetrics_b200 import _native
+
+    supported = _native.stat_reduce_supported
+    for name, fn_ in reducers:
+        for average in averages:
+            for multilabel in (False, True):
+                kw = dict(average=average, multidim_average=mda, multilabel=multilabel)
+                want = fn_(tp, fp, tn, fn, **kw)
+                got = fn_(*dev, **kw)
+                _native.stat_reduce_supported = lambda *a: False  # the same torch ops on the GPU
+                try:
+                    torch_ops = fn_(*dev, **kw)
+                finally:
+                    _native.stat_reduce_supported = supported
+                assert got.is_cuda and got.dtype == want.dtype and got.shape == want.shape, (name, kw)
+                assert torch.equal(got, torch_ops), (name, kw, got, torch_ops)  # bit for bit
+                if average in ("binary", "none", None, "micro"):
+                    assert torch.equal(got.cpu(), want), (name, kw)
+                else:  # torch adds the terms in a different order on the CPU
+                    assert torch.allclose(got.cpu(), want, rtol=2e-6, atol=1e-7), (name, kw, got.cpu(), want)
+
+
+@pytest.mark.gpu
+def test_stat_reduce_is_one_launch_per_metric():
+    """compute() of the precision / recall / F1 modules goes through the fused kernel (same values as the functional
+    form evaluated from CPU states)."""
+    import torchmetrics_b200 as tm
+    from torchmetrics_b200 import _native
+
+    L = 100
+    g = torch.Generator().manual_seed(3)
+    p = torch.rand(4096, L, generator=g)
+    t = torch.randint(0, 2, (4096, L), generator=g)
+    calls = []
+    orig = _native.stat_reduce
+    _native.stat_reduce = lambda *a, **k: (calls.append(a[0]), orig(*a, **k))[1]
+    try:
+        for cls in (tm.MultilabelPrecision, tm.MultilabelRecall, tm.MultilabelF1Score, tm.MultilabelAccuracy,
+                    tm.MultilabelSpecificity):
+            m = cls(num_labels=L).to(DEV)
+            m.update(p.to(DEV), t.to(DEV))
+            got = m.compute()
+            tp, fp, tn, fn = (getattr(m, k).cpu() for k in ("tp", "fp", "tn", "fn"))
+            ref = cls(num_labels=L)
+            ref.tp, ref.fp, ref.tn, ref.fn = tp, fp, tn, fn
+            ref._update_count = 1
+            assert torch.allclose(got.cpu(), ref.compute(), rtol=2e-6, atol=1e-7), cls.__name__
+    finally:
+        _native.stat_reduce = orig
+    assert len(calls) == 5  # one launch per compute() (plus torch.sum over the labels for the macro average)

@@ -98,6 +98,8 @@ _SIGNATURES = {
                                         _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p]),
     "tmb_class_stats_rows": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                         _c.c_int64, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_void_p]),
+    "tmb_stat_reduce": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_int,
+                                   _c.c_int, _c.c_int, _c.c_double, _c.c_void_p, _c.c_void_p]),
 }
 
 _lib = None
@@ -472,6 +474,39 @@ def class_stats_rows(preds: Tensor, target: Tensor, num_classes: int, ignore_ind
         raise RuntimeError("tmb_class_stats_rows failed with TMB_ERR_TOO_LARGE: " + load().tmb_last_cuda_error().decode())
     _check(rc, "tmb_class_stats_rows")
     return out
+
+
+STAT_PRECISION, STAT_RECALL, STAT_SPECIFICITY, STAT_ACCURACY, STAT_FBETA = range(5)
+_AVERAGE_CODES = {None: 0, "none": 0, "binary": 0, "micro": 1, "macro": 2, "weighted": 3}
+
+
+def stat_reduce_supported(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str]) -> bool:
+    """True when `stat_reduce` serves these states: int64 CUDA tensors of one shape, a known averaging mode."""
+    return (tp.is_cuda and average in _AVERAGE_CODES and tp.dtype == torch.int64 and fp.dtype == torch.int64
+            and tn.dtype == torch.int64 and fn.dtype == torch.int64 and tp.ndim <= 2
+            and tp.shape == fp.shape == tn.shape == fn.shape and fp.device == tn.device == fn.device == tp.device)
+
+
+def stat_reduce(kind: int, tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str],
+                multilabel: bool = False, beta: float = 1.0) -> Tensor:
+    """float32 score of the tp / fp / tn / fn states in one launch (`tmb_stat_reduce`).  The last dimension holds the
+    classes / labels; "micro", "macro" and "weighted" reduce it, None / "none" / "binary" keep the shape."""
+    dev = tp.device
+    code = _AVERAGE_CODES[average]
+    labels = tp.shape[-1] if tp.ndim else 1
+    rows = tp.numel() // labels if labels else 0
+    # micro reduces the labels inside the kernel; macro / weighted come back as terms that torch.sum adds up
+    out = torch.empty(tp.shape[:-1] if code == 1 else tp.shape, dtype=torch.float32, device=dev)
+    if out.numel() == 0:
+        return out.sum(-1) if code >= 2 and tp.ndim else out
+    if labels == 0:  # micro over no labels: 0 / 1
+        return out.zero_()
+    tp, fp, tn, fn = tp.contiguous(), fp.contiguous(), tn.contiguous(), fn.contiguous()
+    with torch.cuda.device(dev):
+        rc = load().tmb_stat_reduce(tp.data_ptr(), fp.data_ptr(), tn.data_ptr(), fn.data_ptr(), rows, labels, kind,
+                                    code, bool(multilabel), float(beta), out.data_ptr(), _stream_ptr(dev))
+    _check(rc, "tmb_stat_reduce")
+    return out.sum(-1) if code >= 2 else out
 
 
 def exact_curve(preds: Tensor, target: Tensor, pos_label: int = 1):

@@ -6,13 +6,18 @@ from torch import Tensor
 from typing_extensions import Literal
 
 D = import_module("torchmetrics_b200.functional.classification._derived")
-from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _safe_divide
+from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _fused_stat_reduce, _safe_divide
 from torchmetrics_b200.utilities.enums import ClassificationTask
 
 
 def _accuracy_reduce(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str],
                      multidim_average: str = "global", multilabel: bool = False) -> Tensor:
     """(tp+tn)/all for binary and multilabel, tp/(tp+fn) per class for multiclass (accuracy.py:37-86)."""
+    # (tp + tn) / all for binary and multilabel states, tp / (tp + fn) for multiclass ones
+    fused = _fused_stat_reduce("accuracy" if multilabel or average == "binary" else "recall", tp, fp, tn, fn, average,
+                               multidim_average, multilabel)
+    if fused is not None:
+        return fused
     if average == "binary":
         return _safe_divide(tp + tn, tp + tn + fp + fn)
     if average == "micro":

@@ -7,13 +7,16 @@ from torch import Tensor
 from typing_extensions import Literal
 
 D = import_module("torchmetrics_b200.functional.classification._derived")
-from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _safe_divide
+from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _fused_stat_reduce, _safe_divide
 from torchmetrics_b200.utilities.enums import ClassificationTask
 
 
 def _fbeta_reduce(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, beta: float, average: Optional[str],
                   multidim_average: str = "global", multilabel: bool = False) -> Tensor:
     """(1+b^2) tp / ((1+b^2) tp + b^2 fn + fp) (f_beta.py:37-57)."""
+    fused = _fused_stat_reduce("fbeta", tp, fp, tn, fn, average, multidim_average, multilabel, beta)
+    if fused is not None:
+        return fused
     b2 = beta ** 2
     if average == "binary":
         return _safe_divide((1 + b2) * tp, (1 + b2) * tp + b2 * fn + fp)

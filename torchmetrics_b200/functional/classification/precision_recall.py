@@ -7,7 +7,7 @@ from torch import Tensor
 from typing_extensions import Literal
 
 D = import_module("torchmetrics_b200.functional.classification._derived")
-from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _safe_divide
+from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _fused_stat_reduce, _safe_divide
 from torchmetrics_b200.utilities.enums import ClassificationTask
 
 
@@ -15,6 +15,9 @@ def _precision_recall_reduce(stat: Literal["precision", "recall"], tp: Tensor, f
                              average: Optional[str], multidim_average: str = "global",
                              multilabel: bool = False) -> Tensor:
     """tp / (tp + fp) or tp / (tp + fn) (precision_recall.py:37-57)."""
+    fused = _fused_stat_reduce(stat, tp, fp, tn, fn, average, multidim_average, multilabel)
+    if fused is not None:
+        return fused
     other = fp if stat == "precision" else fn
     if average == "binary":
         return _safe_divide(tp, tp + other)

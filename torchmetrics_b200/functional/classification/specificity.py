@@ -7,12 +7,15 @@ from torch import Tensor
 from typing_extensions import Literal
 
 D = import_module("torchmetrics_b200.functional.classification._derived")
-from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _safe_divide
+from torchmetrics_b200.utilities.compute import _adjust_weights_safe_divide, _fused_stat_reduce, _safe_divide
 from torchmetrics_b200.utilities.enums import ClassificationTask
 
 
 def _specificity_reduce(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str],
                         multidim_average: str = "global", multilabel: bool = False) -> Tensor:
+    fused = _fused_stat_reduce("specificity", tp, fp, tn, fn, average, multidim_average, multilabel)
+    if fused is not None:
+        return fused
     if average == "micro":
         d = 0 if multidim_average == "global" else 1
         tn, fp = tn.sum(dim=d), fp.sum(dim=d)

@@ -1,11 +1,29 @@
 """O(C) / O(T) reducers that turn count states into scores (reference: utilities/compute.py:46-157).
 
-These run on a few hundred elements per compute(); they stay torch ops on whatever device the state is on.
+On CPU tensors these are the reference's torch ops.  For int64 count states on a CUDA device the stat-score family
+(`_fused_stat_reduce`) runs the whole chain in one kernel launch (`tmb_stat_reduce`), which is what `compute()` costs.
 """
 from typing import Optional, Tuple
 
 import torch
 from torch import Tensor
+
+
+def _fused_stat_reduce(kind: str, tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str],
+                       multidim_average: str = "global", multilabel: bool = False, beta: float = 1.0) -> Optional[Tensor]:
+    """precision / recall / specificity / accuracy / fbeta of CUDA int64 states in one launch, or None when the states
+    are not served by the kernel (CPU tensors, other dtypes): the caller then runs the reference's torch ops."""
+    if not tp.is_cuda:
+        return None
+    from torchmetrics_b200 import _native as N
+
+    if not N.stat_reduce_supported(tp, fp, tn, fn, average):
+        return None
+    if average in ("micro", "macro", "weighted") and tp.ndim not in (0, 1 if multidim_average == "global" else 2):
+        return None
+    code = {"precision": N.STAT_PRECISION, "recall": N.STAT_RECALL, "specificity": N.STAT_SPECIFICITY,
+            "accuracy": N.STAT_ACCURACY, "fbeta": N.STAT_FBETA}[kind]
+    return N.stat_reduce(code, tp, fp, tn, fn, average, multilabel, beta)
 
 
 def _safe_divide(num: Tensor, denom: Tensor) -> Tensor:
