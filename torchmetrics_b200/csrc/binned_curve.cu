@@ -231,8 +231,6 @@ __global__ void __launch_bounds__(kWarpHistThreads, 2) binned_warphist_kernel(co
   constexpr bool SIGMOID = MODE == kModeSigmoid;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BinnedWs* ws = P.ws;
-  if (P.only_if_flag && ws->flag_oor == 0) return;
-
   const int NT = kWarpHistThreads, tid = threadIdx.x, warp = tid >> 5;
   const int T = P.T, NB = T + 1, NB2 = 2 * NB;
   const int copies = P.hist_copies;
@@ -243,6 +241,11 @@ __global__ void __launch_bounds__(kWarpHistThreads, 2) binned_warphist_kernel(co
   __shared__ int s_last;
 
   for (int i = tid; i < copies * NB2; i += NT) s_hist[i] = 0;
+  // Launched with programmatic stream serialisation: the launch and everything above overlap the tail of the kernel
+  // before this one in the stream (the previous update, or the first pass of an AUTO update); nothing in global
+  // memory - not even the thresholds - is read before that kernel has completed.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (P.only_if_flag && *(volatile int*)&ws->flag_oor == 0) return;
   BinMap m;
   const bool sorted = load_thresholds(P.thr, T, s_thr, m);
   if (!sorted) {
@@ -299,6 +302,9 @@ __global__ void __launch_bounds__(kWarpHistThreads, 2) binned_warphist_kernel(co
     }
   };
   if (um.ok) run(std::true_type{}); else run(std::false_type{});
+  // every CTA of this grid is resident (at most two per SM are launched), so the next kernel of the stream may start
+  // taking the places of the CTAs that leave; it waits for this grid to complete before it touches global memory
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (CHECK && oor) atomicOr(&ws->flag_oor, 1);
   if (vbits) report_status(P.status, vbits);
   __syncthreads();
@@ -722,7 +728,17 @@ static int launch_binned(BinnedParams P, int prob_mode, cudaStream_t st) {
       const int mode = sigmoid ? kModeSigmoid : (P.check_range ? kModeAsIsCheck : kModeAsIs);
       auto k = pick_warphist<TT>(mode, P.has_ignore != 0);
       TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k<<<grid, kWarpHistThreads, smem, st>>>(P);
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3((unsigned)grid);
+      cfg.blockDim = dim3(kWarpHistThreads);
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      TMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k, P));
     } else {
       const size_t fixed = (((size_t)NB * 4 + kLutCells * 2 + 7) & ~(size_t)7) + (size_t)2 * NB * 8;
       const size_t with_bins = fixed + (size_t)nbins * 4;

@@ -257,6 +257,10 @@ __global__ void __launch_bounds__(kRegThreads, kRegCtasPerSm) confmat_partition_
   carve(F, smem_reg, s_hot_key, s_hot_cnt);
   const int tid = threadIdx.x;
   F.init(P, tid, kRegThreads);
+  // launched with programmatic stream serialisation: the launch and the set-up above overlap the tail of the kernel
+  // before this one in the stream (phase B of the previous update, which signals early); global memory - the batch,
+  // the queues that phase B may still be reading - is only touched after that kernel has completed
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const PT* __restrict__ preds = static_cast<const PT*>(P.preds);
   const TT* __restrict__ target = static_cast<const TT*>(P.target);
   const long long n = P.n;
@@ -386,10 +390,14 @@ __global__ void __launch_bounds__(kTmaThreads, 1) confmat_partition_tma_kernel(c
       mbar_init(smem_addr(&s_empty[i]), kTmaThreads / 32);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    // the first ring-full of loads is on its way while the CTA clears its counters
-    for (u32 slot = 0; slot < kTmaStages && slot < mine; ++slot) issue(slot, slot);
   }
   F.init(P, tid, kTmaThreads);
+  // launched with programmatic stream serialisation: the launch and the set-up above overlap the tail of the kernel
+  // before this one in the stream (phase B of the previous update, which signals early); global memory - the batch,
+  // the queues that phase B may still be reading - is only touched after that kernel has completed
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (tid == 0)
+    for (u32 slot = 0; slot < kTmaStages && slot < mine; ++slot) issue(slot, slot);
   __syncthreads();
 
   for (u32 k0 = 0; k0 < mine; k0 += kTmaStages) {
@@ -494,6 +502,9 @@ __global__ void __launch_bounds__(kHistThreads) confmat_bucket_hist_kernel(const
     len = len1;
     len1 = len2;
   }
+  // all CTAs of this grid are resident (at most four per SM are launched): the next kernel of the stream may begin
+  // its set-up where CTAs leave; it waits for this grid to complete before it touches global memory
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   __syncthreads();
   for (u32 lbin = threadIdx.x; lbin < kBinsPerBucket; lbin += kHistThreads) {
     const u32 c = h[lbin];
@@ -585,7 +596,17 @@ extern "C" int tmb_confmat_update_ws(const void* preds, int preds_dtype, const v
     TMB_DISPATCH_INT(target_dtype, TT, {
       auto launch = [&](auto kern, int threads) -> int {
         TMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<G, threads, smem, st>>>(P);
+        cudaLaunchConfig_t acfg{};
+        acfg.gridDim = dim3(G);
+        acfg.blockDim = dim3((unsigned)threads);
+        acfg.dynamicSmemBytes = smem;
+        acfg.stream = st;
+        cudaLaunchAttribute aattr[1];
+        aattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        aattr[0].val.programmaticStreamSerializationAllowed = 1;
+        acfg.attrs = aattr;
+        acfg.numAttrs = 1;
+        TMB_CUDA_CHECK(cudaLaunchKernelEx(&acfg, kern, P));
         return TMB_OK;
       };
       int rc;
