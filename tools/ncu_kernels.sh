@@ -4,11 +4,13 @@
 # back in gpurun_out/ are the per-launch CSV summaries of tools/ncu_summary.py (copied to profiles/ by hand) and the
 # SASS-level hot spots of tools/ncu_hot.py.
 # Usage: tools/ncu_kernels.sh [name ...]
-#   names: stat binned binned_multi confmat class_stats rows partition exact exact_auroc
+#   names: stat binned binned_multi confmat class_stats rows partition exact exact_auroc reduce
 set -u
 mkdir -p gpurun_out
 REP=${NCU_REPORT_DIR:-/tmp/ncu_reports}
 mkdir -p "$REP"
+# per-kernel DRAM traffic is merged into a copy of the tracked file; copy gpurun_out/traffic.json back by hand
+[ -f gpurun_out/traffic.json ] || cp profiles/traffic.json gpurun_out/traffic.json 2>/dev/null
 names=("$@")
 [ ${#names[@]} -eq 0 ] && names=(stat binned binned_multi confmat class_stats rows partition exact exact_auroc)
 for name in "${names[@]}"; do
@@ -22,13 +24,14 @@ for name in "${names[@]}"; do
     partition) log2n=25; pat='range_partition_kernel|range_offsets_kernel' ;;
     exact) log2n=24; pat='k4_' ;;
     exact_auroc) log2n=24; pat='k4_' ;;
+    reduce) log2n=23; pat='stat_reduce_kernel' ;;
   esac
   python tools/prof_one.py $name $log2n > gpurun_out/prof_${name}_plain.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k "regex:$pat" -c 12 -f \
+  timeout ${NCU_TIMEOUT:-300} ncu --set full --clock-control none --import-source on -k "regex:$pat" -c 12 -f \
       -o "$REP/r2_${name}" python tools/prof_one.py $name $log2n > gpurun_out/prof_${name}_ncu.log 2>&1
   rc=$?
   if [ $rc -eq 0 ]; then
-    python tools/ncu_summary.py "$REP/r2_${name}.ncu-rep" --out gpurun_out > /dev/null 2>&1
+    python tools/ncu_summary.py "$REP/r2_${name}.ncu-rep" --out gpurun_out --traffic > /dev/null 2>&1
     python tools/ncu_hot.py "$REP/r2_${name}.ncu-rep" "" 25 > gpurun_out/r2_${name}_hot.txt 2>&1
   fi
   echo "$name rc=$rc"

@@ -1,4 +1,4 @@
-"""Run one kernel a few times (for ncu). Usage: python tools/prof_one.py binned|binned_multi|confmat|class_stats|stat|rows|partition|exact|exact_auroc [log2n]"""
+"""Run one kernel a few times (for ncu). Usage: python tools/prof_one.py binned|binned_multi|confmat|class_stats|stat|rows|partition|exact|exact_auroc|reduce [log2n]"""
 import os
 import sys
 
@@ -48,6 +48,15 @@ elif what == "class_stats":
     out = torch.zeros(4, C, dtype=torch.int64, device=DEV)
     for _ in range(4):
         N.class_stats_update_(out, p, t, C)
+elif what == "reduce":
+    # the fused reducer: (rows, 100) samplewise states, then the (100,) global ones of config 5
+    rows = max(1, n // 100)
+    st = [torch.randint(0, 1000, (rows, 100), device=DEV, generator=g) for _ in range(4)]
+    for avg in ("macro", "micro", None):
+        N.stat_reduce(N.STAT_FBETA, *st, avg, True, 1.0)
+    one = [t[0].contiguous() for t in st]
+    for kind in (N.STAT_PRECISION, N.STAT_RECALL, N.STAT_FBETA):
+        N.stat_reduce(kind, *one, "macro", True, 1.0)
 elif what == "exact_auroc":
     preds = torch.rand(n, device=DEV, generator=g)
     target = (torch.rand(n, device=DEV, generator=g) < 0.3 + 0.4 * preds).long()
