@@ -679,3 +679,102 @@ def test_derived_metrics_share_compute_groups_and_validate():
         tm.MulticlassJaccardIndex(C, average="samples")
     with pytest.raises(RuntimeError, match="Detected more unique values in `target`"):
         F.multiclass_matthews_corrcoef(p, t + C * (torch.arange(500, device=DEV) % 2), C)
+
+
+# ------------------------------------------------------------------ packed count states (in-place accumulation)
+@pytest.mark.gpu
+@pytest.mark.parametrize("validate", [False, True])
+def test_stat_scores_states_accumulate_in_place(validate):
+    """The four count states are re-pointed at one buffer the kernel accumulates into; everything that replaces or
+    copies the state tensors (reset, forward, deepcopy, pickle, collections) must keep giving the reference's counts."""
+    import copy
+    import pickle
+
+    tm = _tm()
+    F = tm.functional
+    L = 64  # 512-byte states: separately allocated results can sit next to each other in the allocator
+    g = torch.Generator().manual_seed(11)
+    batches = [(torch.rand(96, L, generator=g).to(DEV), torch.randint(0, 2, (96, L), generator=g).to(DEV))
+               for _ in range(4)]
+
+    def want(idx):
+        p = torch.cat([batches[i][0] for i in idx])
+        t = torch.cat([batches[i][1] for i in idx])
+        return F.multilabel_stat_scores(p, t, L, average=None, validate_args=False)
+
+    m = tm.MultilabelStatScores(num_labels=L, average=None, validate_args=validate).to(DEV)
+    m.update(*batches[0])
+    m.update(*batches[1])
+    assert torch.equal(m.compute(), want([0, 1]))
+    if not validate:  # consecutive rows of one buffer
+        assert m.fp.data_ptr() == m.tp.data_ptr() + 8 * L and m.fn.data_ptr() == m.tp.data_ptr() + 24 * L
+    batch_value = m(*batches[2])  # forward: batch value, and the batch joins the running state
+    assert torch.equal(batch_value, want([2]))
+    assert torch.equal(m.compute(), want([0, 1, 2]))
+    for clone in (copy.deepcopy(m), pickle.loads(pickle.dumps(m))):
+        clone.update(*batches[3])
+        assert torch.equal(clone.compute(), want([0, 1, 2, 3]))
+    assert torch.equal(m.compute(), want([0, 1, 2]))  # the copies did not write into the original
+    with torch.inference_mode():  # states created here are inference tensors: keep updating them in here
+        m.reset()
+        m.update(*batches[3])
+        m.update(*batches[0])
+        m.update(*batches[1])
+        assert torch.equal(m.compute(), want([3, 0, 1]))
+    m.reset()
+    with torch.inference_mode():  # ordinary states, updated under inference mode and after it
+        m.update(*batches[3])
+    m.update(*batches[0])
+    assert torch.equal(m.compute(), want([3, 0]))
+
+    mc = tm.MetricCollection([tm.MultilabelStatScores(num_labels=L, average=None, validate_args=validate),
+                              tm.MultilabelF1Score(num_labels=L, average=None, validate_args=validate),
+                              tm.MultilabelRecall(num_labels=L, average=None, validate_args=validate)]).to(DEV)
+    for rounds in range(2):
+        mc.update(*batches[0])
+        mc.update(*batches[1])
+        out = mc.compute()
+        assert torch.equal(out["MultilabelStatScores"], want([0, 1]))
+        p = torch.cat([batches[0][0], batches[1][0]])
+        t = torch.cat([batches[0][1], batches[1][1]])
+        assert torch.equal(out["MultilabelF1Score"], F.multilabel_f1_score(p, t, L, average=None, validate_args=False))
+        assert torch.equal(out["MultilabelRecall"], F.multilabel_recall(p, t, L, average=None, validate_args=False))
+        mc.reset()
+
+    # binary (one number per state) and multiclass (labels, scores, micro) take the same route
+    b = tm.BinaryStatScores(validate_args=validate).to(DEV)
+    mcl = tm.MulticlassStatScores(num_classes=L, average=None, validate_args=validate).to(DEV)
+    mcs = tm.MulticlassStatScores(num_classes=L, average=None, validate_args=validate).to(DEV)
+    mic = tm.MulticlassStatScores(num_classes=L, average="micro", validate_args=validate).to(DEV)
+    lab = [(torch.randint(0, L, (500,), generator=g).to(DEV), torch.randint(0, L, (500,), generator=g).to(DEV))
+           for _ in range(2)]
+    sc = [(torch.randn(500, L, generator=g).to(DEV), lab[i][1]) for i in range(2)]
+    for i in range(2):
+        b.update(batches[i][0][:, 0], batches[i][1][:, 0])
+        mcl.update(*lab[i])
+        mcs.update(*sc[i])
+        mic.update(*lab[i])
+    bp, bt = torch.cat([batches[0][0][:, 0], batches[1][0][:, 0]]), torch.cat([batches[0][1][:, 0], batches[1][1][:, 0]])
+    assert torch.equal(b.compute(), F.binary_stat_scores(bp, bt, validate_args=False))
+    lp, lt = torch.cat([lab[0][0], lab[1][0]]), torch.cat([lab[0][1], lab[1][1]])
+    assert torch.equal(mcl.compute(), F.multiclass_stat_scores(lp, lt, L, average=None, validate_args=False))
+    assert torch.equal(mic.compute(), F.multiclass_stat_scores(lp, lt, L, average="micro", validate_args=False))
+    assert torch.equal(mcs.compute(), F.multiclass_stat_scores(torch.cat([sc[0][0], sc[1][0]]), lt, L, average=None,
+                                                               validate_args=False))
+
+
+@pytest.mark.gpu
+def test_stat_scores_bad_batch_leaves_state_untouched():
+    """validate_args=True: a batch that fails validation is reported before the states change (the kernel then counts
+    into a scratch tensor, not into the states)."""
+    tm = _tm()
+    L = 8
+    m = tm.MultilabelStatScores(num_labels=L, average=None).to(DEV)
+    good_p, good_t = torch.rand(32, L, device=DEV), torch.randint(0, 2, (32, L), device=DEV)
+    m.update(good_p, good_t)
+    before = m.compute().clone()
+    bad_t = good_t.clone()
+    bad_t[3, 2] = 7
+    with pytest.raises(RuntimeError):
+        m.update(good_p, bad_t)
+    assert torch.equal(m.compute(), before)

@@ -195,7 +195,14 @@ def _aligned(t: Tensor) -> Tensor:
     return t
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream_ptr(dev: torch.device) -> int:
+    """cudaStream_t of torch's current stream on `dev` (the raw getter skips building a Stream object: this is called
+    twice per update)."""
+    if _raw_stream is not None:
+        return _raw_stream(dev.index if dev.index is not None else torch.cuda.current_device())
     return torch.cuda.current_stream(dev).cuda_stream
 
 

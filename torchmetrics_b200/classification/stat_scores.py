@@ -32,7 +32,40 @@ class _AbstractStatScores(Metric):
         for name in ("tp", "fp", "tn", "fn"):
             self.add_state(name, default(), dist_reduce_fx=reduce_fx)
 
-    def _update_state(self, tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor) -> None:
+    def _packed_states(self) -> Optional[Tensor]:
+        """The four global count states as the rows of ONE (4, n) int64 tensor, so that the update kernel accumulates
+        into them in place (the reference adds four freshly computed vectors to the four states, stat_scores.py:43-55:
+        a zero-fill and four small additions per update).  States that are not consecutive in memory yet - after
+        `reset`, `to`, a state sync - are re-pointed at a common buffer with `Tensor.set_`: the tensor OBJECTS stay,
+        so compute-group members that alias them follow.  None when the states are not CUDA int64 tensors."""
+        if self.multidim_average != "global":
+            return None
+        tp, fp, tn, fn = self.tp, self.fp, self.tn, self.fn
+        if not (isinstance(tp, Tensor) and tp.is_cuda and tp.dtype == torch.int64 and tp.numel() > 0):
+            return None
+        n = tp.numel()
+        for t in (tp, fp, tn, fn):
+            if not (isinstance(t, Tensor) and t.dtype == torch.int64 and t.numel() == n and t.is_contiguous()
+                    and t.device == tp.device):
+                return None
+        ptr, step = tp.data_ptr(), 8 * n
+        if not (fp.data_ptr() == ptr + step and tn.data_ptr() == ptr + 2 * step and fn.data_ptr() == ptr + 3 * step
+                and fn.untyped_storage().data_ptr() == tp.untyped_storage().data_ptr()):
+            arena = torch.stack([tp.reshape(-1), fp.reshape(-1), tn.reshape(-1), fn.reshape(-1)])
+            for i, t in enumerate((tp, fp, tn, fn)):
+                t.set_(arena.untyped_storage(), i * n, t.shape, t.stride())
+        return tp.as_strided((4, n), (n, 1))
+
+    def _update_state(self, tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, packed: Optional[Tensor] = None) -> None:
+        if packed is not None and isinstance(tp, Tensor):
+            if tp.data_ptr() == packed.data_ptr():
+                return  # the kernel has accumulated into the states themselves
+            n, ptr = packed.shape[1], tp.data_ptr()
+            if (tp.dtype == torch.int64 and tp.numel() == n and fp.data_ptr() == ptr + 8 * n
+                    and tn.data_ptr() == ptr + 16 * n and fn.data_ptr() == ptr + 24 * n
+                    and fn.untyped_storage().data_ptr() == tp.untyped_storage().data_ptr()):
+                packed.add_(tp.as_strided((4, n), (n, 1)))  # the rows of one (4, n) result: one addition, not four
+                return
         if self.multidim_average == "samplewise":
             self.tp.append(tp)
             self.fp.append(fp)
@@ -71,10 +104,11 @@ class BinaryStatScores(_AbstractStatScores):
         if self.validate_args:
             with fv:
                 F._binary_stat_scores_tensor_validation(preds, target, self.multidim_average, self.ignore_index)
+        packed = self._packed_states()
         tp, fp, tn, fn = F._binary_stat_scores_update_fused(preds, target, self.threshold, self.multidim_average,
-                                                            self.ignore_index)
+                                                            self.ignore_index, out=None if fv.enabled else packed)
         fv.finish(preds.device)  # before the state is touched, like the reference's up-front validation
-        self._update_state(tp, fp, tn, fn)
+        self._update_state(tp, fp, tn, fn, packed)
 
     def compute(self) -> Tensor:
         tp, fp, tn, fn = self._final_state()
@@ -109,11 +143,12 @@ class MulticlassStatScores(_AbstractStatScores):
             with fv:
                 F._multiclass_stat_scores_tensor_validation(preds, target, self.num_classes, self.multidim_average,
                                                             self.ignore_index)
+        packed = self._packed_states()
         tp, fp, tn, fn = F._multiclass_stat_scores_update_fused(preds, target, self.num_classes, self.top_k,
                                                                 self.average, self.multidim_average,
-                                                                self.ignore_index)
+                                                                self.ignore_index, out=None if fv.enabled else packed)
         fv.finish(preds.device, self.num_classes)
-        self._update_state(tp, fp, tn, fn)
+        self._update_state(tp, fp, tn, fn, packed)
 
     def _final_state(self) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
         out = super()._final_state()
@@ -152,10 +187,12 @@ class MultilabelStatScores(_AbstractStatScores):
             with fv:
                 F._multilabel_stat_scores_tensor_validation(preds, target, self.num_labels, self.multidim_average,
                                                             self.ignore_index)
+        packed = self._packed_states()
         tp, fp, tn, fn = F._multilabel_stat_scores_update_fused(preds, target, self.num_labels, self.threshold,
-                                                                self.multidim_average, self.ignore_index)
+                                                                self.multidim_average, self.ignore_index,
+                                                                out=None if fv.enabled else packed)
         fv.finish(preds.device)
-        self._update_state(tp, fp, tn, fn)
+        self._update_state(tp, fp, tn, fn, packed)
 
     def compute(self) -> Tensor:
         tp, fp, tn, fn = self._final_state()

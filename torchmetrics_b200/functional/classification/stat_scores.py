@@ -148,8 +148,10 @@ def _multiclass_stat_scores_format(preds: Tensor, target: Tensor, top_k: int = 1
 
 def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: int, top_k: int = 1,
                                    average: Optional[str] = "macro", multidim_average: str = "global",
-                                   ignore_index: Optional[int] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
-    """stat_scores.py:344-419."""
+                                   ignore_index: Optional[int] = None,
+                                   out: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """stat_scores.py:344-419.  `out`: optional (4, C) int64 accumulator for the branches that count per class; the
+    returned rows are then its rows (the other branches ignore it and return fresh tensors)."""
     dev = preds.device
     if (multidim_average == "global" and top_k > 1 and preds.is_cuda and preds.is_floating_point()
             and preds.ndim == target.ndim + 1):
@@ -157,7 +159,7 @@ def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: i
         # (:363-393); the class ids of the k highest scores are all the kernel needs (K1c, top-k form)
         idx = preds.topk(top_k, dim=1).indices  # same call as select_topk: ties resolve identically
         idx = torch.movedim(idx, 1, -1).reshape(-1, top_k)
-        stats = torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
+        stats = out if out is not None else torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
         _native.class_stats_topk_update_(stats, idx, target.reshape(-1), num_classes, ignore_index)
         return stats[0], stats[1], stats[2], stats[3]
     if multidim_average == "samplewise" and top_k == 1 and not preds.is_floating_point():
@@ -176,7 +178,7 @@ def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: i
         return tp, fp, tn, fn
     # the reference fills a C x C confusion matrix and reduces it (:395-419); the four vectors only need three
     # length-C histograms (K1c), so nothing of size C*C is allocated, zeroed or summed
-    stats = torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
+    stats = out if out is not None else torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
     _native.class_stats_update_(stats, preds, target, num_classes, ignore_index)
     return stats[0], stats[1], stats[2], stats[3]
 
@@ -214,15 +216,18 @@ def _multiclass_stat_scores_reports_values(top_k: int, average: Optional[str], m
 
 def _multiclass_stat_scores_update_fused(preds: Tensor, target: Tensor, num_classes: int, top_k: int = 1,
                                          average: Optional[str] = "macro", multidim_average: str = "global",
-                                         ignore_index: Optional[int] = None):
+                                         ignore_index: Optional[int] = None, out: Optional[Tensor] = None):
+    if out is not None and tuple(out.shape) != (4, num_classes):
+        out = None  # micro-averaged states hold one number each
     if (top_k == 1 and multidim_average == "global" and average != "micro" and preds.ndim == 2 and target.ndim == 1
             and preds.is_cuda and preds.is_floating_point() and preds.shape[1] == num_classes):
         # (N, C) scores: the argmax of `_format` rides on the counting kernel, one warp per row (K1c, argmax form)
-        stats = torch.zeros(4, num_classes, dtype=torch.int64, device=preds.device)
+        stats = out if out is not None else torch.zeros(4, num_classes, dtype=torch.int64, device=preds.device)
         _native.class_stats_argmax_update_(stats, preds, target, num_classes, ignore_index)
         return stats[0], stats[1], stats[2], stats[3]
     preds, target = _multiclass_stat_scores_format(preds, target, top_k)
-    return _multiclass_stat_scores_update(preds, target, num_classes, top_k, average, multidim_average, ignore_index)
+    return _multiclass_stat_scores_update(preds, target, num_classes, top_k, average, multidim_average, ignore_index,
+                                          out)
 
 
 def _multiclass_stat_scores_compute(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str] = "macro",
