@@ -778,3 +778,47 @@ def test_stat_scores_bad_batch_leaves_state_untouched():
     with pytest.raises(RuntimeError):
         m.update(good_p, bad_t)
     assert torch.equal(m.compute(), before)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("validate", [False, True])
+@pytest.mark.parametrize("groups_first", [False, True])
+def test_collection_forward_batch_values_and_running_state(groups_first, validate):
+    """forward() of the stat-score family (alone, and as a compute group served by one update) returns the batch's own
+    value and leaves the running state equal to plain accumulation."""
+    tm = _tm()
+    F = tm.functional
+    C = 40
+    g = torch.Generator().manual_seed(5)
+    batches = [(torch.randn(200, C, generator=g).to(DEV), torch.randint(0, C, (200,), generator=g).to(DEV))
+               for _ in range(4)]
+    mc = tm.MetricCollection([tm.MulticlassAccuracy(C, validate_args=validate),
+                              tm.MulticlassPrecision(C, validate_args=validate),
+                              tm.MulticlassRecall(C, average="micro", validate_args=validate),
+                              tm.MulticlassF1Score(C, average=None, validate_args=validate)]).to(DEV)
+    fns = {"MulticlassAccuracy": lambda p, t: F.multiclass_accuracy(p, t, C, validate_args=False),
+           "MulticlassPrecision": lambda p, t: F.multiclass_precision(p, t, C, validate_args=False),
+           "MulticlassRecall": lambda p, t: F.multiclass_recall(p, t, C, average="micro", validate_args=False),
+           "MulticlassF1Score": lambda p, t: F.multiclass_f1_score(p, t, C, average=None, validate_args=False)}
+    seen = []
+    if groups_first:  # compute groups are formed by the first update: Accuracy / Precision / F1 share their states
+        mc.update(*batches[0])
+        seen.append(0)
+        assert any(len(v) > 1 for v in mc.compute_groups.values())
+    for i in (1, 2, 3):
+        out = mc(*batches[i])
+        seen.append(i)
+        for k, fn in fns.items():
+            assert torch.equal(out[k], fn(*batches[i])), (k, i)
+    total = mc.compute()
+    p = torch.cat([batches[i][0] for i in seen])
+    t = torch.cat([batches[i][1] for i in seen])
+    for k, fn in fns.items():
+        assert torch.equal(total[k], fn(p, t)), k
+    # a single metric outside any collection
+    m = tm.MulticlassF1Score(C, validate_args=validate).to(DEV)
+    for i in range(3):
+        assert torch.equal(m(*batches[i]), F.multiclass_f1_score(*batches[i], C, validate_args=False))
+    assert torch.equal(m.compute(), F.multiclass_f1_score(torch.cat([b[0] for b in batches[:3]]),
+                                                         torch.cat([b[1] for b in batches[:3]]), C, validate_args=False))
+    assert m._update_count == 3

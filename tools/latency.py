@@ -59,3 +59,37 @@ S = import_module("torchmetrics_b200.functional.classification.stat_scores")
 p3, t2 = S._multiclass_stat_scores_format(big, bigl, 5)
 bench("  reference's one-hot branch (torch ops on the device), same input", lambda: S._multiclass_stat_scores_onehot(p3, t2, C, 5, "global", None), reps=100)
 bench("  torch.topk alone", lambda: big.topk(5, dim=1), reps=100)
+
+# forward(): the call a training loop makes every step
+for va in (True, False):
+    m = tm.classification.MulticlassF1Score(num_classes=C, validate_args=va).to(DEV)
+    bench(f"MulticlassF1Score(C=1000).forward(logits[256,1000]) validate={va}", lambda: m(logits, labels))
+    coll2 = tm.MetricCollection([tm.classification.MulticlassAccuracy(num_classes=C, validate_args=va),
+                                 tm.classification.MulticlassPrecision(num_classes=C, validate_args=va),
+                                 tm.classification.MulticlassRecall(num_classes=C, validate_args=va),
+                                 tm.classification.MulticlassF1Score(num_classes=C, validate_args=va)]).to(DEV)
+    bench(f"MetricCollection[Acc,P,R,F1](C=1000).forward only (no compute groups) validate={va}",
+          lambda: coll2(logits, labels))
+
+# the unmodified reference on the same GPU (torch ops on the device), when it travelled with the snapshot
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+try:
+    from bench import _import_reference
+
+    ref, where = _import_reference()
+except Exception:
+    ref = None
+if ref is not None:
+    R = ref.classification
+    for va in (True, False):
+        m = R.MulticlassF1Score(num_classes=C, validate_args=va).to(DEV)
+        bench(f"reference MulticlassF1Score(C=1000).update(logits[256,1000]) validate={va}", lambda: m.update(logits, labels))
+        bench(f"reference MulticlassF1Score(C=1000).forward(logits[256,1000]) validate={va}", lambda: m(logits, labels))
+        rc = ref.MetricCollection([R.MulticlassAccuracy(num_classes=C, validate_args=va),
+                                   R.MulticlassPrecision(num_classes=C, validate_args=va),
+                                   R.MulticlassRecall(num_classes=C, validate_args=va),
+                                   R.MulticlassF1Score(num_classes=C, validate_args=va)]).to(DEV)
+        bench(f"reference MetricCollection[Acc,P,R,F1](C=1000).update validate={va}", lambda: rc.update(logits, labels))
+        bench(f"reference MetricCollection[Acc,P,R,F1](C=1000).forward validate={va}", lambda: rc(logits, labels))
+        m = R.BinaryAUROC(thresholds=200, validate_args=va).to(DEV)
+        bench(f"reference BinaryAUROC(thresholds=200).update(p[4096]) validate={va}", lambda: m.update(p, t))

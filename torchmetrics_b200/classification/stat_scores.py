@@ -1,6 +1,6 @@
 """Stateful tp/fp/tn/fn metrics (reference: classification/stat_scores.py:43-551)."""
 from importlib import import_module
-from typing import Any, Callable, List, Optional, Tuple, Union
+from typing import Any, Callable, List, Optional, Sequence, Tuple, Union
 
 import torch
 from torch import Tensor
@@ -81,6 +81,50 @@ class _AbstractStatScores(Metric):
     def _final_state(self) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
         return dim_zero_cat(self.tp), dim_zero_cat(self.fp), dim_zero_cat(self.tn), dim_zero_cat(self.fn)
 
+    # ------------------------------------------------------------------ forward() on packed states
+    def _forward_batch_values(self, group: Sequence["_AbstractStatScores"], args: Any, kwargs: Any) -> Optional[list]:
+        """`forward` of every metric in `group` - this metric first, the others alias its state tensors - with ONE update.
+
+        The generic route (metric.py `_forward_reduce_state_update`; reference metric.py:344-381) resets to fresh states
+        (four clones), updates them, computes, and adds them to the saved running states (four additions) - per metric.
+        Here the batch goes straight into the running states (they are one buffer the kernel accumulates into) and its
+        own counts are the difference to a snapshot of that buffer: one clone and one subtraction, whatever the size of
+        the group.  Returns None when the route does not apply (states not packed, a member synced on step, ...);
+        nothing has been touched then."""
+        for m in group:
+            if (m.dist_sync_on_step or m.full_state_update is not False or m._is_synced or m.compute_on_cpu
+                    or m.multidim_average != "global"):
+                return None
+        packed = self._packed_states()
+        if packed is None:
+            return None
+        before = packed.clone()
+        self.update(*args, **kwargs)  # raises before the states change when the batch fails validation
+        batch = packed - before
+        if len(group) > 1 and hasattr(self, "num_classes"):
+            # the kernel's error word (label outside [0, C)) is read once for the group, not by every member's compute
+            _native.raise_on_status(packed.device, self.num_classes)
+        values = []
+        for m in group:
+            saved = (m.tp, m.fp, m.tn, m.fn)
+            m._update_count = self._update_count
+            with m._batch_scope():
+                try:
+                    m.__dict__["_status_settled"] = len(group) > 1
+                    m.tp, m.fp, m.tn, m.fn = (batch[i].view(saved[i].shape) for i in range(4))
+                    values.append(m.compute())
+                finally:
+                    m.tp, m.fp, m.tn, m.fn = saved
+                    m.__dict__["_status_settled"] = False
+        return values
+
+    def _forward_reduce_state_update(self, *args: Any, **kwargs: Any) -> Any:
+        if not self.__dict__.get("_state_shared", False):  # see MetricCollection._compute_groups_create_state_ref
+            values = self._forward_batch_values([self], args, kwargs)
+            if values is not None:
+                return values[0]
+        return super()._forward_reduce_state_update(*args, **kwargs)
+
 
 class BinaryStatScores(_AbstractStatScores):
     is_differentiable = False
@@ -152,7 +196,7 @@ class MulticlassStatScores(_AbstractStatScores):
 
     def _final_state(self) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
         out = super()._final_state()
-        if out[0].is_cuda:
+        if out[0].is_cuda and not self.__dict__.get("_status_settled", False):
             _native.raise_on_status(out[0].device, self.num_classes)
         return out
 

@@ -128,6 +128,9 @@ class MetricCollection(ModuleDict):
         if not self._state_is_copy:
             for members in self._groups.values():
                 leader = getattr(self, members[0])
+                # metrics whose state tensors are shared must not accumulate into them in place on their own
+                # (classification/stat_scores.py `_forward_reduce_state_update`)
+                leader.__dict__["_state_shared"] = not copy and len(members) > 1
                 for name in members[1:]:
                     m = getattr(self, name)
                     for state in leader._defaults:
@@ -135,6 +138,7 @@ class MetricCollection(ModuleDict):
                         setattr(m, state, deepcopy(val) if copy else val)
                     m._update_count = leader._update_count
                     m._computed = deepcopy(leader._computed) if copy else leader._computed
+                    m.__dict__["_state_shared"] = not copy
         self._state_is_copy = copy
 
     def compute(self) -> Dict[str, Any]:
@@ -183,8 +187,12 @@ class MetricCollection(ModuleDict):
         # link the group members to their leader's state once; the loops below walk the module table directly
         self._compute_groups_create_state_ref(False)
         members = list(self._modules.items())
+        if method_name == "forward":
+            result.update(self._forward_groups(args, kwargs))
         try:
             for k, m in members:
+                if k in result:
+                    continue
                 result[k] = m.compute() if method_name == "compute" else m(*args, **m._filter_kwargs(**kwargs))
         finally:
             if fused:
@@ -213,6 +221,32 @@ class MetricCollection(ModuleDict):
                     key = f"{key}{m.postfix}"
                 flat[key] = v
         return {self._set_name(k): v for k, v in flat.items()}
+
+    def _forward_groups(self, args: Any, kwargs: Any) -> Dict[str, Any]:
+        """`forward` of whole compute groups with one update per group, where the leader knows how
+        (`_forward_batch_values`: the stat-score family on packed states).  The reference forwards every member on its
+        own (collections.py:194-231 via `_compute_and_reduce`); the values are the same, the members keep sharing the
+        leader's state afterwards.  Returns {module key: batch value} for the members it served."""
+        served: Dict[str, Any] = {}
+        if not (self._enable_compute_groups and self._groups_checked) or self._state_is_copy:
+            return served
+        for names in self._groups.values():
+            if len(names) < 2:
+                continue
+            group = [self._modules[n] for n in names]
+            fast = getattr(group[0], "_forward_batch_values", None)
+            if fast is None or any(getattr(m, "_forward_batch_values", None) is None for m in group):
+                continue
+            kw = group[0]._filter_kwargs(**kwargs)
+            if any(m._filter_kwargs(**kwargs) != kw for m in group[1:]):
+                continue
+            values = fast(group, args, kw)
+            if values is None:
+                continue
+            for n, m, v in zip(names, group, values):
+                m._forward_cache = v
+                served[n] = v
+        return served
 
     def reset(self) -> None:
         for m in self.values(copy_state=False):
