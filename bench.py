@@ -170,6 +170,55 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def reference_on_gpu(dev):
+    """BASELINE.md section 5's second comparator: the unmodified reference with its tensors on the B200 (ATen bincount,
+    compare-and-sum loops, CUB sort) - the reference ships no kernels of its own.  Device-timed, inputs resident."""
+    ref, where = _import_reference()
+    if ref is None:
+        return {"unavailable": "reference not importable"}
+    import torch
+
+    R = ref.classification
+
+    def timed(fn, reps):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    out = {"source": where, "note": "torchmetrics 1.4.0dev classes, validate_args=False, CUDA tensors, ms per update"}
+    g = torch.Generator(device=dev).manual_seed(99)
+    n = 1 << 24
+    p = torch.randint(0, NUM_CLASSES, (n,), device=dev, generator=g)
+    t = torch.randint(0, NUM_CLASSES, (n,), device=dev, generator=g)
+    m = R.MulticlassConfusionMatrix(num_classes=NUM_CLASSES, validate_args=False).to(dev)
+    out["confmat_C1000_2p24_ms"] = timed(lambda: m.update(p, t), 5)
+    del m, p, t
+    sc = torch.rand(n, device=dev, generator=g)
+    lb = (torch.rand(n, device=dev, generator=g) < 0.5).long()
+    m = R.BinaryAUROC(thresholds=200, validate_args=False).to(dev)
+    out["binned_auroc_T200_2p24_ms"] = timed(lambda: m.update(sc, lb), 2)
+    m = R.BinaryAUROC(thresholds=None, validate_args=False).to(dev)
+    m.update(sc, lb)
+
+    def exact():
+        m._computed = None
+        return m.compute()
+
+    out["exact_auroc_2p24_compute_ms"] = timed(exact, 2)
+    del m, sc, lb
+    mp = torch.rand(1 << 20, 100, device=dev, generator=g)
+    mt = (torch.rand(1 << 20, 100, device=dev, generator=g) < 0.5).long()
+    m = R.MultilabelStatScores(num_labels=100, validate_args=False).to(dev)
+    out["multilabel_stat_scores_L100_2p20rows_ms"] = timed(lambda: m.update(mp, mt), 2)
+    return out
+
+
 def cpu_baseline_sample(seconds=10.0):
     """Bounded CPU sample of the same workload on the box's host cores: the reference's own code when it can be
     imported (kind "reference"), else the C/OpenMP port."""
@@ -596,6 +645,13 @@ def main():
             }
             del pm
         del ep, et, em
+
+    # ------------------------------------------------------------------ the reference's own torch ops on this GPU
+    if not args.skip_extra and world == 1:
+        try:
+            extra["reference_on_same_gpu"] = reference_on_gpu(dev)
+        except Exception as err:  # a comparator, never a reason to lose the bench line
+            extra["reference_on_same_gpu"] = {"unavailable": f"{type(err).__name__}: {err}"[:200]}
 
     # ------------------------------------------------------------------ CPU baseline (rank 0, N=1 only)
     cpu_baseline = None
