@@ -21,6 +21,11 @@
  *     to pay for the synchronisation (the Python layer does so lazily, on compute()).
  *   - vector loads need natural alignment of the element type times the vector width: every data
  *     pointer must be 32-byte aligned (torch allocations are; offset views must be copied first).
+ *   - the streaming kernels of tmb_confmat_update_ws and tmb_binned_curve_update* are launched with the
+ *     programmatic-stream-serialization attribute: their set-up (shared-memory clears, barrier init)
+ *     may run under the tail of the kernel that precedes them in `stream`; they execute
+ *     griddepcontrol.wait before the first access to global memory, so the results are those of plain
+ *     stream order whatever that preceding kernel is.
  */
 #ifndef TM_B200_H
 #define TM_B200_H
