@@ -318,6 +318,13 @@ TMB_API int tmb_stat_scores_rows(const void* preds_dev, int preds_dtype, const v
 TMB_API int tmb_class_stats_rows(const void* preds_dev, int preds_dtype, const void* target_dev, int target_dtype,
                                  int64_t n_rows, int64_t width, int64_t num_classes, int has_ignore,
                                  int64_t ignore_index, int64_t* out_dev, int32_t* status_dev, void* stream);
+/* The same with top_k > 1 (`select_topk` + one-hot in the reference, stat_scores.py:363-393): topk_ids_dev holds the
+ * class ids of the k highest scores of every element, (n_rows, width, top_k) row-major
+ * (`preds.topk(k, dim=1).indices` moved last); a class among them that is not the target counts as a false positive of
+ * that class, the target as a hit when it is among them and as a miss otherwise. */
+TMB_API int tmb_class_stats_rows_topk(const void* topk_ids_dev, int ids_dtype, const void* target_dev, int target_dtype,
+                                      int64_t n_rows, int64_t width, int top_k, int64_t num_classes, int has_ignore,
+                                      int64_t ignore_index, int64_t* out_dev, int32_t* status_dev, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Fused reducer: count states -> score, one launch.

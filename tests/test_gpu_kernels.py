@@ -1007,3 +1007,37 @@ def test_stat_reduce_is_one_launch_per_metric():
     finally:
         _native.stat_reduce = orig
     assert len(calls) == 5  # one launch per compute() (plus torch.sum over the labels for the macro average)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ignore_index", [None, 3, -1])
+@pytest.mark.parametrize("top_k", [2, 5])
+def test_class_stats_rows_topk_matches_onehot_branch(top_k, ignore_index):
+    """samplewise multiclass statistics with top_k > 1: the row-wise kernel on the top-k class ids against the
+    reference's one-hot formulation (stat_scores.py:363-393) evaluated with torch ops on the same inputs."""
+    from importlib import import_module
+
+    S = import_module("torchmetrics_b200.functional.classification.stat_scores")
+    C, N, X = 11, 37, 53
+    g = torch.Generator().manual_seed(17 + top_k)
+    preds = torch.randn(N, C, X, generator=g)
+    preds[:, :, ::7] = preds[:, :1, ::7]  # ties between all classes at some positions
+    target = torch.randint(0, C, (N, X), generator=g)
+    if ignore_index is not None:
+        target[torch.rand(N, X, generator=g) < 0.2] = ignore_index
+    preds, target = preds.to(DEV), target.to(DEV)
+    want = S._multiclass_stat_scores_onehot(preds, target, C, top_k, "samplewise", ignore_index)
+    got = S._multiclass_stat_scores_update(preds, target, C, top_k, "macro", "samplewise", ignore_index)
+    for w, g_, name in zip(want, got, ("tp", "fp", "tn", "fn")):
+        assert torch.equal(g_, w), name
+    # through the public function and the module (cat states)
+    import torchmetrics_b200 as tm
+
+    f = tm.functional.multiclass_stat_scores(preds, target, C, average=None, top_k=top_k, multidim_average="samplewise",
+                                             ignore_index=ignore_index, validate_args=False)
+    assert torch.equal(f, torch.stack([*want, want[0] + want[3]], dim=-1))
+    m = tm.MulticlassStatScores(C, top_k=top_k, average=None, multidim_average="samplewise", ignore_index=ignore_index,
+                                validate_args=False).to(DEV)
+    m.update(preds[:20], target[:20])
+    m.update(preds[20:], target[20:])
+    assert torch.equal(m.compute(), f)

@@ -98,6 +98,9 @@ _SIGNATURES = {
                                         _c.c_double, _c.c_int, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p]),
     "tmb_class_stats_rows": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
                                         _c.c_int64, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_void_p]),
+    "tmb_class_stats_rows_topk": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int64, _c.c_int64,
+                                             _c.c_int, _c.c_int64, _c.c_int, _c.c_int64, _c.c_void_p, _c.c_void_p,
+                                             _c.c_void_p]),
     "tmb_stat_reduce": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_int,
                                    _c.c_int, _c.c_int, _c.c_double, _c.c_void_p, _c.c_void_p]),
 }
@@ -465,18 +468,27 @@ def stat_scores_rows(preds: Tensor, target: Tensor, width: int, threshold: float
     return out
 
 
-def class_stats_rows(preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int] = None) -> Tensor:
-    """(4, n_rows, C) int64 [tp|fp|tn|fn] per sample and class of (n_rows, width) label tensors (K1c, row-wise)."""
+def class_stats_rows(preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int] = None,
+                     top_k: int = 1) -> Tensor:
+    """(4, n_rows, C) int64 [tp|fp|tn|fn] per sample and class of (n_rows, width) label tensors (K1c, row-wise).
+    With `top_k` > 1, `preds` is (n_rows, width, top_k): the class ids of the k highest scores of every element."""
     dev = require_cuda(preds, target)
-    assert preds.shape == target.shape and preds.ndim == 2
-    n_rows, width = preds.shape
+    assert target.ndim == 2 and tuple(preds.shape) == (tuple(target.shape) + ((top_k,) if top_k > 1 else ()))
+    n_rows, width = target.shape
     preds, target = as_kernel_labels(preds), as_kernel_labels(target)
     out = torch.empty(4, n_rows, num_classes, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
-        rc = load().tmb_class_stats_rows(preds.data_ptr(), dtype_code(preds), target.data_ptr(), dtype_code(target),
-                                         n_rows, width, num_classes, ignore_index is not None,
-                                         0 if ignore_index is None else int(ignore_index), out.data_ptr(),
-                                         scratch(dev).status.data_ptr(), _stream_ptr(dev))
+        if top_k > 1:
+            rc = load().tmb_class_stats_rows_topk(preds.data_ptr(), dtype_code(preds), target.data_ptr(),
+                                                  dtype_code(target), n_rows, width, top_k, num_classes,
+                                                  ignore_index is not None,
+                                                  0 if ignore_index is None else int(ignore_index), out.data_ptr(),
+                                                  scratch(dev).status.data_ptr(), _stream_ptr(dev))
+        else:
+            rc = load().tmb_class_stats_rows(preds.data_ptr(), dtype_code(preds), target.data_ptr(),
+                                             dtype_code(target), n_rows, width, num_classes, ignore_index is not None,
+                                             0 if ignore_index is None else int(ignore_index), out.data_ptr(),
+                                             scratch(dev).status.data_ptr(), _stream_ptr(dev))
     if rc == -4:
         raise RuntimeError("tmb_class_stats_rows failed with TMB_ERR_TOO_LARGE: " + load().tmb_last_cuda_error().decode())
     _check(rc, "tmb_class_stats_rows")

@@ -391,6 +391,7 @@ struct ClassRowsParams {
   const void* preds;
   const void* target;
   long long n_rows, width, C;
+  int top_k;       // class ids per element of `preds` ((n_rows, width, top_k) row-major); 1 = plain labels
   int has_ignore;
   long long ignore;
   long long* out;  // [4][n_rows][C]
@@ -416,19 +417,29 @@ __global__ void __launch_bounds__(kRowsThreads) class_stats_rows_kernel(const Cl
     const long long base = row * P.width;
     u32 valid = 0;
     for (long long j = lane; j < P.width; j += 32) {
-      const long long t = as_i64(target[base + j]), p = as_i64(preds[base + j]);
+      const long long t = as_i64(target[base + j]);
       if (P.has_ignore && t == P.ignore) continue;
-      if ((u64)t >= (u64)C || (u64)p >= (u64)C) {
+      if ((u64)t >= (u64)C) {
         bad = 1;  // the reference's one_hot raises on such a label
         continue;
       }
-      ++valid;
-      if (p == t) {
-        atomicAdd(&hit[t], 1u);
-      } else {
-        atomicAdd(&pred_of[p], 1u);
-        atomicAdd(&targ_of[t], 1u);
+      // top_k class ids per element (the k highest scores; one id for label inputs): a class among them that is not
+      // the target is a false positive of that class, the target is a hit if it is among them and a miss otherwise
+      const PT* ids = preds + (base + j) * P.top_k;
+      bool in_range = true;
+      for (int q = 0; q < P.top_k; ++q) in_range &= (u64)as_i64(ids[q]) < (u64)C;
+      if (!in_range) {
+        bad = 1;
+        continue;
       }
+      ++valid;
+      bool hit_target = false;
+      for (int q = 0; q < P.top_k; ++q) {
+        const long long p = as_i64(ids[q]);
+        if (p == t) hit_target = true;
+        else atomicAdd(&pred_of[p], 1u);
+      }
+      atomicAdd(hit_target ? &hit[t] : &targ_of[t], 1u);
     }
     valid = __reduce_add_sync(0xffffffffu, valid);
     __syncwarp();
@@ -523,10 +534,11 @@ extern "C" int tmb_stat_scores_rows(const void* preds, int preds_dtype, const vo
   return TMB_ERR_ARG;
 }
 
-extern "C" int tmb_class_stats_rows(const void* preds, int preds_dtype, const void* target, int target_dtype,
-                                    int64_t n_rows, int64_t width, int64_t num_classes, int has_ignore,
-                                    int64_t ignore_index, int64_t* out, int32_t* status, void* stream) {
-  if (n_rows < 0 || width < 0 || num_classes < 1 || !out || !status) return TMB_ERR_ARG;
+static int class_stats_rows_impl(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                 int64_t n_rows, int64_t width, int top_k, int64_t num_classes, int has_ignore,
+                                 int64_t ignore_index, int64_t* out, int32_t* status, void* stream) {
+  if (n_rows < 0 || width < 0 || num_classes < 1 || top_k < 1 || top_k > num_classes || !out || !status)
+    return TMB_ERR_ARG;
   if (n_rows == 0) return TMB_OK;
   if (width >= (1LL << 31)) return TMB_ERR_TOO_LARGE;
   cudaStream_t st = (cudaStream_t)stream;
@@ -550,6 +562,7 @@ extern "C" int tmb_class_stats_rows(const void* preds, int preds_dtype, const vo
   P.n_rows = n_rows;
   P.width = width;
   P.C = num_classes;
+  P.top_k = top_k;
   P.has_ignore = has_ignore ? 1 : 0;
   P.ignore = ignore_index;
   P.out = (long long*)out;
@@ -567,4 +580,19 @@ extern "C" int tmb_class_stats_rows(const void* preds, int preds_dtype, const vo
     })
   })
   return TMB_ERR_ARG;
+}
+
+extern "C" int tmb_class_stats_rows(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                    int64_t n_rows, int64_t width, int64_t num_classes, int has_ignore,
+                                    int64_t ignore_index, int64_t* out, int32_t* status, void* stream) {
+  return class_stats_rows_impl(preds, preds_dtype, target, target_dtype, n_rows, width, 1, num_classes, has_ignore,
+                               ignore_index, out, status, stream);
+}
+
+extern "C" int tmb_class_stats_rows_topk(const void* topk_ids, int ids_dtype, const void* target, int target_dtype,
+                                         int64_t n_rows, int64_t width, int top_k, int64_t num_classes,
+                                         int has_ignore, int64_t ignore_index, int64_t* out, int32_t* status,
+                                         void* stream) {
+  return class_stats_rows_impl(topk_ids, ids_dtype, target, target_dtype, n_rows, width, top_k, num_classes,
+                               has_ignore, ignore_index, out, status, stream);
 }

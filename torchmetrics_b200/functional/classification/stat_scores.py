@@ -162,6 +162,14 @@ def _multiclass_stat_scores_update(preds: Tensor, target: Tensor, num_classes: i
         stats = out if out is not None else torch.zeros(4, num_classes, dtype=torch.int64, device=dev)
         _native.class_stats_topk_update_(stats, idx, target.reshape(-1), num_classes, ignore_index)
         return stats[0], stats[1], stats[2], stats[3]
+    if (multidim_average == "samplewise" and top_k > 1 and preds.is_cuda and preds.is_floating_point()
+            and preds.ndim == target.ndim + 1 and target.ndim >= 2):
+        # (N, C, ...) scores: the ids of the k highest scores of every element, laid out (N, X, k), go through the same
+        # per-sample histograms (K1c, row-wise top-k form) instead of (N, X, C) one-hot tensors
+        n = preds.shape[0]
+        idx = torch.movedim(preds.topk(top_k, dim=1).indices, 1, -1).reshape(n, -1, top_k)
+        rows = _native.class_stats_rows(idx, target.reshape(n, -1), num_classes, ignore_index, top_k=top_k)
+        return rows[0], rows[1], rows[2], rows[3]
     if multidim_average == "samplewise" and top_k == 1 and not preds.is_floating_point():
         # (N, X) label tensors: per sample and class counts from three per-sample histograms (K1c, row-wise form)
         rows = _native.class_stats_rows(preds, target, num_classes, ignore_index)
