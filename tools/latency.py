@@ -68,7 +68,7 @@ for va in (True, False):
                                  tm.classification.MulticlassPrecision(num_classes=C, validate_args=va),
                                  tm.classification.MulticlassRecall(num_classes=C, validate_args=va),
                                  tm.classification.MulticlassF1Score(num_classes=C, validate_args=va)]).to(DEV)
-    bench(f"MetricCollection[Acc,P,R,F1](C=1000).forward only (no compute groups) validate={va}",
+    bench(f"MetricCollection[Acc,P,R,F1](C=1000).forward, never updated directly, validate={va}",
           lambda: coll2(logits, labels))
 
 # the unmodified reference on the same GPU (torch ops on the device), when it travelled with the snapshot

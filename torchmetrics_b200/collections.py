@@ -204,6 +204,14 @@ class MetricCollection(ModuleDict):
                         for state in ld._defaults:
                             setattr(m, state, getattr(ld, state))
 
+        if method_name == "forward" and self._enable_compute_groups and not self._groups_checked:
+            # the first forward leaves every metric with the state of one batch, exactly what `update` inspects to form
+            # the compute groups (collections.py:207-215 in the reference, which only does it there): from the second
+            # forward on a group is served by one update (`_forward_groups`)
+            self._merge_compute_groups()
+            self._compute_groups_create_state_ref()
+            self._groups_checked = True
+
         _, duplicates = _flatten_dict(result)
         flat: Dict[str, Any] = {}
         for k, m in members:
