@@ -13,8 +13,26 @@
 
 namespace tmb {
 
-constexpr int kClassThreads = 512;
-constexpr size_t kClassSmemBudget = 48 * 1024;  // bins per CTA: 3 * C u32 per copy
+#ifndef TMB_K1C_THREADS
+#define TMB_K1C_THREADS 512
+#endif
+#ifndef TMB_K1C_SMEM_KB
+#define TMB_K1C_SMEM_KB 48
+#endif
+#ifndef TMB_K1C_PER_SM
+#define TMB_K1C_PER_SM 3
+#endif
+#ifndef TMB_K1C_AM_PER_SM
+#define TMB_K1C_AM_PER_SM 4
+#endif
+constexpr int kClassThreads = TMB_K1C_THREADS;
+constexpr size_t kClassSmemBudget = TMB_K1C_SMEM_KB * 1024;  // bins per CTA: 3 * C u32 per copy
+// CTAs per SM of the label / top-k kernels.  Three, not the four that would fit: measured at C = 1000 on 2^24 / 2^26
+// int64 label pairs, 4 per SM 70.0 / 214 us, 3 per SM 53.6 / 162 us (58 -> 76 % and 76 -> 101 % of the measured copy
+// peak; profiles/r2_k1c_variants.log) - the fourth CTA's 48 KB of shared memory come out of the L1 the loads stream
+// through, and every CTA ends with 3 C atomics on the same 3 C global counters.
+constexpr int kClassCtasPerSm = TMB_K1C_PER_SM;
+constexpr int kClassArgmaxCtasPerSm = TMB_K1C_AM_PER_SM;
 
 struct ClassStatsWs {
   int ticket;
@@ -378,7 +396,7 @@ static int class_stats_launch(const void* preds, int preds_dtype, const void* ta
   P.copies = (int)copies;
   const size_t smem = copies * per_copy;
   long long want = ((top_k > 1 ? n : (n >> 2)) + kClassThreads - 1) / kClassThreads;
-  const long long cap = (long long)sm_count() * 4;
+  const long long cap = (long long)sm_count() * kClassCtasPerSm;
   const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
   cudaStream_t st = (cudaStream_t)stream;
   TMB_DISPATCH_INT(preds_dtype, PT, {
@@ -454,7 +472,7 @@ extern "C" int tmb_class_stats_argmax_update(const void* scores, int scores_dtyp
   P.group = group;
   const long long rows_per_cta = (long long)(kClassThreads / 32) * (32 / group);
   const long long want = (n + rows_per_cta - 1) / rows_per_cta;
-  const long long cap = (long long)sm_count() * 4;
+  const long long cap = (long long)sm_count() * kClassArgmaxCtasPerSm;
   const int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
   cudaStream_t st = (cudaStream_t)stream;
   TMB_DISPATCH_FLOAT(scores_dtype, ST, {
@@ -484,7 +502,7 @@ extern "C" int tmb_rows_argmax(const void* scores, int scores_dtype, int64_t n, 
   while (group < 32 && (long long)group * 8 < num_classes) group <<= 1;
   const long long rows_per_cta = (long long)(kClassThreads / 32) * (32 / group);
   const long long want = (n + rows_per_cta - 1) / rows_per_cta;
-  const long long cap = (long long)sm_count() * 4;
+  const long long cap = (long long)sm_count() * kClassArgmaxCtasPerSm;
   const int grid = (int)(want < cap ? want : cap);
   cudaStream_t st = (cudaStream_t)stream;
   TMB_DISPATCH_FLOAT(scores_dtype, ST, {
