@@ -245,12 +245,16 @@ static int launch_confmat(const PT* preds, const TT* target, long long n, long l
   } else if (algo != 2) {
     return TMB_ERR_ARG;
   } else {
-    // as many copies of the bins as fit ~100 KB (two CTAs per SM), at most one per warp
-    const size_t budget = 100 * 1024;
-    int copies = smem <= budget ? (int)(budget / smem) : 1;
-    if (copies > kSmemThreads / 32) copies = kSmemThreads / 32;
+    // One CTA of 1024 threads per SM.  Copies of the bins: one per warp while 32 of them fit 200 KB (C <= 39), else
+    // as many as fit 100 KB - more copies than that cost more to clear and merge than they save in contention.
+    // Measured against two CTAs per SM with 100 KB each (profiles/r2_k1s_variants.log, 2^24 / 2^26 int64 pairs):
+    // C=10 89.8 / 101 -> 90 / 105 % of the measured copy peak, C=32 82.5 / 94.9 -> 86.2 / 103.6 %, C=100 79.4 / 99
+    // -> 86 / 103.5 %, C=150 73.4 -> 82.5 % at 2^24: half as many CTAs end with C*C atomics on the same C*C cells.
+    int copies;
+    if (smem * (kSmemThreads / 32) <= (size_t)200 * 1024) copies = kSmemThreads / 32;
+    else copies = smem <= (size_t)100 * 1024 ? (int)((size_t)100 * 1024 / smem) : 1;
     const size_t dyn = smem * copies;
-    const int per_sm = dyn <= budget ? 2 : 1;
+    const int per_sm = 1;
     int grid = grid_for(nvec, kSmemThreads, per_sm);
     auto k = confmat_smem_kernel<PT, TT>;
     TMB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
