@@ -116,3 +116,30 @@ def test_nominal_reducers(c):
     close(PE._pearsons_contingency_coefficient_compute(cm), "pearson")
     close(TH._theils_u_compute(cm), "theils_u")
     close(TH._theils_u_compute(cm.T), "theils_u_rev")
+
+
+def test_cpu_states_keep_the_torch_op_reducers_and_the_generic_forward():
+    """The fused reducer kernel and the packed-state routes only exist for CUDA states: on CPU tensors the reducers
+    are the reference's torch ops and the stat-score modules report no packed view (so `forward` and `_update_state`
+    take the generic route)."""
+    import torch
+
+    import torchmetrics_b200 as tm
+    from torchmetrics_b200.functional.classification.f_beta import _fbeta_reduce
+    from torchmetrics_b200.functional.classification.precision_recall import _precision_recall_reduce
+    from torchmetrics_b200.utilities.compute import _fused_stat_reduce
+
+    tp, fp = torch.tensor([3, 0, 5]), torch.tensor([1, 0, 5])
+    tn, fn = torch.tensor([9, 9, 2]), torch.tensor([0, 4, 1])
+    assert _fused_stat_reduce("precision", tp, fp, tn, fn, "macro") is None
+    # compute.py:46-69 by hand: classes 0 and 2 score 3/4 and 5/10, class 1 never predicted (0), all three occur
+    assert torch.allclose(_precision_recall_reduce("precision", tp, fp, tn, fn, average="macro"),
+                          torch.tensor((0.75 + 0.0 + 0.5) / 3))
+    assert torch.allclose(_precision_recall_reduce("recall", tp, fp, tn, fn, average="micro"), torch.tensor(8 / 13))
+    assert torch.allclose(_fbeta_reduce(tp, fp, tn, fn, 1.0, average="none"),
+                          torch.tensor([6 / 7, 0.0, 10 / 16]))
+    m = tm.MultilabelF1Score(num_labels=3, validate_args=False)
+    assert m._packed_states() is None
+    m.tp, m.fp, m.tn, m.fn = tp, fp, tn, fn
+    m._update_count = 1
+    assert torch.allclose(m.compute(), torch.tensor((6 / 7 + 0.0 + 10 / 16) / 3))
