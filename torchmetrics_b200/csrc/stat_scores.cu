@@ -106,10 +106,21 @@ __device__ __forceinline__ void tally(PT pv, TT tv, const StatParams& P, typenam
   }
 }
 
+#ifndef TMB_K2_TILED_PER_SM
+#define TMB_K2_TILED_PER_SM 3
+#endif
+// resident CTAs per SM: four for the flat (L == 1) form, which needs 32 registers - binary stat scores went from
+// 64.7 / 86.6 / 94.4 % of the measured copy peak at 2^24 / 2^26 / 2^28 samples with two CTAs per SM to 70.6 / 95.7 /
+// 105.6 % (profiles/r2_k2flat_variants.log); the tiled form, whose per-label counters live in registers, runs three
+// (40 registers and 40 bytes of spills instead of 60 registers: L = 100 on 2^23 rows 1678 -> 1627 us, 91.5 -> 94.4 %,
+// profiles/r2_k2tiled_variants.log).
+constexpr int kStatFlatCtasPerSm = 4;
+constexpr int kStatTiledCtasPerSm = TMB_K2_TILED_PER_SM;
 // V = 4: L % 4 == 0, a thread owns 4 consecutive labels.  V = 1: any L, a thread owns one label.
 // FLAT (L == 1): every element belongs to label 0 and is read 4 at a time.
 template <typename PT, typename TT, bool SIGMOID, int V, bool FLAT>
-__global__ void __launch_bounds__(kStatThreads, 2) stat_scores_kernel(const StatParams P) {
+__global__ void __launch_bounds__(kStatThreads, FLAT ? kStatFlatCtasPerSm : kStatTiledCtasPerSm)
+stat_scores_kernel(const StatParams P) {
   using CT = typename CmpType<PT>::type;
   StatWs* ws = P.ws;
   if (P.only_if_flag && ws->flag_oor == 0) return;
@@ -243,7 +254,7 @@ static int launch_one(const StatParams& P, cudaStream_t st) {
   if (L == 1) {
     long long nvec = P.n_rows >> 2;
     long long want = (nvec + kStatThreads - 1) / kStatThreads;
-    long long cap = (long long)sm_count() * 2;
+    long long cap = (long long)sm_count() * kStatFlatCtasPerSm;
     int grid = (int)(want < 1 ? 1 : want < cap ? want : cap);
     stat_scores_kernel<PT, TT, SIGMOID, 1, true><<<grid, kStatThreads, 4 * sizeof(u32), st>>>(P);
   } else {
@@ -254,7 +265,7 @@ static int launch_one(const StatParams& P, cudaStream_t st) {
     const long long gy = (colgroups + CW - 1) / CW;
     if (gy > 65535) return TMB_ERR_TOO_LARGE;
     long long want = (P.n_rows + RP - 1) / RP;
-    long long cap = ((long long)sm_count() * 2 + gy - 1) / gy;
+    long long cap = ((long long)sm_count() * kStatTiledCtasPerSm + gy - 1) / gy;
     if (cap < 1) cap = 1;
     int gx = (int)(want < 1 ? 1 : want < cap ? want : cap);
     const size_t smem = (size_t)4 * CW * V * sizeof(u32);
